@@ -1,0 +1,809 @@
+#include "engine.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <mutex>
+#include <thread>
+
+#include "tables.h"
+
+using namespace phmm;
+
+namespace phmm {
+
+template <class T> cudaError_t PinnedBuf<T>::reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = std::max<size_t>(n + n / 4, 1024);
+    T *q = nullptr;
+    cudaError_t e = cudaHostAlloc((void **)&q, want * sizeof(T), cudaHostAllocDefault);
+    if (e != cudaSuccess) return e;
+    if (p) cudaFreeHost(p);
+    p = q; cap = want;
+    return cudaSuccess;
+}
+template <class T> void PinnedBuf<T>::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+template <class T> cudaError_t DevBuf<T>::reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = std::max<size_t>(n + n / 4, 1024);
+    T *q = nullptr;
+    cudaError_t e = cudaMalloc((void **)&q, want * sizeof(T));
+    if (e != cudaSuccess) return e;
+    if (p) cudaFree(p);
+    p = q; cap = want;
+    return cudaSuccess;
+}
+template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+
+void Slot::release() {
+    h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
+    h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release();
+    d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
+    d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
+    d_rescue.release(); d_fres.release(); d_out.release();
+    if (ev_begin) cudaEventDestroy(ev_begin);
+    if (ev_float_done) cudaEventDestroy(ev_float_done);
+    if (ev_end) cudaEventDestroy(ev_end);
+    if (stream) cudaStreamDestroy(stream);
+    ev_begin = ev_float_done = ev_end = nullptr; stream = nullptr;
+}
+
+}  // namespace phmm
+
+namespace {
+
+using clk = std::chrono::steady_clock;
+inline double ms_since(clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); }
+
+std::mutex g_err_mutex;   // plan_region runs on several threads and may report through fail()
+int fail(pairhmm_cuda_handle *h, int status, const std::string &msg) {
+    if (h) { std::lock_guard<std::mutex> lk(g_err_mutex); h->last_error = msg; }
+    return status;
+}
+int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
+    cudaGetLastError();  // clear sticky-less error state
+    return fail(h, e == cudaErrorMemoryAllocation ? PAIRHMM_ERR_OOM : PAIRHMM_ERR_CUDA,
+                std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(h, expr)                                                    \
+    do {                                                               \
+        cudaError_t _e = (expr);                                       \
+        if (_e != cudaSuccess) return fail_cuda((h), _e, #expr);       \
+    } while (0)
+
+// counters layout in d_counters: [0..8] work queues of the FP32 launches (per K), [9..17] rescue
+// counts (per K), [18..26] work queues of the FP64 launches (per K)
+constexpr int kCounterWords = 32;
+constexpr int kQueueF = 0, kRescueCount = 9, kQueueD = 18;
+
+// Runs fn(i) for i in [0,n) on up to `threads` std::threads (dynamic chunks of `grain`).
+template <class F> void parallel_for(size_t n, int threads, size_t grain, F fn) {
+    if (threads <= 1 || n <= grain) { for (size_t i = 0; i < n; ++i) fn(i); return; }
+    std::atomic<size_t> next{0};
+    auto body = [&] {
+        for (;;) {
+            size_t b = next.fetch_add(grain);
+            if (b >= n) break;
+            size_t e = std::min(n, b + grain);
+            for (size_t i = b; i < e; ++i) fn(i);
+        }
+    };
+    int nt = (int)std::min<size_t>((size_t)threads, (n + grain - 1) / grain);
+    std::vector<std::thread> th;
+    th.reserve(nt - 1);
+    for (int t = 1; t < nt; ++t) th.emplace_back(body);
+    body();
+    for (auto &t : th) t.join();
+}
+
+inline uint64_t mix64(uint64_t x) {
+    x ^= x >> 32; x *= 0xd6e8feb86659fd93ull; x ^= x >> 32; x *= 0xd6e8feb86659fd93ull; x ^= x >> 32;
+    return x;
+}
+uint64_t hash_bytes(const uint8_t *p, size_t n, uint64_t h) {
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, p + i, 8); h = mix64(h ^ w) + 0x9e3779b97f4a7c15ull; }
+    uint64_t w = 0;
+    if (i < n) std::memcpy(&w, p + i, n - i);
+    return mix64(h ^ w ^ (uint64_t)n);
+}
+uint64_t hash_read(const phmm_read &r) {
+    uint64_t h = 0x243f6a8885a308d3ull ^ (uint64_t)r.len;
+    h = hash_bytes(r.bases, r.len, h); h = hash_bytes(r.base_q, r.len, h); h = hash_bytes(r.ins_q, r.len, h);
+    h = hash_bytes(r.del_q, r.len, h); h = hash_bytes(r.gcp, r.len, h);
+    return h;
+}
+bool same_read(const phmm_read &a, const phmm_read &b) {
+    return a.len == b.len && !std::memcmp(a.bases, b.bases, a.len) && !std::memcmp(a.base_q, b.base_q, a.len) &&
+           !std::memcmp(a.ins_q, b.ins_q, a.len) && !std::memcmp(a.del_q, b.del_q, a.len) &&
+           !std::memcmp(a.gcp, b.gcp, a.len);
+}
+
+constexpr uint32_t kNoRead = 0xffffffffu;
+
+// Pass A for one region: read de-duplication (VectorLoglessPairHMM.cpp:83-103) and sizes.
+int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, uint32_t group_hint) {
+    pl = RegionPlan();
+    if (rv.n_reads < 0 || rv.n_haps < 0 || (rv.n_reads > 0 && !rv.reads) || (rv.n_haps > 0 && !rv.haps))
+        return fail(h, PAIRHMM_ERR_ARG, "null pointer or negative count in region");
+    pl.uniq_of_read.assign(rv.n_reads, kNoRead);
+    const bool dedup = h->cfg.dedup_reads != 0;
+    std::vector<uint32_t> table;   // open addressing: local unique index + 1
+    std::vector<uint64_t> hashes;
+    size_t mask = 0;
+    if (dedup && rv.n_reads > 1) {
+        size_t cap = 16; while (cap < (size_t)rv.n_reads * 2) cap <<= 1;
+        table.assign(cap, 0); mask = cap - 1; hashes.reserve(rv.n_reads);
+    }
+    int32_t hmax = 0;
+    for (int i = 0; i < rv.n_haps; ++i) {
+        const phmm_hap &hp = rv.haps[i];
+        if (hp.len < 0 || (hp.len > 0 && !hp.bases)) return fail(h, PAIRHMM_ERR_ARG, "bad haplotype");
+        pl.hap_bytes += (uint64_t)hp.len;
+        pl.hap_words += (uint32_t)hp.len + 1;
+        hmax = std::max(hmax, hp.len);
+    }
+    for (int i = 0; i < rv.n_reads; ++i) {
+        const phmm_read &r = rv.reads[i];
+        if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || !r.ins_q || !r.del_q || !r.gcp)))
+            return fail(h, PAIRHMM_ERR_ARG, "bad read");
+        if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
+        if (rows_per_lane(r.len) == 0)
+            return fail(h, PAIRHMM_ERR_ARG, "read longer than 255 bases: not supported by this build");
+        uint32_t u = kNoRead;
+        if (!table.empty()) {
+            const uint64_t hv = hash_read(r);
+            size_t s = (size_t)hv & mask;
+            while (table[s]) {
+                const uint32_t cand = table[s] - 1;
+                if (hashes[cand] == hv && same_read(rv.reads[pl.uniq_src[cand]], r)) { u = cand; break; }
+                s = (s + 1) & mask;
+            }
+            if (u == kNoRead) { table[s] = (uint32_t)pl.uniq_src.size() + 1; hashes.push_back(hv); }
+        }
+        if (u == kNoRead) {
+            u = (uint32_t)pl.uniq_src.size();
+            pl.uniq_src.push_back((uint32_t)i);
+            pl.read_bytes += (uint64_t)r.len;
+        }
+        pl.uniq_of_read[i] = u;
+    }
+    pl.n_uniq = (uint32_t)pl.uniq_src.size();
+    // haplotypes per work unit: all of them unless the chunk is too small to fill the GPU
+    // (group_hint) or the unit would get very long (tail balance)
+    uint32_t g = (uint32_t)std::max(1, rv.n_haps);
+    const uint32_t cap_cols = 16384u / (uint32_t)(hmax + 1);
+    g = std::min(g, std::max(1u, cap_cols));
+    if (group_hint) g = std::min(g, group_hint);
+    pl.group = g;
+    pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;
+    for (uint32_t j = 0; j < pl.n_uniq; ++j)
+        pl.unit_count[rows_per_lane(rv.reads[pl.uniq_src[j]].len)] += pl.n_groups;
+    return PAIRHMM_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// chunk = set of regions packed into one slot
+// ------------------------------------------------------------------------------------------------
+namespace phmm {
+
+int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n_regs, int threads) {
+    auto t0 = clk::now();
+    s.regions.assign(regs, regs + n_regs);
+    s.plans.resize(n_regs);
+    // group hint: if there are few reads, split haplotype runs so that every warp slot gets work
+    uint64_t total_reads = 0;
+    for (size_t i = 0; i < n_regs; ++i) total_reads += (uint64_t)std::max(0, regs[i].n_reads);
+    const uint64_t want_units = (uint64_t)h->sm_count * 24u * 3u;
+    uint32_t group_hint = 0;
+    if (total_reads && total_reads < want_units) {
+        uint64_t splits = (want_units + total_reads - 1) / total_reads;      // units wanted per read
+        uint32_t maxh = 1;
+        for (size_t i = 0; i < n_regs; ++i) maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
+        group_hint = (uint32_t)std::max<uint64_t>(1, maxh / std::min<uint64_t>(splits, maxh));
+    }
+    std::atomic<int> status{PAIRHMM_OK};
+    parallel_for(n_regs, threads, 8, [&](size_t i) {
+        int st = plan_region(h, s.regions[i], s.plans[i], group_hint);
+        if (st != PAIRHMM_OK) status.store(st);
+    });
+    if (status.load() != PAIRHMM_OK) return status.load();
+
+    // prefix sums
+    uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0;
+    uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
+    uint32_t bin_count[kMaxRowsPerLane + 1] = {0};
+    uint32_t bin_pairs[kMaxRowsPerLane + 1] = {0};
+    for (size_t i = 0; i < n_regs; ++i) {
+        RegionPlan &p = s.plans[i];
+        p.first_uniq = nu; p.read_byte_off = rbytes; p.first_hap = nh; p.hap_byte_off = hbytes;
+        p.hap_word_off = hw; p.hap_list_off = hl; p.upair_off = up;
+        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+            p.unit_off[k] = bin_count[k]; bin_count[k] += p.unit_count[k];
+            if (p.n_groups) bin_pairs[k] += p.unit_count[k] / p.n_groups * (uint32_t)s.regions[i].n_haps;
+        }
+        const uint64_t up_next = (uint64_t)up + (uint64_t)p.n_uniq * (uint64_t)s.regions[i].n_haps;
+        if (up_next > 0xfffffff0ull || rbytes + p.read_bytes > 0xfffffff0ull || (uint64_t)hw + p.hap_words > 0xfffffff0ull)
+            return fail(h, PAIRHMM_ERR_ARG, "chunk too large for 32-bit device indices (lower chunk_cells)");
+        nu += p.n_uniq; rbytes += p.read_bytes; nh += (uint32_t)s.regions[i].n_haps; hbytes += p.hap_bytes;
+        hw += p.hap_words; hl += (uint32_t)s.regions[i].n_haps; up = (uint32_t)up_next;
+        uint64_t rl = 0;
+        for (int r = 0; r < s.regions[i].n_reads; ++r) rl += (uint64_t)s.regions[i].reads[r].len;
+        cells += rl * p.hap_bytes;
+        pairs += (uint64_t)s.regions[i].n_reads * (uint64_t)s.regions[i].n_haps;
+        reads_in += (uint64_t)s.regions[i].n_reads;
+    }
+    s.bin_start[0] = s.bin_start[1] = 0;
+    s.rescue_base[0] = s.rescue_base[1] = 0;
+    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+        s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
+        s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
+    }
+    const uint32_t n_units = s.bin_start[kMaxRowsPerLane + 1];
+    s.plane = (rbytes + 15) & ~15ull;
+    s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
+    s.cells = cells; s.pairs = pairs; s.reads_in = reads_in;
+
+    cudaError_t e;
+#define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
+    RES(h_rd, s.plane * 5 + 16); RES(h_reads, nu + 1); RES(h_hapbytes, hbytes + 16); RES(h_hapoff, nh + 1);
+    RES(h_haps, nh + 1); RES(h_haplist, hl + 1); RES(h_units, n_units + 1); RES(h_out, up + 1); RES(h_flag, up + 1);
+    RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
+    RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
+    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+#undef RES
+
+    // pass B: copy bytes, fill descriptors and units
+    parallel_for(n_regs, threads, 4, [&](size_t i) {
+        const RegionView &rv = s.regions[i];
+        const RegionPlan &p = s.plans[i];
+        uint64_t ro = p.read_byte_off;
+        uint32_t fill[kMaxRowsPerLane + 1] = {0};
+        for (uint32_t j = 0; j < p.n_uniq; ++j) {
+            const phmm_read &r = rv.reads[p.uniq_src[j]];
+            uint8_t *d = s.h_rd.p + ro;
+            std::memcpy(d, r.bases, r.len); std::memcpy(d + s.plane, r.base_q, r.len);
+            std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
+            std::memcpy(d + 4 * s.plane, r.gcp, r.len);
+            s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
+            ro += (uint64_t)r.len;
+            const int k = rows_per_lane(r.len);
+            DevUnit *ud = s.h_units.p + s.bin_start[k] + p.unit_off[k] + fill[k];
+            for (uint32_t g = 0; g < p.n_groups; ++g) {
+                const uint32_t h0 = g * p.group;
+                ud[g] = DevUnit{p.first_uniq + j, p.hap_list_off + h0, std::min(p.group, (uint32_t)rv.n_haps - h0),
+                                p.upair_off + j * (uint32_t)rv.n_haps + h0};
+            }
+            fill[k] += p.n_groups;
+        }
+        uint64_t ho = p.hap_byte_off;
+        uint32_t wo = p.hap_word_off;
+        for (int q = 0; q < rv.n_haps; ++q) {
+            const phmm_hap &hp = rv.haps[q];
+            if (hp.len) std::memcpy(s.h_hapbytes.p + ho, hp.bases, hp.len);
+            s.h_hapoff.p[p.first_hap + q] = ho;
+            s.h_haps.p[p.first_hap + q] = DevHap{wo, hp.len};
+            s.h_haplist.p[p.hap_list_off + q] = p.first_hap + (uint32_t)q;
+            ho += (uint64_t)hp.len; wo += (uint32_t)hp.len + 1;
+        }
+    });
+    h->stats.host_ms_pack += ms_since(t0);
+    return PAIRHMM_OK;
+}
+
+// H2D of a packed chunk + haplotype word expansion. Asynchronous on the slot's stream.
+int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
+    cudaStream_t st = s.stream;
+    const uint32_t n_units = s.bin_start[kMaxRowsPerLane + 1];
+    if (s.n_uniq) {
+        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * 5, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
+    }
+    if (s.n_haps) {
+        if (s.hap_bytes) CU(h, cudaMemcpyAsync(s.d_hapbytes.p, s.h_hapbytes.p, s.hap_bytes, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_hapoff.p, s.h_hapoff.p, sizeof(uint64_t) * s.n_haps, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_haps.p, s.h_haps.p, sizeof(DevHap) * s.n_haps, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_haplist.p, s.h_haplist.p, sizeof(uint32_t) * s.n_haplist, cudaMemcpyHostToDevice, st));
+    }
+    if (n_units) CU(h, cudaMemcpyAsync(s.d_units.p, s.h_units.p, sizeof(DevUnit) * n_units, cudaMemcpyHostToDevice, st));
+    CU(h, launch_prep_haps(s.d_hapbytes.p, s.d_hapoff.p, s.d_haps.p, s.n_haps, s.d_hapw.p, st));
+    h->stats.kernel_launches += 1;
+    h->stats.h2d_bytes += s.plane * 5 + sizeof(DevRead) * (uint64_t)s.n_uniq + s.hap_bytes +
+                          (sizeof(uint64_t) + sizeof(DevHap) + sizeof(uint32_t)) * (uint64_t)s.n_haps +
+                          sizeof(DevUnit) * (uint64_t)n_units;
+    return PAIRHMM_OK;
+}
+
+// FP32 pass per K-bin -> finalize -> FP64 rescue per K-bin. Asynchronous on the slot's stream.
+int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
+    cudaStream_t st = s.stream;
+    CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kCounterWords, st));
+    CU(h, cudaEventRecord(s.ev_begin, st));
+    KernelArgs a{};
+    a.rd = s.d_rd.p; a.plane = s.plane; a.reads = s.d_reads.p; a.hapw = s.d_hapw.p; a.haps = s.d_haps.p;
+    a.hap_list = s.d_haplist.p; a.fres = s.d_fres.p; a.out = s.d_out.p; a.flag = s.d_flag.p;
+    a.log10_init_d = h->log10_init_d;
+    const bool all_double = h->cfg.use_double != 0;
+    if (!all_double) {
+        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+            const uint32_t n = s.bin_start[k + 1] - s.bin_start[k];
+            if (!n) continue;
+            a.units = s.d_units.p + s.bin_start[k]; a.n_units = n; a.n_units_dev = nullptr;
+            a.queue = s.d_counters.p + kQueueF + k;
+            a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
+            // every bin appends to its own slice of d_rescue (at most one entry per unique pair)
+            a.rescue_units = s.d_rescue.p + s.rescue_base[k];
+            a.rescue_count = s.d_counters.p + kRescueCount + k;
+            const int grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_f[k]),
+                                                     ((uint64_t)n + 3) / 4);
+            CU(h, launch_forward_float(k, h->cfg.exact_fp32 != 0, a, grid, st));
+            h->stats.kernel_launches += 1;
+        }
+        FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f};
+        CU(h, launch_finalize(f, st));
+        if (s.n_upairs) h->stats.kernel_launches += 1;
+    }
+    CU(h, cudaEventRecord(s.ev_float_done, st));
+    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+        const uint32_t n = s.bin_start[k + 1] - s.bin_start[k];
+        if (!n) continue;
+        a.queue = s.d_counters.p + kQueueD + k;
+        a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
+        a.rescue_units = nullptr; a.rescue_count = nullptr;
+        int grid;
+        if (all_double) {
+            a.units = s.d_units.p + s.bin_start[k]; a.n_units = n; a.n_units_dev = nullptr;
+            grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_d[k]), ((uint64_t)n + 3) / 4);
+        } else {
+            a.units = s.d_rescue.p + s.rescue_base[k]; a.n_units = 0;
+            a.n_units_dev = s.d_counters.p + kRescueCount + k;
+            // the rescue count is only known on the device: launch a full persistent grid, bounded by
+            // the number of pairs of this bin
+            const uint64_t pairs_k = (uint64_t)s.rescue_base[k + 1] - s.rescue_base[k];
+            grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_d[k]), (pairs_k + 3) / 4);
+            if (grid < 1) continue;
+        }
+        CU(h, launch_forward_double(k, a, grid, st));
+        h->stats.kernel_launches += 1;
+    }
+    CU(h, cudaEventRecord(s.ev_end, st));
+    return PAIRHMM_OK;
+}
+
+}  // namespace phmm
+
+namespace phmm {
+
+// D2H of results; asynchronous.
+int download_chunk(pairhmm_cuda_handle *h, Slot &s) {
+    if (s.n_upairs) {
+        CU(h, cudaMemcpyAsync(s.h_out.p, s.d_out.p, sizeof(double) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
+        CU(h, cudaMemcpyAsync(s.h_flag.p, s.d_flag.p, s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
+        h->stats.d2h_bytes += (sizeof(double) + 1) * (uint64_t)s.n_upairs;
+    }
+    return PAIRHMM_OK;
+}
+
+// Waits for the slot's stream, then maps unique (read, hap) results back to every input read
+// (VectorLoglessPairHMM.cpp:123-125: read-major, duplicates share their unique read's row).
+int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
+    CU(h, cudaStreamSynchronize(s.stream));
+    float ms_f = 0.f, ms_all = 0.f;
+    cudaEventElapsedTime(&ms_f, s.ev_begin, s.ev_float_done);
+    cudaEventElapsedTime(&ms_all, s.ev_begin, s.ev_end);
+    h->stats.gpu_ms_float += ms_f; h->stats.gpu_ms_double += ms_all - ms_f; h->stats.gpu_ms_total += ms_all;
+    auto t0 = clk::now();
+    std::atomic<uint64_t> rescued{0}, uniq_pairs{0};
+    parallel_for(s.regions.size(), threads, 16, [&](size_t i) {
+        const RegionView &rv = s.regions[i];
+        const RegionPlan &p = s.plans[i];
+        const size_t nh = (size_t)rv.n_haps;
+        uint64_t resc = 0;
+        for (int r = 0; r < rv.n_reads; ++r) {
+            const uint32_t u = p.uniq_of_read[r];
+            double *o = rv.out + (size_t)r * nh;
+            uint8_t *f = rv.resc ? rv.resc + (size_t)r * nh : nullptr;
+            if (u == kNoRead) {   // zero-length read: no alignment exists
+                for (size_t q = 0; q < nh; ++q) o[q] = -std::numeric_limits<double>::infinity();
+                if (f) std::memset(f, 1, nh);
+                continue;
+            }
+            const size_t src = (size_t)p.upair_off + (size_t)u * nh;
+            std::memcpy(o, s.h_out.p + src, nh * sizeof(double));
+            if (f) std::memcpy(f, s.h_flag.p + src, nh);
+        }
+        for (size_t q = 0; q < (size_t)p.n_uniq * nh; ++q) resc += s.h_flag.p[p.upair_off + q];
+        rescued += resc; uniq_pairs += (uint64_t)p.n_uniq * nh;
+    });
+    h->stats.host_ms_scatter += ms_since(t0);
+    h->stats.regions += s.regions.size(); h->stats.reads += s.reads_in; h->stats.unique_reads += s.n_uniq;
+    h->stats.pairs += s.pairs; h->stats.unique_pairs += uniq_pairs.load(); h->stats.cells += s.cells;
+    h->stats.rescued_pairs += rescued.load();
+    s.busy = false;
+    return PAIRHMM_OK;
+}
+
+int pack_threads(const pairhmm_cuda_handle *h) {
+    if (h->cfg.pack_threads > 0) return h->cfg.pack_threads;
+    unsigned hc = std::thread::hardware_concurrency();
+    return (int)std::max(1u, std::min(hc ? hc : 1u, 16u));
+}
+
+int submit_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n, int threads) {
+    int st = pack_chunk(h, s, regs, n, threads);
+    if (st != PAIRHMM_OK) return st;
+    s.busy = true;
+    if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
+    if ((st = run_kernels(h, s)) != PAIRHMM_OK) return st;
+    return download_chunk(h, s);
+}
+
+}  // namespace phmm
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+int pairhmm_cuda_abi_version(void) { return PAIRHMM_CUDA_ABI_VERSION; }
+
+int pairhmm_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int ok = 0;
+    for (int d = 0; d < n; ++d) {
+        cudaDeviceProp p;
+        if (cudaGetDeviceProperties(&p, d) == cudaSuccess && p.major == 10) ++ok;
+    }
+    return ok;
+}
+
+void pairhmm_cuda_default_config(pairhmm_cuda_config *cfg) {
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->device = -1; cfg->use_double = 0; cfg->exact_fp32 = 0; cfg->dedup_reads = 1; cfg->pack_threads = 0;
+    cfg->chunk_cells = 0;
+}
+
+int pairhmm_cuda_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d) {
+    const HostTables &t = host_tables();
+    if (ph2pr_f) std::memcpy(ph2pr_f, t.ph2pr_f, sizeof t.ph2pr_f);
+    if (mm_f) std::memcpy(mm_f, t.mm_f, sizeof t.mm_f);
+    if (ph2pr_d) std::memcpy(ph2pr_d, t.ph2pr_d, sizeof t.ph2pr_d);
+    if (mm_d) std::memcpy(mm_d, t.mm_d, sizeof t.mm_d);
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **out) {
+    if (!out) return PAIRHMM_ERR_ARG;
+    *out = nullptr;
+    pairhmm_cuda_config c;
+    if (cfg) c = *cfg; else pairhmm_cuda_default_config(&c);
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return PAIRHMM_ERR_NO_DEVICE; }
+    int dev = c.device;
+    if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) return PAIRHMM_ERR_NO_DEVICE; }
+    if (dev >= n) return PAIRHMM_ERR_ARG;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return PAIRHMM_ERR_NO_DEVICE;
+    if (prop.major != 10) return PAIRHMM_ERR_NO_DEVICE;   // kernels are built for sm_100a only
+    auto *h = new (std::nothrow) pairhmm_cuda_handle();
+    if (!h) return PAIRHMM_ERR_OOM;
+    h->cfg = c; h->device = dev; h->sm_count = prop.multiProcessorCount;
+    std::memset(&h->stats, 0, sizeof h->stats);
+    auto bail = [&](int st) { pairhmm_cuda_destroy(h); return st; };
+    if (cudaSetDevice(dev) != cudaSuccess) return bail(PAIRHMM_ERR_CUDA);
+    const HostTables &t = host_tables();
+    h->log10_init_f = log10f(ldexpf(1.f, 120));     // Context.h:184
+    h->log10_init_d = log10(ldexp(1.0, 1020));      // Context.h:143
+#define UP(dst, src) \
+    if (cudaMalloc((void **)&h->dst, sizeof t.src) != cudaSuccess || \
+        cudaMemcpy(h->dst, t.src, sizeof t.src, cudaMemcpyHostToDevice) != cudaSuccess) return bail(PAIRHMM_ERR_CUDA)
+    UP(d_ph2pr_f, ph2pr_f); UP(d_mm_f, mm_f); UP(d_ph2pr_d, ph2pr_d); UP(d_mm_d, mm_d);
+#undef UP
+    for (auto &s : h->slots) {
+        if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreate(&s.ev_begin) != cudaSuccess || cudaEventCreate(&s.ev_float_done) != cudaSuccess ||
+            cudaEventCreate(&s.ev_end) != cudaSuccess || s.d_counters.reserve(64) != cudaSuccess)
+            return bail(PAIRHMM_ERR_CUDA);
+    }
+    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+        h->blocks_per_sm_f[k] = forward_blocks_per_sm(k, false, c.exact_fp32 != 0);
+        h->blocks_per_sm_d[k] = forward_blocks_per_sm(k, true, false);
+        if (h->blocks_per_sm_f[k] < 1 || h->blocks_per_sm_d[k] < 1) return bail(PAIRHMM_ERR_CUDA);
+    }
+    *out = h;
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_destroy(pairhmm_cuda_handle *h) {
+    if (!h) return PAIRHMM_OK;
+    cudaSetDevice(h->device);
+    for (auto &s : h->slots) { if (s.stream) cudaStreamSynchronize(s.stream); s.release(); }
+    if (h->d_ph2pr_f) cudaFree(h->d_ph2pr_f);
+    if (h->d_mm_f) cudaFree(h->d_mm_f);
+    if (h->d_ph2pr_d) cudaFree(h->d_ph2pr_d);
+    if (h->d_mm_d) cudaFree(h->d_mm_d);
+    delete h;
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_initialize(pairhmm_cuda_handle *h, int read_max_len, int hap_max_len) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (read_max_len <= 0 || hap_max_len <= 0)   // PairHMM.cpp:16 asserts haplotypeMaxLength > 0
+        return fail(h, PAIRHMM_ERR_ARG, "initialize: maximum lengths must be positive");
+    h->read_max_len = read_max_len; h->hap_max_len = hap_max_len;
+    return PAIRHMM_OK;
+}
+
+const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h) { return h ? h->last_error.c_str() : "null handle"; }
+
+int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out) {
+    if (!h || !out) return PAIRHMM_ERR_ARG;
+    *out = h->stats;
+    return PAIRHMM_OK;
+}
+int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    std::memset(&h->stats, 0, sizeof h->stats);
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
+                        int n_haps, double *log10_out, uint8_t *rescued_out, pairhmm_cuda_ticket *ticket) {
+    if (!h || !ticket) return PAIRHMM_ERR_ARG;
+    auto t0 = clk::now();
+    CU(h, cudaSetDevice(h->device));
+    int si = !h->slots[0].busy ? 0 : (!h->slots[1].busy ? 1 : -1);
+    if (si < 0) {   // both in flight: retire the older one first
+        si = h->slot_ticket[0] < h->slot_ticket[1] ? 0 : 1;
+        int st = finish_chunk(h, h->slots[si], 1);
+        if (st != PAIRHMM_OK) return st;
+        h->slot_ticket[si] = 0;
+    }
+    RegionView rv{reads, n_reads, haps, n_haps, log10_out, rescued_out};
+    int st = submit_chunk(h, h->slots[si], &rv, 1, 1);
+    if (st != PAIRHMM_OK) { h->slots[si].busy = false; return st; }
+    h->slot_ticket[si] = *ticket = h->next_ticket++;
+    h->stats.calls += 1;
+    h->stats.host_ms_total += ms_since(t0);
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_wait(pairhmm_cuda_handle *h, pairhmm_cuda_ticket ticket) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    auto t0 = clk::now();
+    if (ticket <= 0 || ticket >= h->next_ticket) return fail(h, PAIRHMM_ERR_STATE, "wait: unknown ticket");
+    for (int si = 0; si < 2; ++si)
+        if (h->slot_ticket[si] == ticket) {
+            CU(h, cudaSetDevice(h->device));
+            int st = finish_chunk(h, h->slots[si], 1);
+            h->slot_ticket[si] = 0;
+            h->stats.host_ms_total += ms_since(t0);
+            return st;
+        }
+    return PAIRHMM_OK;   // already retired by a later submit
+}
+
+int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
+                         int n_haps, double *log10_out, uint8_t *rescued_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (n_reads == 0) return PAIRHMM_OK;   // VectorLoglessPairHMM.cpp:46-47
+    pairhmm_cuda_ticket t;
+    int st = pairhmm_cuda_submit(h, reads, n_reads, haps, n_haps, log10_out, rescued_out, &t);
+    if (st != PAIRHMM_OK) return st;
+    return pairhmm_cuda_wait(h, t);
+}
+
+int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions) {
+    if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
+    auto t0 = clk::now();
+    CU(h, cudaSetDevice(h->device));
+    for (int si = 0; si < 2; ++si)
+        if (h->slots[si].busy) { int st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    const int threads = pack_threads(h);
+    const int64_t chunk_cells = h->cfg.chunk_cells > 0 ? h->cfg.chunk_cells : (int64_t)100000000000ll;
+    std::vector<RegionView> views;
+    int64_t i = 0;
+    int si = 0;
+    int status = PAIRHMM_OK;
+    while (i < n_regions && status == PAIRHMM_OK) {
+        views.clear();
+        int64_t cells = 0;
+        uint64_t pairs = 0, rbytes = 0;
+        while (i < n_regions) {
+            const phmm_region &r = regions[i];
+            uint64_t rl = 0, hl = 0;
+            for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.reads[q].len);
+            for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
+            const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
+            if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_cells || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
+            views.push_back(RegionView{r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out});
+            cells += (int64_t)(rl * hl); pairs += p; rbytes += rl;
+            ++i;
+        }
+        Slot &s = h->slots[si];
+        if (s.busy) status = finish_chunk(h, s, threads);
+        if (status == PAIRHMM_OK) status = submit_chunk(h, s, views.data(), views.size(), threads);
+        si ^= 1;
+    }
+    for (int k = 0; k < 2; ++k) {
+        Slot &s = h->slots[(si + k) & 1];
+        if (s.busy) { int st = finish_chunk(h, s, threads); if (status == PAIRHMM_OK) status = st; }
+    }
+    h->stats.calls += 1;
+    h->stats.host_ms_total += ms_since(t0);
+    return status;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// flat / pair-list / resident entry points
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct FlatViews {
+    std::vector<phmm_read> reads;
+    std::vector<phmm_hap> haps;
+    std::vector<phmm_region> regions;
+};
+
+int build_flat_views(pairhmm_cuda_handle *h, FlatViews &v, const uint8_t *read_bases, const uint8_t *base_q,
+                     const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp, const int64_t *read_off,
+                     const int32_t *read_len, int64_t n_reads, const uint8_t *hap_bases, const int64_t *hap_off,
+                     const int32_t *hap_len, int64_t n_haps, const int64_t *reg_read_start,
+                     const int64_t *reg_hap_start, int64_t n_regions, double *log10_out, uint8_t *rescued_out) {
+    if (n_reads < 0 || n_haps < 0 || n_regions < 0) return fail(h, PAIRHMM_ERR_ARG, "negative count");
+    if (n_reads && (!read_bases || !base_q || !ins_q || !del_q || !gcp || !read_off || !read_len))
+        return fail(h, PAIRHMM_ERR_ARG, "null read array");
+    if (n_haps && (!hap_bases || !hap_off || !hap_len)) return fail(h, PAIRHMM_ERR_ARG, "null haplotype array");
+    if (n_regions && (!reg_read_start || !reg_hap_start)) return fail(h, PAIRHMM_ERR_ARG, "null region array");
+    v.reads.resize(n_reads); v.haps.resize(n_haps); v.regions.resize(n_regions);
+    for (int64_t i = 0; i < n_reads; ++i) {
+        const int64_t o = read_off[i];
+        v.reads[i] = phmm_read{read_bases + o, base_q + o, ins_q + o, del_q + o, gcp + o, read_len[i]};
+    }
+    for (int64_t i = 0; i < n_haps; ++i) v.haps[i] = phmm_hap{hap_bases + hap_off[i], hap_len[i]};
+    int64_t out_off = 0;
+    for (int64_t r = 0; r < n_regions; ++r) {
+        const int64_t r0 = reg_read_start[r], r1 = reg_read_start[r + 1], h0 = reg_hap_start[r], h1 = reg_hap_start[r + 1];
+        if (r0 < 0 || r1 < r0 || r1 > n_reads || h0 < 0 || h1 < h0 || h1 > n_haps || r1 - r0 > 0x7fffffff || h1 - h0 > 0x7fffffff)
+            return fail(h, PAIRHMM_ERR_ARG, "region bounds out of range");
+        v.regions[r] = phmm_region{v.reads.data() + r0, (int32_t)(r1 - r0), v.haps.data() + h0, (int32_t)(h1 - h0),
+                                   log10_out ? log10_out + out_off : nullptr, rescued_out ? rescued_out + out_off : nullptr};
+        out_off += (r1 - r0) * (h1 - h0);
+    }
+    return PAIRHMM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pairhmm_cuda_compute_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                              const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                              const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                              const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                              int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                              int64_t n_regions, double *log10_out, uint8_t *rescued_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    auto t0 = clk::now();
+    FlatViews v;
+    int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
+                              hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, log10_out, rescued_out);
+    if (st != PAIRHMM_OK) return st;
+    for (auto &r : v.regions)
+        if ((int64_t)r.n_reads * r.n_haps > 0 && !r.log10_out) return fail(h, PAIRHMM_ERR_ARG, "null output");
+    h->stats.host_ms_total += ms_since(t0);   // view building counts as host time of the call
+    return pairhmm_cuda_compute_batch(h, v.regions.data(), n_regions);
+}
+
+int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
+                               int n_haps, const uint32_t *read_idx, const uint32_t *hap_idx, size_t n_pairs,
+                               double *log10_out, uint8_t *rescued_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (n_pairs == 0) return PAIRHMM_OK;
+    if (!reads || !haps || !read_idx || !hap_idx || !log10_out || n_reads <= 0 || n_haps <= 0)
+        return fail(h, PAIRHMM_ERR_ARG, "compute_pairs: null pointer or empty tables");
+    for (size_t p = 0; p < n_pairs; ++p)
+        if (read_idx[p] >= (uint32_t)n_reads || hap_idx[p] >= (uint32_t)n_haps)
+            return fail(h, PAIRHMM_ERR_ARG, "compute_pairs: index out of range");
+    // full cross product in read-major order = one region
+    bool cross = n_pairs == (size_t)n_reads * (size_t)n_haps;
+    for (size_t p = 0; cross && p < n_pairs; ++p)
+        cross = read_idx[p] == p / (size_t)n_haps && hap_idx[p] == p % (size_t)n_haps;
+    if (cross) return pairhmm_cuda_compute(h, reads, n_reads, haps, n_haps, log10_out, rescued_out);
+    // general list: one single-read region per distinct read, carrying that read's haplotypes
+    std::vector<size_t> start((size_t)n_reads + 1, 0), pos(n_pairs);
+    for (size_t p = 0; p < n_pairs; ++p) start[read_idx[p] + 1]++;
+    for (int r = 0; r < n_reads; ++r) start[r + 1] += start[r];
+    std::vector<size_t> fill(start.begin(), start.end() - 1);
+    std::vector<phmm_hap> hl(n_pairs);
+    for (size_t p = 0; p < n_pairs; ++p) { pos[p] = fill[read_idx[p]]++; hl[pos[p]] = haps[hap_idx[p]]; }
+    std::vector<double> tmp(n_pairs);
+    std::vector<uint8_t> tmpf(n_pairs);
+    std::vector<phmm_region> regs;
+    for (int r = 0; r < n_reads; ++r)
+        if (start[r + 1] > start[r])
+            regs.push_back(phmm_region{reads + r, 1, hl.data() + start[r], (int32_t)(start[r + 1] - start[r]),
+                                       tmp.data() + start[r], tmpf.data() + start[r]});
+    int st = pairhmm_cuda_compute_batch(h, regs.data(), (int64_t)regs.size());
+    if (st != PAIRHMM_OK) return st;
+    for (size_t p = 0; p < n_pairs; ++p) { log10_out[p] = tmp[pos[p]]; if (rescued_out) rescued_out[p] = tmpf[pos[p]]; }
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                               const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                               const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                               const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                               int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                               int64_t n_regions) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    CU(h, cudaSetDevice(h->device));
+    for (int si = 0; si < 2; ++si)
+        if (h->slots[si].busy) { int st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    h->resident_loaded = false;
+    FlatViews v;
+    int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
+                              hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, nullptr, nullptr);
+    if (st != PAIRHMM_OK) return st;
+    std::vector<RegionView> views(n_regions);
+    for (int64_t i = 0; i < n_regions; ++i)
+        views[i] = RegionView{v.regions[i].reads, v.regions[i].n_reads, v.regions[i].haps, v.regions[i].n_haps, nullptr, nullptr};
+    Slot &s = h->slots[0];
+    if ((st = pack_chunk(h, s, views.data(), views.size(), pack_threads(h))) != PAIRHMM_OK) return st;
+    if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
+    CU(h, cudaStreamSynchronize(s.stream));
+    // the views point into `v`, which dies here: keep only the shapes (plans hold everything scatter needs)
+    for (auto &rv : s.regions) { rv.reads = nullptr; rv.haps = nullptr; }
+    h->resident_loaded = true;
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_run: nothing loaded");
+    CU(h, cudaSetDevice(h->device));
+    Slot &s = h->slots[0];
+    int st = run_kernels(h, s);
+    if (st != PAIRHMM_OK) return st;
+    CU(h, cudaStreamSynchronize(s.stream));
+    float a = 0.f, b = 0.f;
+    CU(h, cudaEventElapsedTime(&a, s.ev_begin, s.ev_end));
+    CU(h, cudaEventElapsedTime(&b, s.ev_begin, s.ev_float_done));
+    if (kernel_ms) *kernel_ms = a;
+    if (float_kernel_ms) *float_kernel_ms = b;
+    h->stats.gpu_ms_total += a; h->stats.gpu_ms_float += b; h->stats.gpu_ms_double += a - b;
+    h->stats.cells += s.cells; h->stats.pairs += s.pairs;
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out) {
+    if (!h || !log10_out) return PAIRHMM_ERR_ARG;
+    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: nothing loaded");
+    CU(h, cudaSetDevice(h->device));
+    Slot &s = h->slots[0];
+    size_t off = 0;
+    for (auto &rv : s.regions) {
+        rv.out = log10_out + off; rv.resc = rescued_out ? rescued_out + off : nullptr;
+        off += (size_t)rv.n_reads * (size_t)rv.n_haps;
+    }
+    int st = download_chunk(h, s);
+    if (st != PAIRHMM_OK) return st;
+    const uint64_t c = h->stats.cells, p = h->stats.pairs;   // finish_chunk would count the batch again
+    const double g0 = h->stats.gpu_ms_total, g1 = h->stats.gpu_ms_float, g2 = h->stats.gpu_ms_double;
+    st = finish_chunk(h, s, pack_threads(h));
+    h->stats.cells = c; h->stats.pairs = p;
+    h->stats.gpu_ms_total = g0; h->stats.gpu_ms_float = g1; h->stats.gpu_ms_double = g2;
+    return st;
+}
+
+}  // extern "C"

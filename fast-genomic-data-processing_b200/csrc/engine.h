@@ -1,0 +1,105 @@
+// Host side of libpairhmm_cuda: turns regions (reads x haplotypes) into warp work units, stages them
+// through pinned memory, launches the kernels of kernels.cu and scatters results back.
+// Replaces the compute half of VectorLoglessPairHMM (M2/utils/pairhmm/VectorLoglessPairHMM.cpp:43-148)
+// and all of gkl_pairhmm's dispatch (M2/intel/pairhmm/IntelPairHmm.cc:259-351).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/pairhmm_cuda.h"
+#include "kernels.cuh"
+
+namespace phmm {
+
+// Growable pinned-host / device arrays (never shrink; 1.25x growth).
+template <class T> struct PinnedBuf {
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n);
+    void release();
+};
+template <class T> struct DevBuf {
+    T *p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n);
+    void release();
+};
+
+// One region as the packer sees it (pointers borrowed from the caller).
+struct RegionView {
+    const phmm_read *reads; int32_t n_reads;
+    const phmm_hap *haps; int32_t n_haps;
+    double *out; uint8_t *resc;
+};
+
+// Sizes/offsets of one region inside a packed chunk (filled by pass A + prefix sums).
+struct RegionPlan {
+    uint32_t n_uniq = 0;            // unique reads with len > 0
+    uint32_t first_uniq = 0;        // global unique-read id of this region's first unique read
+    uint64_t read_bytes = 0, read_byte_off = 0;
+    uint32_t first_hap = 0;         // global hap id
+    uint64_t hap_bytes = 0, hap_byte_off = 0;
+    uint32_t hap_words = 0, hap_word_off = 0;
+    uint32_t hap_list_off = 0;
+    uint32_t group = 0, n_groups = 0;   // haplotypes per work unit / units per read
+    uint32_t upair_off = 0;         // first unique-pair index
+    uint32_t unit_count[kMaxRowsPerLane + 1] = {0};
+    uint32_t unit_off[kMaxRowsPerLane + 1] = {0};
+    std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
+    std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
+};
+
+// Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
+struct Slot {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_float_done = nullptr, ev_end = nullptr;
+    // host staging
+    PinnedBuf<uint8_t> h_rd, h_hapbytes, h_flag;
+    PinnedBuf<DevRead> h_reads;
+    PinnedBuf<DevHap> h_haps;
+    PinnedBuf<uint64_t> h_hapoff;
+    PinnedBuf<uint32_t> h_haplist;
+    PinnedBuf<DevUnit> h_units;
+    PinnedBuf<double> h_out;
+    // device
+    DevBuf<uint8_t> d_rd, d_hapbytes, d_flag;
+    DevBuf<DevRead> d_reads;
+    DevBuf<DevHap> d_haps;
+    DevBuf<uint64_t> d_hapoff;
+    DevBuf<uint32_t> d_haplist, d_hapw, d_counters;
+    DevBuf<DevUnit> d_units, d_rescue;
+    DevBuf<float> d_fres;
+    DevBuf<double> d_out;
+    // shape of the packed chunk
+    std::vector<RegionView> regions;
+    std::vector<RegionPlan> plans;
+    uint64_t plane = 0;               // bytes per read plane
+    uint32_t n_uniq = 0, n_haps = 0, n_hap_words = 0, n_haplist = 0, n_upairs = 0;
+    uint64_t hap_bytes = 0;
+    uint32_t bin_start[kMaxRowsPerLane + 2] = {0};   // units of K-bin k are [bin_start[k], bin_start[k+1])
+    uint32_t rescue_base[kMaxRowsPerLane + 2] = {0}; // K-bin k appends its rescue units at d_rescue + rescue_base[k]
+    uint64_t cells = 0, pairs = 0, reads_in = 0;
+    bool busy = false;
+    void release();
+};
+
+}  // namespace phmm
+
+struct pairhmm_cuda_handle {
+    pairhmm_cuda_config cfg;
+    int device = 0;
+    int sm_count = 0;
+    std::string last_error;
+    pairhmm_cuda_stats stats;
+    // device tables (per handle; 70 KB)
+    float *d_ph2pr_f = nullptr, *d_mm_f = nullptr;
+    double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
+    float log10_init_f = 0.f;
+    double log10_init_d = 0.0;
+    int blocks_per_sm_f[phmm::kMaxRowsPerLane + 1] = {0};
+    int blocks_per_sm_d[phmm::kMaxRowsPerLane + 1] = {0};
+    int read_max_len = 0, hap_max_len = 0;
+    phmm::Slot slots[2];
+    int64_t next_ticket = 1;
+    int64_t slot_ticket[2] = {0, 0};
+    bool resident_loaded = false;
+};

@@ -1,0 +1,75 @@
+// Device-side data layout and launch entry points of the PairHMM engine (sm_100a).
+//
+// Layout in HBM (all built by the host packer / the prep kernel):
+//   read planes  uint8  rd[5][plane]    bases | base_q | ins_q | del_q | gcp, raw bytes as the caller
+//                                       gave them (masking &127 and base->code happen on device)
+//   DevRead      {off,len}              byte offset of a read inside every plane
+//   hap words    uint32 hapw[]          words [0,64) = lead/tail padding (31 PAD, 1 SEP, 32 PAD); then
+//                                       per haplotype H code words + 1 SEP word. A code word is the
+//                                       one-hot base code (A1 C2 T4 G8 N15) replicated in all 4 bytes.
+//   DevHap       {off,len}              word offset / H
+//   hap_list     uint32[]               haplotype ids, one run per work unit
+//   DevUnit      {read,hap_list,nh,out} one warp-task: read x nh haplotypes streamed back to back
+//   results      float fres[] (FP32 pass), double out[] (final log10), uint8 flag[] (rescued)
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace phmm {
+
+struct DevRead { uint32_t off; int32_t len; };
+struct DevHap  { uint32_t off; int32_t len; };
+struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t nh; uint32_t out; };
+
+constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain)
+constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next haplotype
+constexpr int kLeadWords = 64;               // hapw[0..30]=PAD, [31]=SEP, [32..63]=PAD
+constexpr int kMaxRowsPerLane = 8;           // K; one warp covers reads up to 32*K-1 rows
+constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition
+
+struct KernelArgs {
+    const uint8_t *rd;          // read planes
+    uint64_t plane;             // plane stride in bytes
+    const DevRead *reads;
+    const uint32_t *hapw;
+    const DevHap *haps;
+    const uint32_t *hap_list;
+    const DevUnit *units;
+    const uint32_t *n_units_dev;  // if non-null the unit count is read from here (rescue lists)
+    uint32_t n_units;
+    uint32_t *queue;              // work counter for this launch (zeroed by the host)
+    // tables (precision of the launch)
+    const void *ph2pr;            // T[128]
+    const void *mm;               // T[8256]
+    // FP32 pass outputs
+    float *fres;                  // scaled forward sum per unique pair
+    DevUnit *rescue_units;        // pairs with fres < 1e-28f, appended
+    uint32_t *rescue_count;
+    // FP64 pass outputs
+    double *out;                  // log10 likelihood
+    uint8_t *flag;                // 1 = went through the FP64 kernel
+    double log10_init_d;          // log10(2^1020), host libm (Context.h:143)
+};
+
+struct FinalizeArgs {
+    const float *fres;
+    double *out;
+    uint8_t *flag;
+    uint32_t n;
+    float log10_init_f;           // log10f(2^120), host libm (Context.h:184)
+};
+
+// rows-per-lane bucket for a read length: smallest K with R <= 32*K - 1 (one row-0 emulator row is
+// always kept above the read); 0 if the read needs the striped path.
+inline int rows_per_lane(int R) { int k = R / 32 + 1; return k <= kMaxRowsPerLane ? k : 0; }
+
+// Launchers (kernels.cu). All asynchronous on `st`; return the cudaError of the launch.
+cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,
+                             uint32_t n_haps, uint32_t *hapw, cudaStream_t st);
+cudaError_t launch_forward_float(int K, bool exact, const KernelArgs &a, int grid_blocks, cudaStream_t st);
+cudaError_t launch_forward_double(int K, const KernelArgs &a, int grid_blocks, cudaStream_t st);
+cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
+// resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
+int forward_blocks_per_sm(int K, bool is_double, bool exact);
+
+}  // namespace phmm

@@ -1,0 +1,317 @@
+"""Seeded synthetic inputs for the five BASELINE.json configs.
+
+Everything is flat SoA numpy so that the CPU checkers and the CUDA engine read identical bytes:
+
+  RegionBatch
+    read_bases/base_q/ins_q/del_q/gcp : uint8[sum R]   five per-read byte arrays, concatenated
+    read_off int64[n_reads], read_len int32[n_reads]
+    hap_bases uint8[sum H], hap_off int64[n_haps], hap_len int32[n_haps]
+    reg_read_start int64[n_regions+1], reg_hap_start int64[n_regions+1]
+  Pairs are implied: every read of a region x every haplotype of that region, results read-major
+  per region (out[r * nHaps + h], VectorLoglessPairHMM.cpp:123-125), regions concatenated.
+
+Quality values are what the kernel sees, i.e. *after* PairHMMLikelihoodCalculationEngine's capping
+(base q <18 -> 6, ins/del floor 6, gcp == 10; PairHMMLikelihoodCalculationEngine.cpp:256-292).
+"""
+from dataclasses import dataclass
+import numpy as np
+
+ACGT = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+
+@dataclass
+class RegionBatch:
+    read_bases: np.ndarray
+    base_q: np.ndarray
+    ins_q: np.ndarray
+    del_q: np.ndarray
+    gcp: np.ndarray
+    read_off: np.ndarray
+    read_len: np.ndarray
+    hap_bases: np.ndarray
+    hap_off: np.ndarray
+    hap_len: np.ndarray
+    reg_read_start: np.ndarray
+    reg_hap_start: np.ndarray
+    name: str = ""
+
+    @property
+    def n_regions(self):
+        return int(self.reg_read_start.shape[0] - 1)
+
+    @property
+    def n_reads(self):
+        return int(self.read_len.shape[0])
+
+    @property
+    def n_haps(self):
+        return int(self.hap_len.shape[0])
+
+    def region_out_offsets(self):
+        nr = np.diff(self.reg_read_start)
+        nh = np.diff(self.reg_hap_start)
+        off = np.zeros(self.n_regions + 1, np.int64)
+        np.cumsum(nr * nh, out=off[1:])
+        return off
+
+    @property
+    def n_pairs(self):
+        return int(self.region_out_offsets()[-1])
+
+    def cells(self):
+        """sum over pairs of R*H (the GCUPS numerator)."""
+        tot = 0
+        for g in range(self.n_regions):
+            r0, r1 = self.reg_read_start[g], self.reg_read_start[g + 1]
+            h0, h1 = self.reg_hap_start[g], self.reg_hap_start[g + 1]
+            tot += int(self.read_len[r0:r1].astype(np.int64).sum()) * int(self.hap_len[h0:h1].astype(np.int64).sum())
+        return tot
+
+    def pair_lists(self):
+        """explicit (pair_read, pair_hap) uint32 arrays in output order."""
+        pr, ph = [], []
+        for g in range(self.n_regions):
+            r0, r1 = int(self.reg_read_start[g]), int(self.reg_read_start[g + 1])
+            h0, h1 = int(self.reg_hap_start[g]), int(self.reg_hap_start[g + 1])
+            pr.append(np.repeat(np.arange(r0, r1, dtype=np.uint32), h1 - h0))
+            ph.append(np.tile(np.arange(h0, h1, dtype=np.uint32), r1 - r0))
+        if not pr:
+            return np.zeros(0, np.uint32), np.zeros(0, np.uint32)
+        return np.concatenate(pr), np.concatenate(ph)
+
+    def as_flat(self):
+        """view with explicit pair lists, the shape the CPU checkers take (oracle_py._Lib.compute)."""
+        pr, ph = self.pair_lists()
+        return FlatPairs(self.read_bases, self.base_q, self.ins_q, self.del_q, self.gcp, self.read_off,
+                         self.read_len, self.hap_bases, self.hap_off, self.hap_len, pr, ph)
+
+    def subset(self, regions):
+        """a new batch holding only the given region indices (used for bounded CPU samples)."""
+        rb, bq, iq, dq, gc, rl, hb, hl = [], [], [], [], [], [], [], []
+        rrs, rhs = [0], [0]
+        for g in regions:
+            r0, r1 = int(self.reg_read_start[g]), int(self.reg_read_start[g + 1])
+            h0, h1 = int(self.reg_hap_start[g]), int(self.reg_hap_start[g + 1])
+            a, b = int(self.read_off[r0]), int(self.read_off[r1 - 1] + self.read_len[r1 - 1])
+            for src, dst in ((self.read_bases, rb), (self.base_q, bq), (self.ins_q, iq), (self.del_q, dq), (self.gcp, gc)):
+                dst.append(src[a:b])
+            rl.append(self.read_len[r0:r1])
+            a, b = int(self.hap_off[h0]), int(self.hap_off[h1 - 1] + self.hap_len[h1 - 1])
+            hb.append(self.hap_bases[a:b])
+            hl.append(self.hap_len[h0:h1])
+            rrs.append(rrs[-1] + (r1 - r0))
+            rhs.append(rhs[-1] + (h1 - h0))
+        rl = np.concatenate(rl).astype(np.int32)
+        hl = np.concatenate(hl).astype(np.int32)
+        return RegionBatch(np.concatenate(rb), np.concatenate(bq), np.concatenate(iq), np.concatenate(dq),
+                           np.concatenate(gc), _offsets(rl), rl, np.concatenate(hb), _offsets(hl), hl,
+                           np.asarray(rrs, np.int64), np.asarray(rhs, np.int64), self.name + "/subset")
+
+
+@dataclass
+class FlatPairs:
+    read_bases: np.ndarray
+    base_q: np.ndarray
+    ins_q: np.ndarray
+    del_q: np.ndarray
+    gcp: np.ndarray
+    read_off: np.ndarray
+    read_len: np.ndarray
+    hap_bases: np.ndarray
+    hap_off: np.ndarray
+    hap_len: np.ndarray
+    pair_read: np.ndarray
+    pair_hap: np.ndarray
+
+
+def _offsets(lens):
+    off = np.zeros(len(lens), np.int64)
+    if len(lens) > 1:
+        np.cumsum(lens[:-1], out=off[1:])
+    return off
+
+
+# --------------------------------------------------------------------------------------------
+# generators
+# --------------------------------------------------------------------------------------------
+def _rand_bases(rng, n, n_rate=0.001):
+    b = ACGT[rng.integers(0, 4, size=n)]
+    if n_rate > 0 and n > 0:
+        b = b.copy()
+        b[rng.random(n) < n_rate] = ord("N")
+    return b
+
+
+def _variant_hap(rng, hap0, target_len):
+    """hap0 with 1-3 SNVs and one 1-5 bp indel, padded/trimmed to target_len."""
+    h = hap0.copy()
+    for _ in range(int(rng.integers(1, 4))):
+        p = int(rng.integers(0, len(h)))
+        h[p] = ACGT[(int(np.searchsorted(ACGT, h[p]) if h[p] in ACGT else 0) + int(rng.integers(1, 4))) % 4]
+    p = int(rng.integers(1, max(2, len(h) - 6)))
+    n = int(rng.integers(1, 6))
+    if rng.random() < 0.5:
+        h = np.concatenate([h[:p], _rand_bases(rng, n, 0.0), h[p:]])
+    else:
+        h = np.concatenate([h[:p], h[p + n:]])
+    if len(h) < target_len:
+        h = np.concatenate([h, _rand_bases(rng, target_len - len(h), 0.0)])
+    return np.ascontiguousarray(h[:target_len])
+
+
+def _quals(rng, shape, profile):
+    n = int(np.prod(shape))
+    if profile == "clean":
+        bq = np.clip(np.rint(rng.normal(32.0, 6.0, size=n)), 2, 41).astype(np.uint8)
+        bq[bq < 18] = 6
+        iq = np.full(n, 45, np.uint8)
+        dq = np.full(n, 45, np.uint8)
+        m = rng.random(n) < 0.10
+        iq[m] = rng.integers(20, 41, size=int(m.sum()))
+        m = rng.random(n) < 0.10
+        dq[m] = rng.integers(20, 41, size=int(m.sum()))
+    elif profile == "lowq":
+        bq = rng.integers(18, 26, size=n).astype(np.uint8)
+        bq[rng.random(n) < 0.70] = 6
+        iq = rng.integers(10, 31, size=n).astype(np.uint8)
+        dq = rng.integers(10, 31, size=n).astype(np.uint8)
+    else:
+        raise ValueError(profile)
+    gc = np.full(n, 10, np.uint8)
+    return bq.reshape(shape), iq.reshape(shape), dq.reshape(shape), gc.reshape(shape)
+
+
+def _region(rng, n_reads, hap_lens, R, profile, sub_rate=None, foreign_frac=0.0):
+    """one region: haps (list of arrays) + [n_reads, R] read arrays. `foreign_frac` of the reads are
+    random sequence unrelated to any haplotype (mis-mapped reads): these are the pairs whose float
+    likelihood underflows 1e-28 and take the double-precision rescue."""
+    H0 = int(hap_lens[0])
+    hap0 = _rand_bases(rng, H0)
+    haps = [hap0] + [_variant_hap(rng, hap0, int(L)) for L in hap_lens[1:]]
+    nh = len(haps)
+    Hmax = max(len(h) for h in haps)
+    hmat = np.empty((nh, max(Hmax, R)), np.uint8)
+    hmat[:] = ACGT[rng.integers(0, 4, size=hmat.shape)]
+    for i, h in enumerate(haps):
+        hmat[i, :len(h)] = h
+    src = rng.integers(0, nh, size=n_reads)
+    lens = np.array([len(h) for h in haps])[src]
+    start = (rng.random(n_reads) * np.maximum(lens - R, 0).astype(np.float64)).astype(np.int64)
+    idx = start[:, None] + np.arange(R)[None, :]
+    bases = hmat[src[:, None], idx]
+    bq, iq, dq, gc = _quals(rng, (n_reads, R), profile)
+    # sequencing errors at 10^(-q/10) (clean) and/or an explicit per-read substitution rate
+    perr = np.power(10.0, -bq.astype(np.float64) / 10.0)
+    if sub_rate is not None:
+        perr = np.maximum(perr, rng.uniform(sub_rate[0], sub_rate[1], size=(n_reads, 1)))
+    err = rng.random((n_reads, R)) < perr
+    bases = np.where(err, ACGT[rng.integers(0, 4, size=(n_reads, R))], bases)
+    if foreign_frac > 0:
+        foreign = rng.random(n_reads) < foreign_frac
+        bases = np.where(foreign[:, None], ACGT[rng.integers(0, 4, size=(n_reads, R))], bases)
+    bases = np.where(rng.random((n_reads, R)) < 0.001, np.uint8(ord("N")), bases).astype(np.uint8)
+    return haps, bases, bq, iq, dq, gc
+
+
+def make_batch(seed, n_reads_per_region, hap_lens_per_region, R, profile="clean", sub_rate=None, name="",
+               foreign_frac=0.0):
+    rng = np.random.default_rng(seed)
+    rb, bq, iq, dq, gc, hb, hl, rl = [], [], [], [], [], [], [], []
+    rrs, rhs = [0], [0]
+    for nr, hls in zip(n_reads_per_region, hap_lens_per_region):
+        haps, b, q, i, d, c = _region(rng, int(nr), hls, R, profile, sub_rate, foreign_frac)
+        rb.append(b.reshape(-1)); bq.append(q.reshape(-1)); iq.append(i.reshape(-1))
+        dq.append(d.reshape(-1)); gc.append(c.reshape(-1))
+        rl.append(np.full(int(nr), R, np.int32))
+        for h in haps:
+            hb.append(h)
+            hl.append(len(h))
+        rrs.append(rrs[-1] + int(nr))
+        rhs.append(rhs[-1] + len(haps))
+    rl = np.concatenate(rl)
+    hl = np.asarray(hl, np.int32)
+    return RegionBatch(np.concatenate(rb), np.concatenate(bq), np.concatenate(iq), np.concatenate(dq),
+                       np.concatenate(gc), _offsets(rl), rl, np.concatenate(hb), _offsets(hl), hl,
+                       np.asarray(rrs, np.int64), np.asarray(rhs, np.int64), name)
+
+
+SEED0 = 0xB200
+
+
+def config1(profile="clean"):
+    """C1: one region, 64 reads x 8 haps, 150 bp x 300 bp (BASELINE.json configs[0])."""
+    return make_batch(SEED0 + 1, [64], [np.full(8, 300)], 150, profile, name="C1-" + profile)
+
+
+def config2(n_regions=10000, profile="clean", seed_extra=0):
+    """C2: WES-like, ~200 reads x 4-16 haps per region, R=150, H in [250,500] (configs[1])."""
+    rng = np.random.default_rng(SEED0 + 2 + 7919 * seed_extra)
+    nr = np.clip(rng.poisson(200, size=n_regions), 50, 400)
+    nh = rng.integers(4, 17, size=n_regions)
+    base = rng.integers(250, 501, size=n_regions)
+    hls = [np.clip(b + rng.integers(-10, 11, size=k), 250, 500) for b, k in zip(base, nh)]
+    return make_batch(SEED0 + 2 + 104729 * seed_extra, nr, hls, 150, profile, name="C2-%s-%d" % (profile, n_regions),
+                      foreign_frac=0.02)
+
+
+def config3(n_reads=2000, n_haps=32, profile="lowq"):
+    """C3: high-depth stress, 2000 reads x 32 haps, R=150, H~600, rescue heavy (configs[2])."""
+    rng = np.random.default_rng(SEED0 + 3)
+    return make_batch(SEED0 + 3, [n_reads], [rng.integers(590, 611, size=n_haps)], 150, profile,
+                      sub_rate=(0.05, 0.25), name="C3-" + profile, foreign_frac=0.30)
+
+
+def config4(n_regions=64, n_reads=128, n_haps=8, profile="clean"):
+    """C4: R=250, H log-uniform in [1000,2000], wide variance (configs[3])."""
+    rng = np.random.default_rng(SEED0 + 4)
+    hls = [np.exp(rng.uniform(np.log(1000), np.log(2000), size=n_haps)).astype(np.int64) for _ in range(n_regions)]
+    return make_batch(SEED0 + 4, [n_reads] * n_regions, hls, 250, profile, name="C4-" + profile,
+                      foreign_frac=0.02)
+
+
+def config5(n_regions=25000, profile="clean", shard=0):
+    """C5: chr20-scale, regions x 200 reads x 10 haps, R=150, H in [300,500] (configs[4]); `shard`
+    reseeds so every rank / shard gets distinct regions."""
+    rng = np.random.default_rng(SEED0 + 5 + 7919 * shard)
+    hls = [rng.integers(300, 501, size=10) for _ in range(n_regions)]
+    return make_batch(SEED0 + 5 + 104729 * shard, [200] * n_regions, hls, 150, profile,
+                      name="C5-%s-%d-s%d" % (profile, n_regions, shard), foreign_frac=0.02)
+
+
+def edge_cases(seed=1234):
+    """ragged edge-case batch: R in {1,2,15,...,255}, H in {1..700} incl. R>H, N bases, lower-case and
+    junk bytes (behave as 'A'), quals with the high bit set, per-base gcp != 10, quals 0/6/93/127."""
+    rng = np.random.default_rng(seed)
+    Rs = [1, 2, 15, 16, 17, 31, 32, 33, 48, 63, 64, 65, 95, 96, 127, 128, 150, 151, 159, 160, 161, 191, 192, 223, 224, 250, 255]
+    rb, bq, iq, dq, gc, rl, hb, hl, rrs, rhs = [], [], [], [], [], [], [], [], [0], [0]
+    for gi, R in enumerate(Rs):
+        nh = 4
+        Hs = [1, max(1, R // 2), R + 3, int(rng.integers(R, 700))][:nh]
+        base = _rand_bases(rng, max(Hs) + R, 0.01)
+        nr = 5
+        for h in Hs:
+            hh = base[:h].copy()
+            if h > 4 and gi % 3 == 0:
+                hh[int(rng.integers(0, h))] = ord("a")      # lower case -> behaves as 'A'
+                hh[int(rng.integers(0, h))] = ord("x")      # junk -> behaves as 'A'
+            hb.append(hh); hl.append(h)
+        for r in range(nr):
+            st = int(rng.integers(0, max(1, max(Hs) - R + 1)))
+            b = base[st:st + R].copy()
+            if len(b) < R:
+                b = np.concatenate([b, _rand_bases(rng, R - len(b))])
+            mut = rng.random(R) < (0.02 if r < 3 else 0.3)
+            b[mut] = ACGT[rng.integers(0, 4, size=int(mut.sum()))]
+            q = rng.choice(np.array([0, 6, 18, 20, 30, 41, 60, 93, 127], np.uint8), size=R)
+            i_ = rng.choice(np.array([0, 6, 10, 30, 45, 93, 127], np.uint8), size=R)
+            d_ = rng.choice(np.array([0, 6, 10, 30, 45, 93, 127], np.uint8), size=R)
+            c_ = rng.choice(np.array([1, 6, 10, 10, 10, 40], np.uint8), size=R)
+            if r == 4:  # high bit set: must be masked with &127 (ReadForPairHMM.cpp:35)
+                q = q | 0x80; i_ = i_ | 0x80; d_ = d_ | 0x80; c_ = c_ | 0x80
+            rb.append(b); bq.append(q.astype(np.uint8)); iq.append(i_.astype(np.uint8))
+            dq.append(d_.astype(np.uint8)); gc.append(c_.astype(np.uint8)); rl.append(R)
+        rrs.append(rrs[-1] + nr); rhs.append(rhs[-1] + nh)
+    rl = np.asarray(rl, np.int32); hl = np.asarray(hl, np.int32)
+    return RegionBatch(np.concatenate(rb), np.concatenate(bq), np.concatenate(iq), np.concatenate(dq),
+                       np.concatenate(gc), _offsets(rl), rl, np.concatenate(hb), _offsets(hl), hl,
+                       np.asarray(rrs, np.int64), np.asarray(rhs, np.int64), "edge")

@@ -1,0 +1,174 @@
+/* libpairhmm_cuda -- C ABI of the B200-native PairHMM read-likelihood engine.
+ *
+ * This is the drop-in boundary for deepmutect / Mutect2Cpp's PairHMM plugin point. Citations are
+ * relative to /root/reference/deepmutect/Mutect2Cpp-master/src ("M2/").
+ *
+ *   reference interface                                          replaced by
+ *   ------------------------------------------------------------ -------------------------------
+ *   initNative(use_double, max_threads)                          pairhmm_cuda_create
+ *       M2/intel/pairhmm/IntelPairHmm.h:37, IntelPairHmm.cc:202
+ *   PairHMM::initialize(readMaxLength, haplotypeMaxLength)       pairhmm_cuda_initialize
+ *       M2/utils/pairhmm/PairHMM.h:22-37, PairHMM.cpp:14-27
+ *   VectorLoglessPairHMM::computeLog10Likelihoods (+_trie,       pairhmm_cuda_compute
+ *   _trie_unique): reads x haplotypes of one region, read-major  (async: _submit / _wait)
+ *   out[r*nHaps+h]  M2/utils/pairhmm/VectorLoglessPairHMM.cpp:43-148,150-286
+ *   computeLikelihoodsNative(testcases, likelihoodArray)         pairhmm_cuda_compute_pairs
+ *       M2/intel/pairhmm/IntelPairHmm.h:39, IntelPairHmm.cc:259-293,332-351
+ *   (many regions from many host threads; the reference has no   pairhmm_cuda_compute_batch
+ *   equivalent -- it loops; here one call = few large launches)
+ *   doneNative (commented JNI original, IntelPairHmm.cc:192-200) pairhmm_cuda_destroy
+ *
+ * Numerics contract: FP32 forward pass scaled by 2^120; a pair whose float
+ * sum is < 1e-28f (MIN_ACCEPTED, M2/intel/pairhmm/pairhmm_common.h:41) is recomputed in FP64 scaled
+ * by 2^1020; value returned = log10 likelihood as double. Qualities are masked with &127
+ * (M2/haplotypecaller/ReadForPairHMM.cpp:35); bases other than A,C,G,T,N behave as 'A'
+ * (pairhmm_common.cc:26); 'N' on either side matches everything (avx-pairhmm-template.h:38,48-51).
+ *
+ * Ownership: all inputs are borrowed for the duration of the call only (for _submit: until _submit
+ * returns -- the engine has copied them to its pinned staging by then); outputs must stay valid
+ * until the call (or the matching _wait) returns. No C++ types and no exceptions cross this ABI.
+ * Every function returns 0 on success or a negative pairhmm_cuda_status; the text of the last
+ * error on a handle is available from pairhmm_cuda_last_error.
+ *
+ * Threading: one handle per host thread (as Mutect2Cpp keeps one PairHMM per worker thread,
+ * M2/main.cpp:199); calls on different handles are fully concurrent. A handle owns its CUDA
+ * streams, pinned staging and device buffers.
+ */
+#ifndef PAIRHMM_CUDA_H
+#define PAIRHMM_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PAIRHMM_CUDA_ABI_VERSION 1
+
+typedef enum pairhmm_cuda_status {
+    PAIRHMM_OK = 0,
+    PAIRHMM_ERR_ARG = -1,      /* null pointer, negative size, length above the initialised maximum */
+    PAIRHMM_ERR_CUDA = -2,     /* a CUDA runtime call failed (text in last_error)                    */
+    PAIRHMM_ERR_NO_DEVICE = -3,/* no usable sm_100 device: the engine has NO CPU fallback            */
+    PAIRHMM_ERR_OOM = -4,      /* host or device allocation failed                                   */
+    PAIRHMM_ERR_STATE = -5     /* e.g. wait on an unknown ticket                                     */
+} pairhmm_cuda_status;
+
+/* One read as VectorLoglessPairHMM.cpp:71-77 gathers it: five byte arrays of length len. */
+typedef struct phmm_read {
+    const uint8_t *bases;  /* getBasesNoCopy()                                   */
+    const uint8_t *base_q; /* getBaseQualitiesNoCopy()                           */
+    const uint8_t *ins_q;  /* ReadUtils::getBaseInsertionQualities (default 45)  */
+    const uint8_t *del_q;  /* ReadUtils::getBaseDeletionQualities  (default 45)  */
+    const uint8_t *gcp;    /* gap continuation penalties, (*gcp)[read]           */
+    int32_t len;
+} phmm_read;
+
+/* One haplotype: HaplotypeDataHolder{haplotypeBases,length}, M2/utils/pairhmm/HaplotypeDataHolder.h:13 */
+typedef struct phmm_hap {
+    const uint8_t *bases;
+    int32_t len;
+} phmm_hap;
+
+/* One active region = one computeLog10Likelihoods call. log10_out / rescued_out are
+ * [n_reads * n_haps], read-major; rescued_out may be NULL. */
+typedef struct phmm_region {
+    const phmm_read *reads;
+    int32_t n_reads;
+    const phmm_hap *haps;
+    int32_t n_haps;
+    double *log10_out;
+    uint8_t *rescued_out;
+} phmm_region;
+
+typedef struct pairhmm_cuda_config {
+    int32_t device;          /* CUDA ordinal; -1 = current device                                  */
+    int32_t use_double;      /* initNative's use_double: 1 = every pair through the FP64 kernel     */
+    int32_t exact_fp32;      /* 1 = FP32 pass without FMA contraction (bit-identical to the         */
+                             /*     reference's AVX-256 build); 0 = contracted (as its AVX-512 build) */
+    int32_t dedup_reads;     /* 1 = de-duplicate identical reads per region (VLPH.cpp:83-103)       */
+    int32_t pack_threads;    /* host threads used to pack a batch (0 = auto)                        */
+    int64_t chunk_cells;     /* target DP cells per internal launch group (0 = default)             */
+    int32_t reserved[8];
+} pairhmm_cuda_config;
+
+typedef struct pairhmm_cuda_stats {
+    uint64_t calls, regions, reads, unique_reads, pairs, unique_pairs, cells;
+    uint64_t rescued_pairs;      /* pairs routed to the FP64 kernel                       */
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t kernel_launches;    /* launches of this library's own kernels                */
+    double gpu_ms_float, gpu_ms_double, gpu_ms_total; /* CUDA-event times, summed over calls   */
+    double host_ms_pack, host_ms_scatter, host_ms_total;
+} pairhmm_cuda_stats;
+
+typedef struct pairhmm_cuda_handle pairhmm_cuda_handle;
+typedef int64_t pairhmm_cuda_ticket;
+
+int pairhmm_cuda_abi_version(void);
+/* number of usable sm_100 devices (0 if none / no driver) */
+int pairhmm_cuda_device_count(void);
+
+void pairhmm_cuda_default_config(pairhmm_cuda_config *cfg);
+int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **out);
+int pairhmm_cuda_destroy(pairhmm_cuda_handle *h);
+
+/* PairHMM::initialize(readMaxLength, haplotypeMaxLength): both must be > 0 (PairHMM.cpp:16).
+ * Sizes the staging for one region; larger inputs later make the buffers grow, they are not an error. */
+int pairhmm_cuda_initialize(pairhmm_cuda_handle *h, int read_max_len, int hap_max_len);
+
+/* One region, blocking. n_reads == 0 returns immediately (VectorLoglessPairHMM.cpp:46-47). */
+int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads,
+                         const phmm_hap *haps, int n_haps, double *log10_out, uint8_t *rescued_out);
+
+/* Same, asynchronous: inputs are consumed before _submit returns; outputs are written by _wait. */
+int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads,
+                        const phmm_hap *haps, int n_haps, double *log10_out, uint8_t *rescued_out,
+                        pairhmm_cuda_ticket *ticket);
+int pairhmm_cuda_wait(pairhmm_cuda_handle *h, pairhmm_cuda_ticket ticket);
+
+/* Many regions in one call (coalesced into few large launches, packing overlapped with compute). */
+int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions);
+
+/* Flat form of the same batch for language bindings: five read byte arrays and the haplotype bytes
+ * concatenated, per-item offsets/lengths, region r owns reads [reg_read_start[r], reg_read_start[r+1])
+ * and haps [reg_hap_start[r], reg_hap_start[r+1]); output region-major then read-major, i.e.
+ * region r starts at sum_{q<r} nReads_q * nHaps_q. */
+int pairhmm_cuda_compute_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                              const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                              const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                              const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                              int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                              int64_t n_regions, double *log10_out, uint8_t *rescued_out);
+
+/* Explicit pair list (computeLikelihoodsNative's testcase vector): out[p] for pair
+ * (reads[read_idx[p]], haps[hap_idx[p]]). */
+int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads,
+                               const phmm_hap *haps, int n_haps, const uint32_t *read_idx,
+                               const uint32_t *hap_idx, size_t n_pairs, double *log10_out,
+                               uint8_t *rescued_out);
+
+/* Device-resident replay, for measuring the kernels without host<->device traffic: stage a flat batch
+ * once (H2D + layout), then run the float+rescue kernels on it any number of times; results stay on
+ * the device until _resident_fetch. kernel_ms (nullable) receives the CUDA-event time of the run. */
+int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                               const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                               const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                               const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                               int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                               int64_t n_regions);
+int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms);
+int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out);
+
+int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);
+int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h);
+const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h);
+
+/* The lookup tables the engine uploaded (ph2pr[128], matchToMatchProb triangle for q<128 = 8256
+ * entries), for tests: they must equal Context<float/double>'s (M2/intel/pairhmm/Context.h:75-89). */
+#define PAIRHMM_CUDA_MM_COUNT 8256
+int pairhmm_cuda_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PAIRHMM_CUDA_H */

@@ -1,0 +1,92 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes loaders for the CPU checkers.
+
+  * ``load_oracle()``    -> oracle/libpairhmm_oracle.so (our scalar C restatement, pairhmm_oracle.c)
+  * ``load_reference()`` -> oracle/_ref/libref_pairhmm.so (the reference's own sources compiled by
+    oracle/Makefile; present only if it was built in the container that has /root/reference)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg import this.
+The product package never does.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+MM_COUNT = 32640
+
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C")
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C")
+
+_COMPUTE_ARGS = [_u8p, _u8p, _u8p, _u8p, _u8p, _i64p, _i32p, C.c_int, _u8p, _i64p, _i32p, C.c_int,
+                 _u32p, _u32p, C.c_int64, C.c_int, C.c_int, C.c_int, _f64p, C.c_void_p]
+
+
+def build(ref=True):
+    """make the oracle (+ the reference .so when /root/reference is here)."""
+    subprocess.run(["make", "-s", "-C", HERE, "libpairhmm_oracle.so"] + (["ref"] if ref else []), check=True)
+
+
+class _Lib:
+    def __init__(self, path, prefix):
+        self.path = path
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self._compute = getattr(self.lib, prefix + "_compute")
+        self._compute.argtypes = _COMPUTE_ARGS
+        self._compute.restype = C.c_double
+        self._tables = getattr(self.lib, prefix + "_tables")
+        self._tables.argtypes = [C.c_void_p] * 4 + [C.c_int]
+        self._tables.restype = None
+
+    def tables(self):
+        pf = np.zeros(128, np.float32); mf = np.zeros(MM_COUNT, np.float32)
+        pd = np.zeros(128, np.float64); md = np.zeros(MM_COUNT, np.float64)
+        self._tables(pf.ctypes.data, mf.ctypes.data, pd.ctypes.data, md.ctypes.data, MM_COUNT)
+        return pf, mf, pd, md
+
+    def compute(self, b, use_double=False, threads=1, tables_in_timed_region=False, want_rescued=True):
+        """b: a FlatBatch (see synth.py). Returns (log10[n_pairs] f64, rescued[n_pairs] u8, seconds)."""
+        n = int(b.pair_read.shape[0])
+        out = np.zeros(n, np.float64)
+        resc = np.zeros(n, np.uint8)
+        if n == 0:
+            return out, resc, 0.0
+        secs = self._compute(b.read_bases, b.base_q, b.ins_q, b.del_q, b.gcp, b.read_off, b.read_len,
+                             int(b.read_len.shape[0]), b.hap_bases, b.hap_off, b.hap_len,
+                             int(b.hap_len.shape[0]), b.pair_read, b.pair_hap, n, int(use_double),
+                             int(threads), int(tables_in_timed_region), out,
+                             resc.ctypes.data if want_rescued else None)
+        return out, resc, secs
+
+
+class Oracle(_Lib):
+    def __init__(self):
+        super().__init__(os.path.join(HERE, "libpairhmm_oracle.so"), "oracle")
+
+
+class Reference(_Lib):
+    def __init__(self):
+        super().__init__(os.path.join(HERE, "_ref", "libref_pairhmm.so"), "ref_pairhmm")
+        self.lib.ref_pairhmm_isa.restype = C.c_int
+
+    def isa(self):
+        return int(self.lib.ref_pairhmm_isa())
+
+
+def load_oracle():
+    p = os.path.join(HERE, "libpairhmm_oracle.so")
+    if not os.path.exists(p):
+        build(ref=False)
+    return Oracle()
+
+
+def reference_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_pairhmm.so"))
+
+
+def load_reference():
+    return Reference()

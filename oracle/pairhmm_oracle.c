@@ -1,0 +1,205 @@
+/* TEST INFRASTRUCTURE ONLY -- scalar C restatement of the reference PairHMM (see pairhmm_oracle.h).
+ * Compile with -ffp-contract=off: the reference's AVX-256 objects contain no FMA (built -mavx only,
+ * M2/intel/pairhmm/CMakeLists.txt:7), and this file is meant to agree with them bit for bit.
+ * M2 = /root/reference/deepmutect/Mutect2Cpp-master/src. */
+#include "pairhmm_oracle.h"
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+#if defined(__x86_64__) || defined(__i386__)
+#include <xmmintrin.h>
+#define FTZ_ON() unsigned _csr = _mm_getcsr(); _mm_setcsr(_csr | 0x8000u) /* IntelPairHmm.cc:230 */
+#define FTZ_RESTORE() _mm_setcsr(_csr)
+#else
+#define FTZ_ON() (void)0
+#define FTZ_RESTORE() (void)0
+#endif
+
+/* ---- tables: Context.h:30-34 constants ---- */
+#define MAX_QUAL 254
+#define JAC_TOL 8.0
+#define JAC_STEP 0.0001
+#define JAC_INV_STEP (1.0 / JAC_STEP)
+#define JAC_SIZE 80001 /* (int)(8.0/0.0001)+1 */
+
+static float g_ph2pr_f[128], g_mm_f[ORACLE_MM_COUNT], g_jac_f[JAC_SIZE];
+static double g_ph2pr_d[128], g_mm_d[ORACLE_MM_COUNT], g_jac_d[JAC_SIZE];
+static pthread_once_t g_once = PTHREAD_ONCE_INIT;
+
+/* Context.h:92-121, NUMBER = float */
+static float approx_log10_sum_f(float small, float big) {
+    if (small > big) { float t = big; big = small; small = t; }
+    if (isinf(small) || isinf(big)) return big;
+    float diff = big - small;
+    if (diff >= (float)JAC_TOL) return big;
+    float d = (float)(diff * ((float)JAC_INV_STEP));
+    int ind = (d > 0.0f) ? (int)(d + 0.5f) : (int)(d - 0.5f); /* fastRound, Context.h:87-90 */
+    return big + g_jac_f[ind];
+}
+/* Context.h:92-121, NUMBER = double */
+static double approx_log10_sum_d(double small, double big) {
+    if (small > big) { double t = big; big = small; small = t; }
+    if (isinf(small) || isinf(big)) return big;
+    double diff = big - small;
+    if (diff >= JAC_TOL) return big;
+    double d = diff * JAC_INV_STEP;
+    int ind = (d > 0.0) ? (int)(d + 0.5) : (int)(d - 0.5);
+    return big + g_jac_d[ind];
+}
+
+static void build_tables(void) {
+    const double INV_LN10 = 0.434294; /* truncated on purpose, Context.h:76 */
+    for (int k = 0; k < JAC_SIZE; k++) { /* Context.h:65-72 */
+        double v = log10(1.0 + pow(10.0, -((double)k) * JAC_STEP));
+        g_jac_d[k] = v;
+        g_jac_f[k] = (float)v;
+    }
+    for (int i = 0, offset = 0; i <= MAX_QUAL; offset += ++i) /* Context.h:78-88 */
+        for (int j = 0; j <= i; j++) {
+            double sf = approx_log10_sum_f((float)-0.1 * (float)i, (float)-0.1 * (float)j);
+            double lf = log1p(-fmin(1.0, pow(10, sf))) * INV_LN10;
+            g_mm_f[offset + j] = (float)pow(10, lf);
+            double sd = approx_log10_sum_d((double)-0.1 * (double)i, (double)-0.1 * (double)j);
+            double ld = log1p(-fmin(1.0, pow(10, sd))) * INV_LN10;
+            g_mm_d[offset + j] = pow(10, ld);
+        }
+    for (int x = 0; x < 128; x++) { /* Context.h:137-140,178-181 */
+        g_ph2pr_d[x] = pow(10.0, -((double)x) / 10.0);
+        g_ph2pr_f[x] = powf(10.f, -((float)x) / 10.f);
+    }
+}
+
+void oracle_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, int mm_count) {
+    pthread_once(&g_once, build_tables);
+    memcpy(ph2pr_f, g_ph2pr_f, sizeof g_ph2pr_f);
+    memcpy(ph2pr_d, g_ph2pr_d, sizeof g_ph2pr_d);
+    memcpy(mm_f, g_mm_f, (size_t)mm_count * sizeof(float));
+    memcpy(mm_d, g_mm_d, (size_t)mm_count * sizeof(double));
+}
+
+/* triangular lookup of set_mm_prob (Context.h:156-167): quals are <128 so always the table branch */
+static inline int mm_index(int ins, int del) {
+    int mn = del, mx = ins;
+    if (ins <= del) { mn = ins; mx = del; }
+    return ((mx * (mx + 1)) >> 1) + mn;
+}
+
+/* pairhmm_common.h:69-85: A0 C1 T2 G3 N4, every other byte behaves as 'A' (zero-initialised table) */
+static inline int base_code(uint8_t b) {
+    switch (b) { case 'A': return 0; case 'C': return 1; case 'T': return 2; case 'G': return 3; case 'N': return 4; default: return 0; }
+}
+
+/* The forward recurrence, one macro body for both precisions (avx-pairhmm-template.h:110-121,
+ * 150-169, 177-192, 310-344 restated row-major). */
+#define FORWARD_BODY(T, PH2PR, MM, INITC)                                                        \
+    pthread_once(&g_once, build_tables);                                                         \
+    if (R <= 0 || H <= 0) return (T)0;                                                           \
+    T *buf = (T *)malloc(sizeof(T) * 6 * (size_t)(H + 1));                                       \
+    T *Mp = buf, *Xp = Mp + (H + 1), *Yp = Xp + (H + 1), *Mc = Yp + (H + 1), *Xc = Mc + (H + 1), \
+      *Yc = Xc + (H + 1);                                                                        \
+    uint8_t *hc = (uint8_t *)malloc((size_t)H);                                                  \
+    for (int c = 0; c < H; c++) hc[c] = (uint8_t)base_code(hap[c]);                              \
+    const T initY = (INITC) / (T)H;                                                              \
+    for (int c = 0; c <= H; c++) { Mp[c] = (T)0; Xp[c] = (T)0; Yp[c] = initY; }                  \
+    for (int r = 1; r <= R; r++) {                                                               \
+        const int iq = ins_q[r - 1] & 127, dq = del_q[r - 1] & 127, cq = gcp[r - 1] & 127,       \
+                  bq = base_q[r - 1] & 127;                                                      \
+        const T pMM = MM[mm_index(iq, dq)], pXX = PH2PR[cq], pYY = PH2PR[cq], pMX = PH2PR[iq],   \
+                pMY = PH2PR[dq], pGAPM = (T)1.0 - PH2PR[cq], dist = PH2PR[bq];                   \
+        const T d1 = (T)1.0 - dist, d3 = dist / (T)3.0;                                          \
+        const int rc = base_code(read[r - 1]);                                                   \
+        Mc[0] = Xc[0] = Yc[0] = (T)0;                                                            \
+        for (int c = 1; c <= H; c++) {                                                           \
+            const int h = hc[c - 1];                                                             \
+            const T e = (rc == h || rc == 4 || h == 4) ? d1 : d3;                                \
+            T t0 = Mp[c - 1] * pMM;                                                              \
+            T t1 = Xp[c - 1] * pGAPM;                                                            \
+            T t2 = Yp[c - 1] * pGAPM;                                                            \
+            Mc[c] = ((t0 + t1) + t2) * e;                                                        \
+            T u0 = Mp[c] * pMX, u1 = Xp[c] * pXX;                                                \
+            Xc[c] = u0 + u1;                                                                     \
+            T v0 = Mc[c - 1] * pMY, v1 = Yc[c - 1] * pYY;                                        \
+            Yc[c] = v0 + v1;                                                                     \
+        }                                                                                        \
+        T *t;                                                                                    \
+        t = Mp; Mp = Mc; Mc = t; t = Xp; Xp = Xc; Xc = t; t = Yp; Yp = Yc; Yc = t;               \
+    }                                                                                            \
+    T sumM = (T)0, sumX = (T)0;                                                                  \
+    for (int c = 1; c <= H; c++) { sumM = sumM + Mp[c]; sumX = sumX + Xp[c]; }                   \
+    T res = sumM + sumX;                                                                         \
+    free(buf); free(hc);                                                                         \
+    return res;
+
+float oracle_forward_float(const uint8_t *read, const uint8_t *base_q, const uint8_t *ins_q,
+                           const uint8_t *del_q, const uint8_t *gcp, int R, const uint8_t *hap, int H) {
+    FORWARD_BODY(float, g_ph2pr_f, g_mm_f, ldexpf(1.f, 120))
+}
+double oracle_forward_double(const uint8_t *read, const uint8_t *base_q, const uint8_t *ins_q,
+                             const uint8_t *del_q, const uint8_t *gcp, int R, const uint8_t *hap, int H) {
+    FORWARD_BODY(double, g_ph2pr_d, g_mm_d, ldexp(1.0, 1020))
+}
+
+/* ---- flat pair list driver (IntelPairHmm.cc:332-351 dispatch) ---- */
+typedef struct {
+    const uint8_t *rb, *bq, *iq, *dq, *gc, *hb;
+    const int64_t *roff, *hoff;
+    const int32_t *rlen, *hlen;
+    const uint32_t *pr, *ph;
+    int64_t n_pairs;
+    int use_double, tid, nth;
+    double *out;
+    uint8_t *rescued;
+} job_t;
+
+static void *worker(void *arg) {
+    job_t *j = (job_t *)arg;
+    FTZ_ON();
+    const float LOG10_INIT_F = log10f(ldexpf(1.f, 120));   /* Context.h:184 */
+    const double LOG10_INIT_D = log10(ldexp(1.0, 1020));   /* Context.h:143 */
+    for (int64_t p = j->tid; p < j->n_pairs; p += j->nth) {
+        const int64_t ro = j->roff[j->pr[p]], ho = j->hoff[j->ph[p]];
+        const int R = j->rlen[j->pr[p]], H = j->hlen[j->ph[p]];
+        float f = j->use_double ? 0.0f
+                                : oracle_forward_float(j->rb + ro, j->bq + ro, j->iq + ro, j->dq + ro,
+                                                       j->gc + ro, R, j->hb + ho, H);
+        if (f < 1e-28f) { /* MIN_ACCEPTED, pairhmm_common.h:41 */
+            double d = oracle_forward_double(j->rb + ro, j->bq + ro, j->iq + ro, j->dq + ro, j->gc + ro,
+                                             R, j->hb + ho, H);
+            j->out[p] = log10(d) - LOG10_INIT_D;
+            if (j->rescued) j->rescued[p] = 1;
+        } else {
+            j->out[p] = (double)(log10f(f) - LOG10_INIT_F);
+            if (j->rescued) j->rescued[p] = 0;
+        }
+    }
+    FTZ_RESTORE();
+    return NULL;
+}
+
+double oracle_compute(const uint8_t *read_bases, const uint8_t *base_q, const uint8_t *ins_q,
+                      const uint8_t *del_q, const uint8_t *gcp, const int64_t *read_off,
+                      const int32_t *read_len, int n_reads, const uint8_t *hap_bases,
+                      const int64_t *hap_off, const int32_t *hap_len, int n_haps,
+                      const uint32_t *pair_read, const uint32_t *pair_hap, int64_t n_pairs,
+                      int use_double, int n_threads, int tables_in_timed_region, double *out,
+                      uint8_t *rescued) {
+    (void)n_reads; (void)n_haps; (void)tables_in_timed_region; /* the port builds row constants inline */
+    pthread_once(&g_once, build_tables);
+    if (n_threads < 1) n_threads = 1;
+    pthread_t *th = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)n_threads);
+    job_t *jobs = (job_t *)malloc(sizeof(job_t) * (size_t)n_threads);
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    for (int t = 0; t < n_threads; t++) {
+        job_t j = {read_bases, base_q, ins_q, del_q, gcp, hap_bases, read_off, hap_off, read_len, hap_len,
+                   pair_read, pair_hap, n_pairs, use_double, t, n_threads, out, rescued};
+        jobs[t] = j;
+        pthread_create(&th[t], NULL, worker, &jobs[t]);
+    }
+    for (int t = 0; t < n_threads; t++) pthread_join(th[t], NULL);
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    free(th); free(jobs);
+    return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
+}

@@ -1,0 +1,37 @@
+/* TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference PairHMM numerics.
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may use it.
+ * Parity status: PINNED against the reference's own code compiled here (oracle/_ref, see
+ * tests/test_oracle_vs_reference.py and the golden fixtures under tests/golden/ made from it);
+ * the reference ships no golden vectors of its own for this path. */
+#ifndef PAIRHMM_ORACLE_H
+#define PAIRHMM_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORACLE_MM_COUNT 32640 /* ((254+1)*(254+2))>>1, Context.h:52 */
+
+/* Lookup tables exactly as Context<float>/Context<double> build them (Context.h:65-89,137-183). */
+void oracle_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d, int mm_count);
+
+/* One pair. Inputs are the raw bytes the reference's testcase carries (quals are masked &127 here,
+ * ReadForPairHMM.cpp:35). Returns the scaled forward sum (2^120 float / 2^1020 double scale). */
+float oracle_forward_float(const uint8_t *read, const uint8_t *base_q, const uint8_t *ins_q,
+                           const uint8_t *del_q, const uint8_t *gcp, int R, const uint8_t *hap, int H);
+double oracle_forward_double(const uint8_t *read, const uint8_t *base_q, const uint8_t *ins_q,
+                             const uint8_t *del_q, const uint8_t *gcp, int R, const uint8_t *hap, int H);
+
+/* Flat pair list, same signature as oracle/ref_driver.cpp:ref_pairhmm_compute (dispatch + rescue rule
+ * of IntelPairHmm.cc:332-351). Returns wall seconds of the compute loop. */
+double oracle_compute(const uint8_t *read_bases, const uint8_t *base_q, const uint8_t *ins_q,
+                      const uint8_t *del_q, const uint8_t *gcp, const int64_t *read_off,
+                      const int32_t *read_len, int n_reads, const uint8_t *hap_bases,
+                      const int64_t *hap_off, const int32_t *hap_len, int n_haps,
+                      const uint32_t *pair_read, const uint32_t *pair_hap, int64_t n_pairs,
+                      int use_double, int n_threads, int tables_in_timed_region, double *out,
+                      uint8_t *rescued);
+#ifdef __cplusplus
+}
+#endif
+#endif

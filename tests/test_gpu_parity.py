@@ -1,0 +1,159 @@
+"""-m gpu: the CUDA path, called through the C ABI, against the CPU oracle on identical bytes."""
+import numpy as np
+import pytest
+
+import fgdp_b200
+from fgdp_b200 import synth
+from util import assert_parity, TOL
+
+pytestmark = pytest.mark.gpu
+
+
+def _region_lists(b, g=0):
+    r0, r1 = int(b.reg_read_start[g]), int(b.reg_read_start[g + 1])
+    h0, h1 = int(b.reg_hap_start[g]), int(b.reg_hap_start[g + 1])
+    reads = []
+    for r in range(r0, r1):
+        o, n = int(b.read_off[r]), int(b.read_len[r])
+        reads.append(tuple(a[o:o + n] for a in (b.read_bases, b.base_q, b.ins_q, b.del_q, b.gcp)))
+    haps = [b.hap_bases[int(b.hap_off[h]):int(b.hap_off[h]) + int(b.hap_len[h])] for h in range(h0, h1)]
+    return reads, haps
+
+
+@pytest.mark.parametrize("profile", ["clean", "lowq"])
+def test_config1_region_call(engine, oracle, profile):
+    """BASELINE configs[0]: 64 reads x 8 haps, through pairhmm_cuda_compute as the adapter calls it."""
+    b = synth.config1(profile)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    reads, haps = _region_lists(b)
+    engine.initialize(150, 300)
+    got, gresc = engine.compute(reads, haps)
+    assert got.shape == (64, 8)
+    assert_parity(got, gresc, want, wresc, what="C1-" + profile)
+
+
+def test_edge_cases(engine, oracle):
+    b = synth.edge_cases()
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    got, gresc = engine.compute_batch(b)
+    assert_parity(got, gresc, want, wresc, what="edge")
+    assert wresc.sum() > 50 and (wresc == 0).sum() > 50     # both routes are exercised
+
+
+def test_exact_mode_is_bit_identical_to_the_unfused_oracle(oracle):
+    """exact_fp32=1 disables FMA contraction: same IEEE operations in the same order as the scalar oracle
+    (and as the reference's AVX-256 build), so the FP32 route must agree to the last bit."""
+    e = fgdp_b200.Engine(exact_fp32=True)
+    try:
+        for b in (synth.config1("clean"), synth.edge_cases(), synth.config3(96, 6)):
+            want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+            got, gresc = e.compute_batch(b)
+            assert np.array_equal(gresc, wresc), b.name
+            f = wresc == 0
+            assert np.array_equal(got[f], want[f]), "%s: FP32 route not bit-identical" % b.name
+            assert_parity(got, gresc, want, wresc, what=b.name)
+    finally:
+        e.close()
+
+
+def test_config3_rescue_heavy(engine, oracle):
+    b = synth.config3(200, 8)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    got, gresc = engine.compute_batch(b)
+    assert_parity(got, gresc, want, wresc, what="C3")
+    assert wresc.mean() > 0.2
+
+
+def test_config4_long_haps(engine, oracle):
+    b = synth.config4(3, 12, 4)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    got, gresc = engine.compute_batch(b)
+    assert_parity(got, gresc, want, wresc, what="C4")
+
+
+def test_config2_many_regions_chunked(oracle):
+    """several regions, forced through several chunks and both staging slots"""
+    b = synth.config2(12)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=8)
+    e = fgdp_b200.Engine(chunk_cells=int(b.cells() // 5))
+    try:
+        got, gresc = e.compute_batch(b)
+        st = e.stats()
+    finally:
+        e.close()
+    assert_parity(got, gresc, want, wresc, what="C2")
+    assert st["pairs"] == b.n_pairs and st["cells"] == b.cells() and st["regions"] == 12
+    assert st["kernel_launches"] >= 5 * 3
+
+
+def test_use_double_everything_rescued(oracle):
+    b = synth.config1("clean")
+    want, _, _ = oracle.compute(b.as_flat(), use_double=True, threads=4)
+    e = fgdp_b200.Engine(use_double=True)
+    try:
+        got, gresc = e.compute_batch(b)
+    finally:
+        e.close()
+    assert gresc.all()
+    assert np.abs(got - want).max() < 1e-9
+
+
+def test_dedup_and_duplicates(engine, oracle):
+    """identical reads share one DP (VectorLoglessPairHMM.cpp:83-103) and still get their own rows"""
+    b = synth.config1("clean")
+    reads, haps = _region_lists(b)
+    reads = reads[:10] + reads[:10] + reads[3:5]
+    engine.stats_reset()
+    got, _ = engine.compute(reads, haps)
+    st = engine.stats()
+    assert st["reads"] == 22 and st["unique_reads"] == 10
+    assert np.array_equal(got[:10], got[10:20]) and np.array_equal(got[3:5], got[20:22])
+    want, _, _ = oracle.compute(b.as_flat(), threads=2)
+    assert np.abs(got[:10].reshape(-1) - want[:80]).max() <= TOL
+
+
+def test_submit_wait_overlap(engine, oracle):
+    b = synth.config2(3)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    off = b.region_out_offsets()
+    tickets = []
+    for g in range(3):
+        reads, haps = _region_lists(b, g)
+        tickets.append(engine.submit(reads, haps))
+    for g, (t, out, resc) in enumerate(tickets):
+        engine.wait(t)
+        assert_parity(out, resc, want[off[g]:off[g + 1]], wresc[off[g]:off[g + 1]], what="submit %d" % g)
+
+
+def test_pair_list(engine, oracle):
+    b = synth.config1("lowq")
+    reads, haps = _region_lists(b)
+    rng = np.random.default_rng(5)
+    ri = rng.integers(0, 64, size=300).astype(np.uint32); hi = rng.integers(0, 8, size=300).astype(np.uint32)
+    want, _, _ = oracle.compute(b.as_flat(), threads=2)
+    got, _ = engine.compute_pairs(reads, haps, ri, hi)
+    assert np.abs(got - want.reshape(64, 8)[ri, hi]).max() <= TOL
+
+
+def test_empty_and_errors(engine):
+    out, resc = engine.compute([], [np.frombuffer(b"ACGT", np.uint8)])
+    assert out.shape == (0, 1)
+    with pytest.raises(fgdp_b200.PairHMMError):
+        engine.initialize(10, 0)
+    r = tuple(np.full(300, v, np.uint8) for v in (65, 30, 45, 45, 10))
+    with pytest.raises(fgdp_b200.PairHMMError):
+        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 255 rows: refused loudly, not faked
+    z = tuple(np.zeros(0, np.uint8) for _ in range(5))
+    out, resc = engine.compute([z], [np.frombuffer(b"ACGT", np.uint8)])
+    assert np.isneginf(out).all() and resc.all()
+
+
+def test_resident_replay_matches(engine, oracle):
+    b = synth.config2(6)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=8)
+    engine.resident_load(b)
+    for _ in range(2):
+        ms, ms_f = engine.resident_run()
+        assert ms > 0 and ms_f > 0
+    got, gresc = engine.resident_fetch()
+    assert_parity(got, gresc, want, wresc, what="resident")
