@@ -144,7 +144,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         const phmm_hap &hp = rv.haps[i];
         if (hp.len < 0 || (hp.len > 0 && !hp.bases)) return fail(h, PAIRHMM_ERR_ARG, "bad haplotype");
         pl.hap_bytes += (uint64_t)hp.len;
-        pl.hap_words += (uint32_t)hp.len + 1;
+        pl.hap_words += hap_words(hp.len);
         hmax = std::max(hmax, hp.len);
     }
     for (int i = 0; i < rv.n_reads; ++i) {
@@ -256,7 +256,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     RES(h_haps, nh + 1); RES(h_haplist, hl + 1); RES(h_units, n_units + 1); RES(h_out, up + 1); RES(h_flag, up + 1);
     RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
     RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
-    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 2 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
 #undef RES
 
     // pass B: copy bytes, fill descriptors and units
@@ -290,7 +290,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             s.h_hapoff.p[p.first_hap + q] = ho;
             s.h_haps.p[p.first_hap + q] = DevHap{wo, hp.len};
             s.h_haplist.p[p.hap_list_off + q] = p.first_hap + (uint32_t)q;
-            ho += (uint64_t)hp.len; wo += (uint32_t)hp.len + 1;
+            ho += (uint64_t)hp.len; wo += hap_words(hp.len);
         }
     });
     h->stats.host_ms_pack += ms_since(t0);
@@ -804,6 +804,19 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
     h->stats.cells = c; h->stats.pairs = p;
     h->stats.gpu_ms_total = g0; h->stats.gpu_ms_float = g1; h->stats.gpu_ms_double = g2;
     return st;
+}
+
+// Raw FP32-pass sums (2^120-scaled, before log10) per UNIQUE pair, in region-major / unique-read-major
+// order (= pair order when no read is duplicated). For bit-exactness tests of the FP32 kernel.
+int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n) {
+    if (!h || !fres_out) return PAIRHMM_ERR_ARG;
+    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch_raw: nothing loaded");
+    Slot &s = h->slots[0];
+    if (n != (int64_t)s.n_upairs) return fail(h, PAIRHMM_ERR_ARG, "resident_fetch_raw: n != unique pairs");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(fres_out, s.d_fres.p, sizeof(float) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
+    CU(h, cudaStreamSynchronize(s.stream));
+    return PAIRHMM_OK;
 }
 
 }  // extern "C"

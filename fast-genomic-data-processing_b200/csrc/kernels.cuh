@@ -4,10 +4,14 @@
 //   read planes  uint8  rd[5][plane]    bases | base_q | ins_q | del_q | gcp, raw bytes as the caller
 //                                       gave them (masking &127 and base->code happen on device)
 //   DevRead      {off,len}              byte offset of a read inside every plane
-//   hap words    uint32 hapw[]          words [0,64) = lead/tail padding (31 PAD, 1 SEP, 32 PAD); then
-//                                       per haplotype H code words + 1 SEP word. A code word is the
-//                                       one-hot base code (A1 C2 T4 G8 N15) replicated in all 4 bytes.
-//   DevHap       {off,len}              word offset / H
+//   hap words    uint32 hapw[]          one word per DP column, in tiles of kTile columns. Words
+//                                       [0,kLeadWords) = pipeline fill (PAD.. + one SEP) and drain (PAD..);
+//                                       then per haplotype: H code words, one SEP, and PADs up to the next
+//                                       tile boundary (a PAD after a SEP is a no-op column). A code word holds the
+//                                       base index b (A0 C1 T2 G3 N4) pre-multiplied for every rows-per-lane
+//                                       bucket (see code_word()), so a lane turns it into K match bits with
+//                                       one funnel shift of its per-base row masks.
+//   DevHap       {off,len}              word offset (multiple of kTile) / H
 //   hap_list     uint32[]               haplotype ids, one run per work unit
 //   DevUnit      {read,hap_list,nh,out} one warp-task: read x nh haplotypes streamed back to back
 //   results      float fres[] (FP32 pass), double out[] (final log10), uint8 flag[] (rescued)
@@ -21,11 +25,24 @@ struct DevRead { uint32_t off; int32_t len; };
 struct DevHap  { uint32_t off; int32_t len; };
 struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t nh; uint32_t out; };
 
-constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain)
+constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
 constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next haplotype
-constexpr int kLeadWords = 64;               // hapw[0..30]=PAD, [31]=SEP, [32..63]=PAD
+constexpr int kTile = 2;                     // columns a lane advances per pipeline step
+constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1] SEP, rest PAD
 constexpr int kMaxRowsPerLane = 8;           // K; one warp covers reads up to 32*K-1 rows
 constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition
+
+// words a haplotype of length H occupies in hapw (code words + alignment PADs + SEP)
+inline uint32_t hap_words(int32_t H) { return ((uint32_t)H / kTile + 1u) * kTile; }
+
+// match-mask geometry of a rows-per-lane bucket: rows are split into groups of kGroupBits(K) rows, each
+// group keeps 5 (one per haplotype base) bit fields of that width in one 32-bit register
+__host__ __device__ constexpr int group_bits(int K) { return K <= 6 ? K : 4; }
+// bit position inside a code word of the field that holds b * group_bits(K)
+__host__ __device__ constexpr int code_field(int K) {
+    return group_bits(K) == 5 ? 0 : group_bits(K) == 4 ? 5 : group_bits(K) == 6 ? 10
+         : group_bits(K) == 3 ? 15 : group_bits(K) == 2 ? 20 : 25;
+}
 
 struct KernelArgs {
     const uint8_t *rd;          // read planes

@@ -17,6 +17,7 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_destroy", "pairhmm_cuda_initialize", "pairhmm_cuda_compute", "pairhmm_cuda_submit",
     "pairhmm_cuda_wait", "pairhmm_cuda_compute_batch", "pairhmm_cuda_compute_flat", "pairhmm_cuda_compute_pairs",
     "pairhmm_cuda_resident_load", "pairhmm_cuda_resident_run", "pairhmm_cuda_resident_fetch",
+    "pairhmm_cuda_resident_fetch_raw",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
 ]
 MM_COUNT = 8256
@@ -96,6 +97,7 @@ def load_library():
     lib.pairhmm_cuda_resident_load.argtypes = [vp] + flat
     lib.pairhmm_cuda_resident_run.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.pairhmm_cuda_resident_fetch.argtypes = [vp, vp, vp]
+    lib.pairhmm_cuda_resident_fetch_raw.argtypes = [vp, vp, i64]
     lib.pairhmm_cuda_stats_get.argtypes = [vp, C.POINTER(Stats)]
     lib.pairhmm_cuda_stats_reset.argtypes = [vp]
     lib.pairhmm_cuda_last_error.argtypes = [vp]
@@ -234,6 +236,12 @@ class Engine:
         out = np.zeros(self._resident_pairs, np.float64); resc = np.zeros(self._resident_pairs, np.uint8)
         self._check(self.lib.pairhmm_cuda_resident_fetch(self.h, out.ctypes.data, resc.ctypes.data))
         return out, resc
+
+    def resident_fetch_raw(self):
+        """raw 2^120-scaled FP32 sums per unique pair (test hook)"""
+        out = np.zeros(self._resident_pairs, np.float32)
+        self._check(self.lib.pairhmm_cuda_resident_fetch_raw(self.h, out.ctypes.data, out.shape[0]))
+        return out
 
     def stats(self):
         s = Stats()

@@ -66,6 +66,18 @@ class _Lib:
 class Oracle(_Lib):
     def __init__(self):
         super().__init__(os.path.join(HERE, "libpairhmm_oracle.so"), "oracle")
+        self.lib.oracle_forward_float_pairs.argtypes = [_u8p, _u8p, _u8p, _u8p, _u8p, _i64p, _i32p, _u8p, _i64p,
+                                                        _i32p, _u32p, _u32p, C.c_int64, C.c_void_p]
+        self.lib.oracle_forward_float_pairs.restype = None
+
+    def forward_float(self, b):
+        """raw 2^120-scaled FP32 sums (FTZ on, no FMA) for every pair of a FlatPairs"""
+        n = int(b.pair_read.shape[0])
+        out = np.zeros(n, np.float32)
+        self.lib.oracle_forward_float_pairs(b.read_bases, b.base_q, b.ins_q, b.del_q, b.gcp, b.read_off, b.read_len,
+                                            b.hap_bases, b.hap_off, b.hap_len, b.pair_read, b.pair_hap, n,
+                                            out.ctypes.data)
+        return out
 
 
 class Reference(_Lib):

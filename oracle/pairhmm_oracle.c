@@ -203,3 +203,18 @@ double oracle_compute(const uint8_t *read_bases, const uint8_t *base_q, const ui
     free(th); free(jobs);
     return (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec);
 }
+
+/* raw scaled sums of the FP32 pass for a flat pair list (FTZ on), for bit-exactness tests */
+void oracle_forward_float_pairs(const uint8_t *read_bases, const uint8_t *base_q, const uint8_t *ins_q,
+                                const uint8_t *del_q, const uint8_t *gcp, const int64_t *read_off,
+                                const int32_t *read_len, const uint8_t *hap_bases, const int64_t *hap_off,
+                                const int32_t *hap_len, const uint32_t *pair_read, const uint32_t *pair_hap,
+                                int64_t n_pairs, float *out) {
+    FTZ_ON();
+    for (int64_t p = 0; p < n_pairs; p++) {
+        const int64_t ro = read_off[pair_read[p]], ho = hap_off[pair_hap[p]];
+        out[p] = oracle_forward_float(read_bases + ro, base_q + ro, ins_q + ro, del_q + ro, gcp + ro,
+                                      read_len[pair_read[p]], hap_bases + ho, hap_len[pair_hap[p]]);
+    }
+    FTZ_RESTORE();
+}

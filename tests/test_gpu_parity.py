@@ -42,15 +42,21 @@ def test_edge_cases(engine, oracle):
 
 def test_exact_mode_is_bit_identical_to_the_unfused_oracle(oracle):
     """exact_fp32=1 disables FMA contraction: same IEEE operations in the same order as the scalar oracle
-    (and as the reference's AVX-256 build), so the FP32 route must agree to the last bit."""
-    e = fgdp_b200.Engine(exact_fp32=True)
+    (and as the reference's AVX-256 build), so the raw FP32 forward sums must agree to the last bit.
+    (The final log10 is not compared bitwise: glibc's log10f is not correctly rounded, the device's is.)"""
+    e = fgdp_b200.Engine(exact_fp32=True, dedup_reads=False)
     try:
-        for b in (synth.config1("clean"), synth.edge_cases(), synth.config3(96, 6)):
-            want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
-            got, gresc = e.compute_batch(b)
-            assert np.array_equal(gresc, wresc), b.name
-            f = wresc == 0
-            assert np.array_equal(got[f], want[f]), "%s: FP32 route not bit-identical" % b.name
+        for b in (synth.config1("clean"), synth.config1("lowq"), synth.edge_cases(), synth.config3(96, 6),
+                  synth.config4(2, 6, 3)):
+            flat = b.as_flat()
+            want_raw = oracle.forward_float(flat)
+            want, wresc, _ = oracle.compute(flat, threads=4)
+            e.resident_load(b)
+            e.resident_run()
+            raw = e.resident_fetch_raw()
+            got, gresc = e.resident_fetch()
+            assert np.array_equal(raw.view(np.uint32), want_raw.view(np.uint32)), \
+                "%s: %d of %d FP32 sums differ in bits" % (b.name, (raw.view(np.uint32) != want_raw.view(np.uint32)).sum(), raw.size)
             assert_parity(got, gresc, want, wresc, what=b.name)
     finally:
         e.close()
