@@ -75,10 +75,10 @@ int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
         if (_e != cudaSuccess) return fail_cuda((h), _e, #expr);       \
     } while (0)
 
-// counters layout in d_counters: [0..8] work queues of the FP32 launches (per K), [9..17] rescue
-// counts (per K), [18..26] work queues of the FP64 launches (per K)
-constexpr int kCounterWords = 32;
-constexpr int kQueueF = 0, kRescueCount = 9, kQueueD = 18;
+// counters layout in d_counters, one word per (K,KL) bin each: work queues of the FP32 launches,
+// rescue counts, work queues of the FP64 launches
+constexpr int kCounterWords = 3 * kNumBins + 4;
+constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = 2 * kNumBins;
 
 // Runs fn(i) for i in [0,n) on up to `threads` std::threads (dynamic chunks of `grain`).
 template <class F> void parallel_for(size_t n, int threads, size_t grain, F fn) {
@@ -153,7 +153,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
         if (rows_per_lane(r.len) == 0)
-            return fail(h, PAIRHMM_ERR_ARG, "read longer than 255 bases: not supported by this build");
+            return fail(h, PAIRHMM_ERR_ARG, "read longer than 256 bases: not supported by this build");
         uint32_t u = kNoRead;
         if (!table.empty()) {
             const uint64_t hv = hash_read(r);
@@ -169,6 +169,10 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             u = (uint32_t)pl.uniq_src.size();
             pl.uniq_src.push_back((uint32_t)i);
             pl.read_bytes += (uint64_t)r.len;
+            for (int q = 0; q < r.len; ++q) {       // gap-continuation range, as the kernel sees it (&127)
+                const uint8_t c = r.gcp[q] & 127;
+                pl.gcp_min = std::min(pl.gcp_min, c); pl.gcp_max = std::max(pl.gcp_max, c);
+            }
         }
         pl.uniq_of_read[i] = u;
     }
@@ -182,7 +186,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     pl.group = g;
     pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;
     for (uint32_t j = 0; j < pl.n_uniq; ++j)
-        pl.unit_count[rows_per_lane(rv.reads[pl.uniq_src[j]].len)] += pl.n_groups;
+        pl.unit_count[bin_of_read(rv.reads[pl.uniq_src[j]].len)] += pl.n_groups;
     return PAIRHMM_OK;
 }
 
@@ -218,13 +222,15 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // prefix sums
     uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0;
     uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
-    uint32_t bin_count[kMaxRowsPerLane + 1] = {0};
-    uint32_t bin_pairs[kMaxRowsPerLane + 1] = {0};
+    uint32_t bin_count[kNumBins] = {0};
+    uint32_t bin_pairs[kNumBins] = {0};
+    uint8_t gmin = 255, gmax = 0;
     for (size_t i = 0; i < n_regs; ++i) {
         RegionPlan &p = s.plans[i];
         p.first_uniq = nu; p.read_byte_off = rbytes; p.first_hap = nh; p.hap_byte_off = hbytes;
         p.hap_word_off = hw; p.hap_list_off = hl; p.upair_off = up;
-        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+        gmin = std::min(gmin, p.gcp_min); gmax = std::max(gmax, p.gcp_max);
+        for (int k = 0; k < kNumBins; ++k) {
             p.unit_off[k] = bin_count[k]; bin_count[k] += p.unit_count[k];
             if (p.n_groups) bin_pairs[k] += p.unit_count[k] / p.n_groups * (uint32_t)s.regions[i].n_haps;
         }
@@ -239,13 +245,15 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         pairs += (uint64_t)s.regions[i].n_reads * (uint64_t)s.regions[i].n_haps;
         reads_in += (uint64_t)s.regions[i].n_reads;
     }
-    s.bin_start[0] = s.bin_start[1] = 0;
-    s.rescue_base[0] = s.rescue_base[1] = 0;
-    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+    s.bin_start[0] = 0;
+    s.rescue_base[0] = 0;
+    s.uniform_gcp = gmin == gmax;     // also true for "no reads" (255,0 never equal -> false; harmless)
+    s.gcp_value = gmin;
+    for (int k = 0; k < kNumBins; ++k) {
         s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
         s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
     }
-    const uint32_t n_units = s.bin_start[kMaxRowsPerLane + 1];
+    const uint32_t n_units = s.bin_start[kNumBins];
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
     s.cells = cells; s.pairs = pairs; s.reads_in = reads_in;
@@ -264,7 +272,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         const RegionView &rv = s.regions[i];
         const RegionPlan &p = s.plans[i];
         uint64_t ro = p.read_byte_off;
-        uint32_t fill[kMaxRowsPerLane + 1] = {0};
+        uint32_t fill[kNumBins] = {0};
         for (uint32_t j = 0; j < p.n_uniq; ++j) {
             const phmm_read &r = rv.reads[p.uniq_src[j]];
             uint8_t *d = s.h_rd.p + ro;
@@ -273,7 +281,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             std::memcpy(d + 4 * s.plane, r.gcp, r.len);
             s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
             ro += (uint64_t)r.len;
-            const int k = rows_per_lane(r.len);
+            const int k = bin_of_read(r.len);
             DevUnit *ud = s.h_units.p + s.bin_start[k] + p.unit_off[k] + fill[k];
             for (uint32_t g = 0; g < p.n_groups; ++g) {
                 const uint32_t h0 = g * p.group;
@@ -300,7 +308,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 // H2D of a packed chunk + haplotype word expansion. Asynchronous on the slot's stream.
 int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
-    const uint32_t n_units = s.bin_start[kMaxRowsPerLane + 1];
+    const uint32_t n_units = s.bin_start[kNumBins];
     if (s.n_uniq) {
         CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * 5, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
@@ -320,29 +328,40 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     return PAIRHMM_OK;
 }
 
-// FP32 pass per K-bin -> finalize -> FP64 rescue per K-bin. Asynchronous on the slot's stream.
+// FP32 pass per (K,KL) bin -> finalize -> FP64 rescue per bin. Asynchronous on the slot's stream.
 int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
     CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kCounterWords, st));
     CU(h, cudaEventRecord(s.ev_begin, st));
+    const HostTables &t = host_tables();
     KernelArgs a{};
     a.rd = s.d_rd.p; a.plane = s.plane; a.reads = s.d_reads.p; a.hapw = s.d_hapw.p; a.haps = s.d_haps.p;
     a.hap_list = s.d_haplist.p; a.fres = s.d_fres.p; a.out = s.d_out.p; a.flag = s.d_flag.p;
     a.log10_init_d = h->log10_init_d;
+    // uniform gap-continuation constants, computed exactly as the per-row path does (ph2pr[c], 1 - ph2pr[c])
+    const int gc = s.gcp_value & 127;
+    a.u_xy_f = t.ph2pr_f[gc]; a.u_gapm_f = 1.0f - t.ph2pr_f[gc];
+    a.u_xy_d = t.ph2pr_d[gc]; a.u_gapm_d = 1.0 - t.ph2pr_d[gc];
     const bool all_double = h->cfg.use_double != 0;
+    const Variant vf = h->cfg.exact_fp32 ? Variant::F32_EXACT
+                       : (s.uniform_gcp && !h->cfg.reserved[0]) ? Variant::F32_UG : Variant::F32_GEN;
+    const Variant vd = Variant::F64_GEN;
+    auto grid_for = [&](Variant v, int K, uint64_t work_items) {
+        const uint64_t full = (uint64_t)h->sm_count * (uint64_t)std::max(1, h->blocks_per_sm[(int)v][K]);
+        return (int)std::min<uint64_t>(full, (work_items + 3) / 4);
+    };
     if (!all_double) {
-        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
-            const uint32_t n = s.bin_start[k + 1] - s.bin_start[k];
+        for (int b = 0; b < kNumBins; ++b) {
+            const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
             if (!n) continue;
-            a.units = s.d_units.p + s.bin_start[k]; a.n_units = n; a.n_units_dev = nullptr;
-            a.queue = s.d_counters.p + kQueueF + k;
+            int K, KL; bin_shape(b, K, KL);
+            a.units = s.d_units.p + s.bin_start[b]; a.n_units = n; a.n_units_dev = nullptr;
+            a.queue = s.d_counters.p + kQueueF + b;
             a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
             // every bin appends to its own slice of d_rescue (at most one entry per unique pair)
-            a.rescue_units = s.d_rescue.p + s.rescue_base[k];
-            a.rescue_count = s.d_counters.p + kRescueCount + k;
-            const int grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_f[k]),
-                                                     ((uint64_t)n + 3) / 4);
-            CU(h, launch_forward_float(k, h->cfg.exact_fp32 != 0, a, grid, st));
+            a.rescue_units = s.d_rescue.p + s.rescue_base[b];
+            a.rescue_count = s.d_counters.p + kRescueCount + b;
+            CU(h, launch_forward(vf, K, KL, a, grid_for(vf, K, n), st));
             h->stats.kernel_launches += 1;
         }
         FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f};
@@ -350,26 +369,25 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         if (s.n_upairs) h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_float_done, st));
-    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
-        const uint32_t n = s.bin_start[k + 1] - s.bin_start[k];
+    for (int b = 0; b < kNumBins; ++b) {
+        const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
         if (!n) continue;
-        a.queue = s.d_counters.p + kQueueD + k;
+        int K, KL; bin_shape(b, K, KL);
+        a.queue = s.d_counters.p + kQueueD + b;
         a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
         a.rescue_units = nullptr; a.rescue_count = nullptr;
         int grid;
         if (all_double) {
-            a.units = s.d_units.p + s.bin_start[k]; a.n_units = n; a.n_units_dev = nullptr;
-            grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_d[k]), ((uint64_t)n + 3) / 4);
+            a.units = s.d_units.p + s.bin_start[b]; a.n_units = n; a.n_units_dev = nullptr;
+            grid = grid_for(vd, K, n);
         } else {
-            a.units = s.d_rescue.p + s.rescue_base[k]; a.n_units = 0;
-            a.n_units_dev = s.d_counters.p + kRescueCount + k;
-            // the rescue count is only known on the device: launch a full persistent grid, bounded by
-            // the number of pairs of this bin
-            const uint64_t pairs_k = (uint64_t)s.rescue_base[k + 1] - s.rescue_base[k];
-            grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * std::max(1, h->blocks_per_sm_d[k]), (pairs_k + 3) / 4);
+            // the rescue count is only known on the device: a persistent grid bounded by the bin's pairs
+            a.units = s.d_rescue.p + s.rescue_base[b]; a.n_units = 0;
+            a.n_units_dev = s.d_counters.p + kRescueCount + b;
+            grid = grid_for(vd, K, (uint64_t)s.rescue_base[b + 1] - s.rescue_base[b]);
             if (grid < 1) continue;
         }
-        CU(h, launch_forward_double(k, a, grid, st));
+        CU(h, launch_forward(vd, K, KL, a, grid, st));
         h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_end, st));
@@ -510,14 +528,14 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
     for (auto &s : h->slots) {
         if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreate(&s.ev_begin) != cudaSuccess || cudaEventCreate(&s.ev_float_done) != cudaSuccess ||
-            cudaEventCreate(&s.ev_end) != cudaSuccess || s.d_counters.reserve(64) != cudaSuccess)
+            cudaEventCreate(&s.ev_end) != cudaSuccess || s.d_counters.reserve(kCounterWords) != cudaSuccess)
             return bail(PAIRHMM_ERR_CUDA);
     }
-    for (int k = 1; k <= kMaxRowsPerLane; ++k) {
-        h->blocks_per_sm_f[k] = forward_blocks_per_sm(k, false, c.exact_fp32 != 0);
-        h->blocks_per_sm_d[k] = forward_blocks_per_sm(k, true, false);
-        if (h->blocks_per_sm_f[k] < 1 || h->blocks_per_sm_d[k] < 1) return bail(PAIRHMM_ERR_CUDA);
-    }
+    for (int v = 0; v < 4; ++v)
+        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
+            h->blocks_per_sm[v][k] = forward_blocks_per_sm((Variant)v, k, k - 1);
+            if (h->blocks_per_sm[v][k] < 1) return bail(PAIRHMM_ERR_CUDA);
+        }
     *out = h;
     return PAIRHMM_OK;
 }

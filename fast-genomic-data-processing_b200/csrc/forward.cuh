@@ -1,0 +1,287 @@
+// PairHMM forward kernel template for sm_100a (no tensor cores: the M/X/Y recurrence is a wavefront).
+//
+// Work decomposition: one WARP sweeps one work unit = one read against a run of haplotypes.
+//   * lane l owns K consecutive rows of the DP matrix (read rows l*K .. l*K+K-1, top-aligned); rows past
+//     the end of the read are dead slots (all constants 0). The read's last row is slot KL of lane
+//     (R-1)/K; KL is a template parameter so that the two running sums of the last row stay in fixed
+//     registers.
+//   * lanes are skewed by one tile (kTile columns): at step t lane l works on tile t-l of the unit's
+//     column stream. The only cross-lane traffic per column is two shuffles: the bottom row of lane l,
+//     pre-combined with the transition constants of the row below it (D = diagonal term of M, U = the
+//     X of that row). Lane 0 substitutes the matrix's row-0 boundary (D = 2^s/H * pGAPM[row 1], U = 0).
+//   * the haplotypes of a unit are streamed back to back through the same pipeline, separated by one
+//     SEP word (= column 0 of the next haplotype), so pipeline fill/drain is paid once per unit.
+//   * UG ("uniform gap continuation"): when every gcp byte of the launch is the same value -- always
+//     the case for Mutect2Cpp, which fills a constant array (PairHMMLikelihoodCalculationEngine.cpp:
+//     284-292) -- pXX=pYY and pGAPM come from the kernel's constant bank instead of registers. This
+//     matters on sm_100: an FFMA with three distinct REGISTER sources issues at ~0.6/clk/SMSP, with a
+//     constant-bank operand at ~0.9 (tools/ubench/fma_rate.cu, measured on B200), and it is what keeps
+//     every FMA-pipe instruction of the inner loop at <= 2 register reads.
+// Numerics follow avx-pairhmm-template.h:177-192 / SURVEY.md Appendix A (association order kept).
+#pragma once
+#include "kernels.cuh"
+
+namespace phmm {
+
+constexpr unsigned kFull = 0xffffffffu;
+
+template <typename T> struct Num;
+template <> struct Num<float> {
+    static __device__ __forceinline__ float init_const() { return 1.329227995784916e+36f; }  // 2^120
+    template <bool EXACT> static __device__ __forceinline__ float mul(float a, float b) { return EXACT ? __fmul_rn(a, b) : a * b; }
+    template <bool EXACT> static __device__ __forceinline__ float add(float a, float b) { return EXACT ? __fadd_rn(a, b) : a + b; }
+    // a*b + c, contracted unless EXACT
+    template <bool EXACT> static __device__ __forceinline__ float mad(float a, float b, float c) {
+        return EXACT ? __fadd_rn(__fmul_rn(a, b), c) : fmaf(a, b, c);
+    }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+    static __device__ __forceinline__ float uxy(const KernelArgs &a) { return a.u_xy_f; }
+    static __device__ __forceinline__ float ugapm(const KernelArgs &a) { return a.u_gapm_f; }
+};
+template <> struct Num<double> {
+    static __device__ __forceinline__ double init_const() { return 1.1235582092889474e+307; }  // 2^1020
+    template <bool EXACT> static __device__ __forceinline__ double mul(double a, double b) { return EXACT ? __dmul_rn(a, b) : a * b; }
+    template <bool EXACT> static __device__ __forceinline__ double add(double a, double b) { return EXACT ? __dadd_rn(a, b) : a + b; }
+    template <bool EXACT> static __device__ __forceinline__ double mad(double a, double b, double c) {
+        return EXACT ? __dadd_rn(__dmul_rn(a, b), c) : fma(a, b, c);
+    }
+    static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+    static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+    static __device__ __forceinline__ double uxy(const KernelArgs &a) { return a.u_xy_d; }
+    static __device__ __forceinline__ double ugapm(const KernelArgs &a) { return a.u_gapm_d; }
+};
+
+// A0 C1 T2 G3 N4 of pairhmm_common.h:69-85; every byte that is not C,T,G,N behaves as 'A'.
+__device__ __forceinline__ uint32_t base_index(uint32_t b) {
+    uint32_t c = 0u;
+    c = (b == 'C') ? 1u : c;
+    c = (b == 'T') ? 2u : c;
+    c = (b == 'G') ? 3u : c;
+    c = (b == 'N') ? 4u : c;
+    return c;
+}
+
+template <int C> struct TileWord;
+template <> struct TileWord<1> { using type = uint32_t; };
+template <> struct TileWord<2> { using type = uint2; };
+template <> struct TileWord<4> { using type = uint4; };
+__device__ __forceinline__ uint32_t tw_get(const uint32_t &t, int) { return t; }
+__device__ __forceinline__ uint32_t tw_get(const uint2 &t, int j) { return j == 0 ? t.x : t.y; }
+__device__ __forceinline__ uint32_t tw_get(const uint4 &t, int j) { return j == 0 ? t.x : j == 1 ? t.y : j == 2 ? t.z : t.w; }
+__device__ __forceinline__ uint32_t tw_or(const uint32_t &t) { return t; }
+__device__ __forceinline__ uint32_t tw_or(const uint2 &t) { return t.x | t.y; }
+__device__ __forceinline__ uint32_t tw_or(const uint4 &t) { return t.x | t.y | t.z | t.w; }
+
+template <typename T, int K, int KL, bool EXACT, bool UG>
+__global__ void __launch_bounds__(kThreads) forward_kernel(const KernelArgs a) {
+    static_assert(KL >= 0 && KL < K, "last-row slot out of range");
+    static_assert(!(EXACT && UG), "the exact mode uses the general path");
+    using N = Num<T>;
+    constexpr int C = kTile;
+    using Tile = typename TileWord<C>::type;
+    constexpr int GB = group_bits(K);           // rows per match-mask register
+    constexpr int NG = (K + GB - 1) / GB;
+    constexpr int FIELD = code_field(K);
+    constexpr int KR = UG ? 1 : K;              // per-row pXY/pGAPM registers only on the general path
+    const int lane = threadIdx.x & 31;
+    const bool lane0 = lane == 0;
+    const T *__restrict__ ph = static_cast<const T *>(a.ph2pr);
+    const T *__restrict__ mmt = static_cast<const T *>(a.mm);
+    const Tile *__restrict__ tiles = reinterpret_cast<const Tile *>(a.hapw);
+    const uint32_t n_units = a.n_units_dev ? *a.n_units_dev : a.n_units;
+
+    for (;;) {
+        uint32_t u = 0;
+        if (lane0) u = atomicAdd(a.queue, 1u);
+        u = __shfl_sync(kFull, u, 0);
+        if (u >= n_units) break;
+        const DevUnit unit = a.units[u];
+        const DevRead rr = a.reads[unit.read];
+        const int last_lane = (rr.len - 1) / K;       // owns the read's last row, in slot KL
+
+        // ---- per-slot constants (ReadForPairHMM.cpp:72-80; stripeINITIALIZATION template.h:150-152)
+        T pMM[K], pMX[K], pMY[K], d1[K], d3[K], pXYr[KR], pGAPMr[KR];
+        uint32_t mask[NG];                            // per haplotype base b: bit GB*b+i = row i of the group matches
+#pragma unroll
+        for (int i = 0; i < NG; ++i) mask[i] = 0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int g = lane * K + k;               // 0-based read row
+            if (g < rr.len) {
+                const uint8_t *p = a.rd + rr.off + g;
+                const uint32_t rb = base_index(p[0]);
+                const int bq = p[a.plane] & 127, iq = p[2 * a.plane] & 127, dq = p[3 * a.plane] & 127,
+                          cq = p[4 * a.plane] & 127;
+                const int mx = max(iq, dq), mn = min(iq, dq);
+                pMM[k] = mmt[((mx * (mx + 1)) >> 1) + mn];
+                pMX[k] = ph[iq];
+                pMY[k] = ph[dq];
+                if constexpr (!UG) { pXYr[k] = ph[cq]; pGAPMr[k] = N::sub((T)1.0, ph[cq]); }
+                const T dist = ph[bq];
+                d1[k] = N::sub((T)1.0, dist);
+                d3[k] = N::div(dist, (T)3.0);
+                // match: same base, or either side is N (template.h:38,48-51)
+                const uint32_t one = 1u << (k % GB);
+                const uint32_t all = one | (one << GB) | (one << (2 * GB)) | (one << (3 * GB)) | (one << (4 * GB));
+                mask[k / GB] |= (rb == 4u) ? all : ((one << (GB * rb)) | (one << (4 * GB)));
+            } else {                                   // dead slot below the read
+                pMM[k] = pMX[k] = pMY[k] = d1[k] = d3[k] = (T)0;
+                if constexpr (!UG) { pXYr[k] = pGAPMr[k] = (T)0; }
+            }
+        }
+        // transition constants of the row below this lane's last slot (= slot 0 of lane+1; 0 past lane 31)
+        T nMM = __shfl_down_sync(kFull, pMM[0], 1), nMX = __shfl_down_sync(kFull, pMX[0], 1);
+        T nXXr = (T)0, nGAPMr = (T)0;
+        if constexpr (!UG) { nXXr = __shfl_down_sync(kFull, pXYr[0], 1); nGAPMr = __shfl_down_sync(kFull, pGAPMr[0], 1); }
+        if (lane == 31) { nMM = nMX = nXXr = nGAPMr = (T)0; }
+        // gap-continuation constants: constant bank (UG) or this row's registers
+#define PXY(k)   (UG ? N::uxy(a) : pXYr[UG ? 0 : (k)])
+#define PGAPM(k) (UG ? N::ugapm(a) : pGAPMr[UG ? 0 : (k)])
+#define NXX      (UG ? N::uxy(a) : nXXr)
+#define NGAPM    (UG ? N::ugapm(a) : nGAPMr)
+
+        // pipeline steps: 32 (fill) + sum over haplotypes of their tile count
+        int steps = 0;
+        for (uint32_t i = lane; i < unit.nh; i += 32) steps += a.haps[a.hap_list[unit.hap_list + i]].len / C + 1;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) steps += __shfl_xor_sync(kFull, steps, o);
+        steps += 32;
+
+        T M[K], X[K], Y[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) { M[k] = X[k] = Y[k] = (T)0; }
+        T Dprev = (T)0, sumM = (T)0, sumX = (T)0, Dbound = (T)0;
+        T Din[C], Uin[C];
+#pragma unroll
+        for (int j = 0; j < C; ++j) { Din[j] = Uin[j] = (T)0; }
+        int cur = -1;
+        uint32_t tix = 31 - lane;                      // tile index: lane l sees l PAD tiles, then [PAD..,SEP]
+        Tile w = tiles[tix];
+
+        // one DP column for this lane's K rows (computeMXY, template.h:177-192): Dd = diagonal term and
+        // Uu = X of the row above, both as delivered by the lane above (or the row-0 boundary)
+        auto column = [&](uint32_t cw, T Dd, T Uu) {
+            uint32_t mbits[NG];
+#pragma unroll
+            for (int g = 0; g < NG; ++g) mbits[g] = __funnelshift_r(mask[g], 0u, FIELD ? (cw >> FIELD) : cw);
+            T Mn[K], Xn[K], Yn[K];
+            {
+                const T e = (mbits[0] & 1u) ? d1[0] : d3[0];
+                Mn[0] = N::template mul<EXACT>(Dd, e);
+                Xn[0] = Uu;
+                if (EXACT) Yn[0] = N::template add<true>(N::template mul<true>(M[0], pMY[0]), N::template mul<true>(Y[0], PXY(0)));
+                else       Yn[0] = N::template mad<false>(Y[0], PXY(0), M[0] * pMY[0]);
+            }
+#pragma unroll
+            for (int k = 1; k < K; ++k) {
+                const T e = ((mbits[k / GB] >> (k % GB)) & 1u) ? d1[k] : d3[k];
+                T s;
+                if (EXACT) {
+                    s = N::template add<true>(N::template add<true>(N::template mul<true>(M[k - 1], pMM[k]),
+                                                                      N::template mul<true>(X[k - 1], PGAPM(k))),
+                                              N::template mul<true>(Y[k - 1], PGAPM(k)));
+                    Mn[k] = N::template mul<true>(s, e);
+                    Xn[k] = N::template add<true>(N::template mul<true>(Mn[k - 1], pMX[k]), N::template mul<true>(Xn[k - 1], PXY(k)));
+                    Yn[k] = N::template add<true>(N::template mul<true>(M[k], pMY[k]), N::template mul<true>(Y[k], PXY(k)));
+                } else {
+                    // every FFMA keeps the gap-continuation constant as its multiplier: with UG that is a
+                    // constant-bank operand, i.e. two register reads per instruction
+                    s = N::template mad<false>(Y[k - 1], PGAPM(k), N::template mad<false>(X[k - 1], PGAPM(k), M[k - 1] * pMM[k]));
+                    Mn[k] = s * e;
+                    Xn[k] = N::template mad<false>(Xn[k - 1], PXY(k), Mn[k - 1] * pMX[k]);
+                    Yn[k] = N::template mad<false>(Y[k], PXY(k), M[k] * pMY[k]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < K; ++k) { M[k] = Mn[k]; X[k] = Xn[k]; Y[k] = Yn[k]; }
+            sumM = N::template add<EXACT>(sumM, M[KL]);                           // template.h:326,329
+            sumX = N::template add<EXACT>(sumX, X[KL]);
+        };
+        // bottom row, pre-combined with the transition constants of the row below it
+        auto emit_down = [&](T &Dout, T &Uout) {
+            if (EXACT) {
+                Dout = N::template add<true>(N::template add<true>(N::template mul<true>(M[K - 1], nMM),
+                                                                     N::template mul<true>(X[K - 1], NGAPM)),
+                                             N::template mul<true>(Y[K - 1], NGAPM));
+                Uout = N::template add<true>(N::template mul<true>(M[K - 1], nMX), N::template mul<true>(X[K - 1], NXX));
+            } else {
+                Dout = N::template mad<false>(Y[K - 1], NGAPM, N::template mad<false>(X[K - 1], NGAPM, M[K - 1] * nMM));
+                Uout = N::template mad<false>(X[K - 1], NXX, M[K - 1] * nMX);
+            }
+        };
+        // flagged word: column 0 of a haplotype (SEP) or fill/drain/alignment (PAD)
+        auto flagged = [&](uint32_t cw, uint32_t &next_tix) {
+            if (!(cw & 0x40000000u)) {
+                if (lane == last_lane && (uint32_t)cur < unit.nh) {
+                    const T r = N::template add<EXACT>(sumM, sumX);              // template.h:339-343
+                    if constexpr (sizeof(T) == 4) {
+                        a.fres[unit.out + cur] = r;
+                        if (r < 1e-28f) {                                          // IntelPairHmm.cc:342
+                            const uint32_t slot = atomicAdd(a.rescue_count, 1u);
+                            a.rescue_units[slot] = DevUnit{unit.read, unit.hap_list + (uint32_t)cur, 1u,
+                                                           unit.out + (uint32_t)cur};
+                        }
+                    } else {
+                        a.out[unit.out + cur] = log10(r) - a.log10_init_d;        // IntelPairHmm.cc:344
+                        a.flag[unit.out + cur] = 1;
+                    }
+                }
+                ++cur;
+                sumM = sumX = (T)0;
+                T initY = (T)0;
+                if ((uint32_t)cur < unit.nh) {
+                    const DevHap h = a.haps[a.hap_list[unit.hap_list + cur]];
+                    next_tix = h.off / C;
+                    initY = N::div(N::init_const(), (T)h.len);                   // template.h:115
+                } else {
+                    next_tix = 32;                                                // drain PAD tiles
+                }
+                // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
+                Dbound = N::template mul<EXACT>(initY, PGAPM(0));
+                if (lane0) Din[C - 1] = Dbound;        // becomes Dprev of the next step's first column
+            }
+#pragma unroll
+            for (int k = 0; k < K; ++k) { M[k] = (T)0; X[k] = (T)0; Y[k] = (T)0; }
+        };
+
+#pragma unroll 1
+        for (int t = 0; t < steps; ++t) {
+            uint32_t next_tix = tix + 1;
+            Tile wn = __ldg(tiles + next_tix);         // next step's tile, in flight during this step
+            T Dout[C], Uout[C];
+            if ((int)tw_or(w) < 0) {
+                const uint32_t seq_tix = next_tix;
+#pragma unroll
+                for (int j = 0; j < C; ++j) {
+                    const uint32_t cw = tw_get(w, j);
+                    if ((int)cw < 0) flagged(cw, next_tix);
+                    else column(cw, j == 0 ? Dprev : Din[j - 1], Uin[j]);
+                    emit_down(Dout[j], Uout[j]);
+                }
+                if (next_tix != seq_tix) wn = __ldg(tiles + next_tix);
+            } else {
+#pragma unroll
+                for (int j = 0; j < C; ++j) {
+                    column(tw_get(w, j), j == 0 ? Dprev : Din[j - 1], Uin[j]);
+                    emit_down(Dout[j], Uout[j]);
+                }
+            }
+            Dprev = Din[C - 1];   // D of the last column of the PREVIOUS exchange: diagonal of next step's first column
+#pragma unroll
+            for (int j = 0; j < C; ++j) {
+                const T dn = __shfl_up_sync(kFull, Dout[j], 1), un = __shfl_up_sync(kFull, Uout[j], 1);
+                Din[j] = lane0 ? Dbound : dn;
+                Uin[j] = lane0 ? (T)0 : un;
+            }
+            tix = next_tix;
+            w = wn;
+        }
+#undef PXY
+#undef PGAPM
+#undef NXX
+#undef NGAPM
+    }
+}
+
+}  // namespace phmm

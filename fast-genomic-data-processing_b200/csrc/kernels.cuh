@@ -58,6 +58,9 @@ struct KernelArgs {
     // tables (precision of the launch)
     const void *ph2pr;            // T[128]
     const void *mm;               // T[8256]
+    // uniform gap-continuation constants (UG kernels): ph2pr[gcp] and 1 - ph2pr[gcp]
+    float u_xy_f, u_gapm_f;
+    double u_xy_d, u_gapm_d;
     // FP32 pass outputs
     float *fres;                  // scaled forward sum per unique pair
     DevUnit *rescue_units;        // pairs with fres < 1e-28f, appended
@@ -76,17 +79,22 @@ struct FinalizeArgs {
     float log10_init_f;           // log10f(2^120), host libm (Context.h:184)
 };
 
-// rows-per-lane bucket for a read length: smallest K with R <= 32*K - 1 (one row-0 emulator row is
-// always kept above the read); 0 if the read needs the striped path.
-inline int rows_per_lane(int R) { int k = R / 32 + 1; return k <= kMaxRowsPerLane ? k : 0; }
+// Work bins: a read of length R goes to rows-per-lane bucket K = ceil(R/32) (1..kMaxRowsPerLane) and
+// its last row lands in slot KL = (R-1) % K of lane (R-1)/K. One kernel instantiation per (K, KL).
+constexpr int kNumBins = kMaxRowsPerLane * (kMaxRowsPerLane + 1) / 2;    // 36
+inline int rows_per_lane(int R) { int k = (R + 31) / 32; return k <= kMaxRowsPerLane ? k : 0; }
+inline int bin_of(int K, int KL) { return K * (K - 1) / 2 + KL; }
+inline int bin_of_read(int R) { const int K = rows_per_lane(R); return K ? bin_of(K, (R - 1) % K) : -1; }
+inline void bin_shape(int bin, int &K, int &KL) { K = 1; while (bin_of(K + 1, 0) <= bin) ++K; KL = bin - bin_of(K, 0); }
 
-// Launchers (kernels.cu). All asynchronous on `st`; return the cudaError of the launch.
+enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3 };
+
+// Launchers. All asynchronous on `st`; return the cudaError of the launch.
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,
                              uint32_t n_haps, uint32_t *hapw, cudaStream_t st);
-cudaError_t launch_forward_float(int K, bool exact, const KernelArgs &a, int grid_blocks, cudaStream_t st);
-cudaError_t launch_forward_double(int K, const KernelArgs &a, int grid_blocks, cudaStream_t st);
+cudaError_t launch_forward(Variant v, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
-int forward_blocks_per_sm(int K, bool is_double, bool exact);
+int forward_blocks_per_sm(Variant v, int K, int KL);
 
 }  // namespace phmm

@@ -282,7 +282,8 @@ def edge_cases(seed=1234):
     """ragged edge-case batch: R in {1,2,15,...,255}, H in {1..700} incl. R>H, N bases, lower-case and
     junk bytes (behave as 'A'), quals with the high bit set, per-base gcp != 10, quals 0/6/93/127."""
     rng = np.random.default_rng(seed)
-    Rs = [1, 2, 15, 16, 17, 31, 32, 33, 48, 63, 64, 65, 95, 96, 127, 128, 150, 151, 159, 160, 161, 191, 192, 223, 224, 250, 255]
+    Rs = [1, 2, 15, 16, 17, 31, 32, 33, 48, 63, 64, 65, 95, 96, 97, 127, 128, 129, 150, 151, 159, 160, 161, 191, 192,
+          193, 223, 224, 225, 250, 255, 256]
     rb, bq, iq, dq, gc, rl, hb, hl, rrs, rhs = [], [], [], [], [], [], [], [], [0], [0]
     for gi, R in enumerate(Rs):
         nh = 4

@@ -89,7 +89,7 @@ typedef struct pairhmm_cuda_config {
     int32_t dedup_reads;     /* 1 = de-duplicate identical reads per region (VLPH.cpp:83-103)       */
     int32_t pack_threads;    /* host threads used to pack a batch (0 = auto)                        */
     int64_t chunk_cells;     /* target DP cells per internal launch group (0 = default)             */
-    int32_t reserved[8];
+    int32_t reserved[8];     /* [0] != 0: never use the uniform-gcp kernels (testing)                */
 } pairhmm_cuda_config;
 
 typedef struct pairhmm_cuda_stats {

@@ -62,6 +62,44 @@ def test_exact_mode_is_bit_identical_to_the_unfused_oracle(oracle):
         e.close()
 
 
+def test_uniform_gcp_kernels_equal_general_kernels():
+    """the constant-bank (uniform gcp) kernels do the same FMAs as the per-row-register kernels"""
+    b = synth.config2(5)
+    assert b.gcp.min() == b.gcp.max() == 10
+    raws = []
+    for force_general in (False, True):
+        e = fgdp_b200.Engine(force_general=force_general, dedup_reads=False)
+        try:
+            e.resident_load(b); e.resident_run()
+            raws.append(e.resident_fetch_raw())
+        finally:
+            e.close()
+    assert np.array_equal(raws[0].view(np.uint32), raws[1].view(np.uint32))
+
+
+def test_every_bin(engine, oracle):
+    """one region per read length 1..256: every (rows-per-lane, last-row slot) kernel instantiation runs,
+    on the uniform-gcp path (gcp == 10 everywhere) and, with gcp perturbed, on the general path"""
+    rng = np.random.default_rng(77)
+    for perturb in (False, True):
+        lens = np.arange(1, 257)
+        hls = [np.array([max(1, int(R * 1.3) + 7), 40]) for R in lens]
+        parts = [synth.make_batch(1000 + int(R), [2], [hl], int(R), "clean", foreign_frac=0.5) for R, hl in zip(lens, hls)]
+        b = parts[0].__class__(*[np.concatenate([getattr(p, f) for p in parts]) for f in
+                                 ("read_bases", "base_q", "ins_q", "del_q", "gcp")],
+                               None, np.concatenate([p.read_len for p in parts]),
+                               np.concatenate([p.hap_bases for p in parts]), None,
+                               np.concatenate([p.hap_len for p in parts]),
+                               np.arange(0, 2 * len(parts) + 1, 2, dtype=np.int64),
+                               np.arange(0, 2 * len(parts) + 1, 2, dtype=np.int64), "allbins")
+        b.read_off = synth._offsets(b.read_len); b.hap_off = synth._offsets(b.hap_len)
+        if perturb:
+            b.gcp = b.gcp.copy(); b.gcp[rng.random(b.gcp.shape[0]) < 0.3] = 7
+        want, wresc, _ = oracle.compute(b.as_flat(), threads=8)
+        got, gresc = engine.compute_batch(b)
+        assert_parity(got, gresc, want, wresc, what="all bins, perturb=%s" % perturb)
+
+
 def test_config3_rescue_heavy(engine, oracle):
     b = synth.config3(200, 8)
     want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
@@ -148,7 +186,7 @@ def test_empty_and_errors(engine):
         engine.initialize(10, 0)
     r = tuple(np.full(300, v, np.uint8) for v in (65, 30, 45, 45, 10))
     with pytest.raises(fgdp_b200.PairHMMError):
-        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 255 rows: refused loudly, not faked
+        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 256 rows: refused loudly, not faked
     z = tuple(np.zeros(0, np.uint8) for _ in range(5))
     out, resc = engine.compute([z], [np.frombuffer(b"ACGT", np.uint8)])
     assert np.isneginf(out).all() and resc.all()
