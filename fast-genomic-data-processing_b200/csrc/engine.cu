@@ -182,6 +182,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     uint32_t g = (uint32_t)std::max(1, rv.n_haps);
     const uint32_t cap_cols = 16384u / (uint32_t)(hmax + 1);
     g = std::min(g, std::max(1u, cap_cols));
+    g = std::min(g, (uint32_t)kMaxUnitHaps);
     if (group_hint) g = std::min(g, group_hint);
     pl.group = g;
     pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;

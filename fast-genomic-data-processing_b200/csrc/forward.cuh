@@ -73,8 +73,19 @@ __device__ __forceinline__ uint32_t tw_or(const uint32_t &t) { return t; }
 __device__ __forceinline__ uint32_t tw_or(const uint2 &t) { return t.x | t.y; }
 __device__ __forceinline__ uint32_t tw_or(const uint4 &t) { return t.x | t.y | t.z | t.w; }
 
+// per-warp table of the unit's haplotypes (first tile, 2^s/H), filled once per unit so that the SEP
+// handler -- which runs divergently, one lane at a time -- needs no global loads and no division
+template <typename T> struct HapInfo { uint32_t tix; T initY; };
+
+// minimum resident CTAs per SM requested from ptxas (caps registers): the FP32 kernels are issue-bound
+// and want >= 5-6 warps per scheduler; the FP64 kernels need their registers
+#ifndef PHMM_MINB_F32
+#define PHMM_MINB_F32 6
+#endif
+#define PHMM_MINB(T, K) ((sizeof(T) == 4 && (K) <= 5) ? PHMM_MINB_F32 : 1)
+
 template <typename T, int K, int KL, bool EXACT, bool UG>
-__global__ void __launch_bounds__(kThreads) forward_kernel(const KernelArgs a) {
+__global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(const KernelArgs a) {
     static_assert(KL >= 0 && KL < K, "last-row slot out of range");
     static_assert(!(EXACT && UG), "the exact mode uses the general path");
     using N = Num<T>;
@@ -90,6 +101,8 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(const KernelArgs a) {
     const T *__restrict__ mmt = static_cast<const T *>(a.mm);
     const Tile *__restrict__ tiles = reinterpret_cast<const Tile *>(a.hapw);
     const uint32_t n_units = a.n_units_dev ? *a.n_units_dev : a.n_units;
+    __shared__ HapInfo<T> hap_info_all[kThreads / 32][kMaxUnitHaps];
+    HapInfo<T> *hap_info = hap_info_all[threadIdx.x >> 5];
 
     for (;;) {
         uint32_t u = 0;
@@ -141,9 +154,15 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(const KernelArgs a) {
 #define NXX      (UG ? N::uxy(a) : nXXr)
 #define NGAPM    (UG ? N::ugapm(a) : nGAPMr)
 
-        // pipeline steps: 32 (fill) + sum over haplotypes of their tile count
+        // pipeline steps: 32 (fill) + sum over haplotypes of their tile count; hap table for the SEP handler
         int steps = 0;
-        for (uint32_t i = lane; i < unit.nh; i += 32) steps += a.haps[a.hap_list[unit.hap_list + i]].len / C + 1;
+        __syncwarp();                                  // previous unit's readers are done with hap_info
+        if (lane < unit.nh) {                          // unit.nh <= kMaxUnitHaps == 32 (host guarantees)
+            const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
+            steps = hp.len / C + 1;
+            hap_info[lane] = HapInfo<T>{hp.off / C, N::div(N::init_const(), (T)hp.len)};   // template.h:115
+        }
+        __syncwarp();
 #pragma unroll
         for (int o = 16; o; o >>= 1) steps += __shfl_xor_sync(kFull, steps, o);
         steps += 32;
@@ -230,13 +249,8 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(const KernelArgs a) {
                 ++cur;
                 sumM = sumX = (T)0;
                 T initY = (T)0;
-                if ((uint32_t)cur < unit.nh) {
-                    const DevHap h = a.haps[a.hap_list[unit.hap_list + cur]];
-                    next_tix = h.off / C;
-                    initY = N::div(N::init_const(), (T)h.len);                   // template.h:115
-                } else {
-                    next_tix = 32;                                                // drain PAD tiles
-                }
+                next_tix = 32;                                                    // drain PAD tiles
+                if ((uint32_t)cur < unit.nh) { const HapInfo<T> hi = hap_info[cur]; next_tix = hi.tix; initY = hi.initY; }
                 // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
                 Dbound = N::template mul<EXACT>(initY, PGAPM(0));
                 if (lane0) Din[C - 1] = Dbound;        // becomes Dprev of the next step's first column

@@ -27,7 +27,11 @@ struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t nh; uint
 
 constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
 constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next haplotype
-constexpr int kTile = 2;                     // columns a lane advances per pipeline step
+#ifndef PHMM_TILE
+#define PHMM_TILE 2
+#endif
+constexpr int kTile = PHMM_TILE;             // columns a lane advances per pipeline step
+constexpr int kMaxUnitHaps = 32;             // haplotypes streamed by one work unit (one per lane in the per-warp table)
 constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1] SEP, rest PAD
 constexpr int kMaxRowsPerLane = 8;           // K; one warp covers reads up to 32*K-1 rows
 constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition

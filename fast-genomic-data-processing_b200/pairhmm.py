@@ -63,7 +63,8 @@ class PhmmRegion(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libpairhmm_cuda.so")
+    # PAIRHMM_CUDA_LIB selects another build of the same library (kernel-variant experiments)
+    return os.environ.get("PAIRHMM_CUDA_LIB") or os.path.join(_HERE, "libpairhmm_cuda.so")
 
 
 _LIB = None
