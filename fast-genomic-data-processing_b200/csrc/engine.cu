@@ -41,7 +41,7 @@ template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; 
 
 void Slot::release() {
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
-    h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release();
+    h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release(); h_rescue_base.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
     d_rescue.release(); d_fres.release(); d_out.release();
@@ -77,8 +77,11 @@ int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
 
 // counters layout in d_counters, one word per (K,KL) bin each: work queues of the FP32 launches,
 // rescue counts, work queues of the FP64 launches
-constexpr int kCounterWords = 3 * kNumBins + 4;
-constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = 2 * kNumBins;
+// (zeroed per run), then the device copy of Slot::rescue_base
+constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32;
+constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32;
+constexpr int kRescueBaseDev = kZeroedWords;
+constexpr int kCounterWords = kZeroedWords + kNumBinsW32 + 4;
 
 // Runs fn(i) for i in [0,n) on up to `threads` std::threads (dynamic chunks of `grain`).
 template <class F> void parallel_for(size_t n, int threads, size_t grain, F fn) {
@@ -152,7 +155,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || !r.ins_q || !r.del_q || !r.gcp)))
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
-        if (rows_per_lane(r.len) == 0)
+        if (bin_of_read(r.len, 32) < 0)
             return fail(h, PAIRHMM_ERR_ARG, "read longer than 256 bases: not supported by this build");
         uint32_t u = kNoRead;
         if (!table.empty()) {
@@ -186,9 +189,49 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     if (group_hint) g = std::min(g, group_hint);
     pl.group = g;
     pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;
-    for (uint32_t j = 0; j < pl.n_uniq; ++j)
-        pl.unit_count[bin_of_read(rv.reads[pl.uniq_src[j]].len)] += pl.n_groups;
     return PAIRHMM_OK;
+}
+
+// Lane-group width for a read of length R under the given FP32 variant. Narrow groups (more rows per
+// lane) exist for the uniform-gcp kernels only; forced_w (config.reserved[1]) overrides the choice.
+int choose_width(int R, Variant v, int forced_w) {
+    if (v != Variant::F32_UG) return 32;
+    if (forced_w && bin_of_read(R, forced_w) >= 0) return forced_w;
+    // measured on B200 (C2, R = 150): W=32 2.00, W=16 2.32, W=8 2.56 TCUPS -- the narrowest group that fits wins
+    if (bin_of_read(R, 8) >= 0) return 8;
+    if (bin_of_read(R, 16) >= 0) return 16;
+    return 32;
+}
+
+// Pass A2 for one region, once the chunk's kernel variant is known: order the unique reads by kernel bin
+// (stable, so equal-length reads keep their input order) and form the bin runs.
+void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w) {
+    const uint32_t n = pl.n_uniq;
+    std::vector<uint16_t> bin(n);
+    for (uint32_t j = 0; j < n; ++j) {
+        const int R = rv.reads[pl.uniq_src[j]].len;
+        bin[j] = (uint16_t)bin_of_read(R, choose_width(R, v, forced_w));
+        pl.pairs32[bin_of_read(R, 32)] += (uint32_t)rv.n_haps;
+    }
+    std::vector<uint32_t> order(n), inv(n);
+    for (uint32_t j = 0; j < n; ++j) order[j] = j;
+    bool sorted = true;
+    for (uint32_t j = 1; j < n && sorted; ++j) sorted = bin[j - 1] <= bin[j];
+    if (!sorted) {
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return bin[a] < bin[b]; });
+        std::vector<uint32_t> src(n);
+        for (uint32_t j = 0; j < n; ++j) { src[j] = pl.uniq_src[order[j]]; inv[order[j]] = j; }
+        pl.uniq_src.swap(src);
+        for (auto &u : pl.uniq_of_read) if (u != kNoRead) u = inv[u];
+    }
+    pl.runs.clear();
+    for (uint32_t j = 0; j < n;) {
+        const uint16_t b = bin[order[j]];
+        uint32_t e = j;
+        while (e < n && bin[order[e]] == b) ++e;
+        pl.runs.push_back(RegionPlan::BinRun{b, j, e - j, 0});
+        j = e;
+    }
 }
 
 }  // namespace
@@ -220,21 +263,34 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     });
     if (status.load() != PAIRHMM_OK) return status.load();
 
+    // kernel variant of the chunk: uniform gap-continuation penalty -> constant-bank kernels
+    uint8_t gmin = 255, gmax = 0;
+    for (size_t i = 0; i < n_regs; ++i) { gmin = std::min(gmin, s.plans[i].gcp_min); gmax = std::max(gmax, s.plans[i].gcp_max); }
+    s.uniform_gcp = gmin == gmax;
+    s.gcp_value = gmin;
+    s.float_variant = (h->cfg.use_double || h->cfg.exact_fp32) ? (h->cfg.exact_fp32 ? Variant::F32_EXACT : Variant::F32_GEN)
+                      : (s.uniform_gcp && !h->cfg.reserved[0]) ? Variant::F32_UG : Variant::F32_GEN;
+    const int forced_w = h->cfg.reserved[1];
+    parallel_for(n_regs, threads, 8, [&](size_t i) { bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w); });
+
     // prefix sums
     uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0;
     uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
-    uint32_t bin_count[kNumBins] = {0};
-    uint32_t bin_pairs[kNumBins] = {0};
-    uint8_t gmin = 255, gmax = 0;
+    std::vector<uint32_t> bin_count(kNumBins, 0);
+    uint32_t bin_pairs[kNumBinsW32] = {0};
     for (size_t i = 0; i < n_regs; ++i) {
         RegionPlan &p = s.plans[i];
         p.first_uniq = nu; p.read_byte_off = rbytes; p.first_hap = nh; p.hap_byte_off = hbytes;
         p.hap_word_off = hw; p.hap_list_off = hl; p.upair_off = up;
-        gmin = std::min(gmin, p.gcp_min); gmax = std::max(gmax, p.gcp_max);
-        for (int k = 0; k < kNumBins; ++k) {
-            p.unit_off[k] = bin_count[k]; bin_count[k] += p.unit_count[k];
-            if (p.n_groups) bin_pairs[k] += p.unit_count[k] / p.n_groups * (uint32_t)s.regions[i].n_haps;
+        for (auto &run : p.runs) {
+            int W, K, KL; bin_shape(run.bin, W, K, KL);
+            const uint32_t per_warp = 32u / (uint32_t)W;
+            run.unit_off = bin_count[run.bin];
+            bin_count[run.bin] += (run.n_reads + per_warp - 1) / per_warp * p.n_groups;
         }
+        for (int k = 0; k < kNumBinsW32; ++k) bin_pairs[k] += p.pairs32[k];
+        if ((uint32_t)s.regions[i].n_haps > 0xffffu)
+            return fail(h, PAIRHMM_ERR_ARG, "more than 65535 haplotypes in one region");
         const uint64_t up_next = (uint64_t)up + (uint64_t)p.n_uniq * (uint64_t)s.regions[i].n_haps;
         if (up_next > 0xfffffff0ull || rbytes + p.read_bytes > 0xfffffff0ull || (uint64_t)hw + p.hap_words > 0xfffffff0ull)
             return fail(h, PAIRHMM_ERR_ARG, "chunk too large for 32-bit device indices (lower chunk_cells)");
@@ -248,12 +304,8 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     }
     s.bin_start[0] = 0;
     s.rescue_base[0] = 0;
-    s.uniform_gcp = gmin == gmax;     // also true for "no reads" (255,0 never equal -> false; harmless)
-    s.gcp_value = gmin;
-    for (int k = 0; k < kNumBins; ++k) {
-        s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
-        s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
-    }
+    for (int k = 0; k < kNumBins; ++k) s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
+    for (int k = 0; k < kNumBinsW32; ++k) s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
     const uint32_t n_units = s.bin_start[kNumBins];
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
@@ -263,6 +315,8 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 #define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
     RES(h_rd, s.plane * 5 + 16); RES(h_reads, nu + 1); RES(h_hapbytes, hbytes + 16); RES(h_hapoff, nh + 1);
     RES(h_haps, nh + 1); RES(h_haplist, hl + 1); RES(h_units, n_units + 1); RES(h_out, up + 1); RES(h_flag, up + 1);
+    RES(h_rescue_base, kNumBinsW32 + 1);
+    std::memcpy(s.h_rescue_base.p, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
     RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
     RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
     RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 2 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
@@ -273,7 +327,6 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         const RegionView &rv = s.regions[i];
         const RegionPlan &p = s.plans[i];
         uint64_t ro = p.read_byte_off;
-        uint32_t fill[kNumBins] = {0};
         for (uint32_t j = 0; j < p.n_uniq; ++j) {
             const phmm_read &r = rv.reads[p.uniq_src[j]];
             uint8_t *d = s.h_rd.p + ro;
@@ -282,14 +335,22 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             std::memcpy(d + 4 * s.plane, r.gcp, r.len);
             s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
             ro += (uint64_t)r.len;
-            const int k = bin_of_read(r.len);
-            DevUnit *ud = s.h_units.p + s.bin_start[k] + p.unit_off[k] + fill[k];
-            for (uint32_t g = 0; g < p.n_groups; ++g) {
-                const uint32_t h0 = g * p.group;
-                ud[g] = DevUnit{p.first_uniq + j, p.hap_list_off + h0, std::min(p.group, (uint32_t)rv.n_haps - h0),
-                                p.upair_off + j * (uint32_t)rv.n_haps + h0};
+        }
+        // work units: per bin run, 32/W consecutive reads per warp, one unit per haplotype group
+        const uint32_t nhap = (uint32_t)rv.n_haps;
+        for (const auto &run : p.runs) {
+            int W, K, KL; bin_shape(run.bin, W, K, KL);
+            const uint32_t per_warp = 32u / (uint32_t)W;
+            DevUnit *ud = s.h_units.p + s.bin_start[run.bin] + run.unit_off;
+            for (uint32_t j = 0; j < run.n_reads; j += per_warp) {
+                const uint32_t nr = std::min(per_warp, run.n_reads - j), first = run.first + j;
+                for (uint32_t g = 0; g < p.n_groups; ++g) {
+                    const uint32_t h0 = g * p.group;
+                    *ud++ = DevUnit{p.first_uniq + first, p.hap_list_off + h0,
+                                    unit_shape(std::min(p.group, nhap - h0), nr, nhap),
+                                    p.upair_off + first * nhap + h0};
+                }
             }
-            fill[k] += p.n_groups;
         }
         uint64_t ho = p.hap_byte_off;
         uint32_t wo = p.hap_word_off;
@@ -329,10 +390,18 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     return PAIRHMM_OK;
 }
 
-// FP32 pass per (K,KL) bin -> finalize -> FP64 rescue per bin. Asynchronous on the slot's stream.
+// FP32 pass per (W,K,KL) bin -> finalize -> FP64 rescue per W=32 bin. Asynchronous on the slot's stream.
+static int blocks_for(pairhmm_cuda_handle *h, Variant v, int bin) {
+    int &n = h->blocks_per_sm[(int)v][bin];
+    if (n == 0) { int W, K, KL; bin_shape(bin, W, K, KL); n = std::max(1, forward_blocks_per_sm(v, W, K, KL)); }
+    return n;
+}
+
 int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
-    CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kCounterWords, st));
+    CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kZeroedWords, st));
+    CU(h, cudaMemcpyAsync(s.d_counters.p + kRescueBaseDev, s.h_rescue_base.p, sizeof(uint32_t) * (kNumBinsW32 + 1),
+                          cudaMemcpyHostToDevice, st));
     CU(h, cudaEventRecord(s.ev_begin, st));
     const HostTables &t = host_tables();
     KernelArgs a{};
@@ -344,25 +413,23 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     a.u_xy_f = t.ph2pr_f[gc]; a.u_gapm_f = 1.0f - t.ph2pr_f[gc];
     a.u_xy_d = t.ph2pr_d[gc]; a.u_gapm_d = 1.0 - t.ph2pr_d[gc];
     const bool all_double = h->cfg.use_double != 0;
-    const Variant vf = h->cfg.exact_fp32 ? Variant::F32_EXACT
-                       : (s.uniform_gcp && !h->cfg.reserved[0]) ? Variant::F32_UG : Variant::F32_GEN;
-    const Variant vd = Variant::F64_GEN;
-    auto grid_for = [&](Variant v, int K, uint64_t work_items) {
-        const uint64_t full = (uint64_t)h->sm_count * (uint64_t)std::max(1, h->blocks_per_sm[(int)v][K]);
+    const Variant vf = s.float_variant, vd = Variant::F64_GEN;
+    auto grid_for = [&](Variant v, int bin, uint64_t work_items) {
+        const uint64_t full = (uint64_t)h->sm_count * (uint64_t)blocks_for(h, v, bin);
         return (int)std::min<uint64_t>(full, (work_items + 3) / 4);
     };
     if (!all_double) {
+        a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
+        a.rescue_units = s.d_rescue.p;
+        a.rescue_base = s.d_counters.p + kRescueBaseDev;
+        a.rescue_count = s.d_counters.p + kRescueCount;
         for (int b = 0; b < kNumBins; ++b) {
             const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
             if (!n) continue;
-            int K, KL; bin_shape(b, K, KL);
+            int W, K, KL; bin_shape(b, W, K, KL);
             a.units = s.d_units.p + s.bin_start[b]; a.n_units = n; a.n_units_dev = nullptr;
             a.queue = s.d_counters.p + kQueueF + b;
-            a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
-            // every bin appends to its own slice of d_rescue (at most one entry per unique pair)
-            a.rescue_units = s.d_rescue.p + s.rescue_base[b];
-            a.rescue_count = s.d_counters.p + kRescueCount + b;
-            CU(h, launch_forward(vf, K, KL, a, grid_for(vf, K, n), st));
+            CU(h, launch_forward(vf, W, K, KL, a, grid_for(vf, b, n), st));
             h->stats.kernel_launches += 1;
         }
         FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f};
@@ -370,25 +437,26 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         if (s.n_upairs) h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_float_done, st));
-    for (int b = 0; b < kNumBins; ++b) {
-        const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
-        if (!n) continue;
-        int K, KL; bin_shape(b, K, KL);
+    a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
+    a.rescue_units = nullptr; a.rescue_base = nullptr; a.rescue_count = nullptr;
+    for (int b = 0; b < kNumBinsW32; ++b) {
+        int W, K, KL; bin_shape(b, W, K, KL);
         a.queue = s.d_counters.p + kQueueD + b;
-        a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
-        a.rescue_units = nullptr; a.rescue_count = nullptr;
         int grid;
-        if (all_double) {
+        if (all_double) {      // every unit straight to the FP64 kernels (the chunk was binned at W = 32)
+            const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
+            if (!n) continue;
             a.units = s.d_units.p + s.bin_start[b]; a.n_units = n; a.n_units_dev = nullptr;
-            grid = grid_for(vd, K, n);
+            grid = grid_for(vd, b, n);
         } else {
             // the rescue count is only known on the device: a persistent grid bounded by the bin's pairs
+            const uint64_t cap = (uint64_t)s.rescue_base[b + 1] - s.rescue_base[b];
+            if (!cap) continue;
             a.units = s.d_rescue.p + s.rescue_base[b]; a.n_units = 0;
             a.n_units_dev = s.d_counters.p + kRescueCount + b;
-            grid = grid_for(vd, K, (uint64_t)s.rescue_base[b + 1] - s.rescue_base[b]);
-            if (grid < 1) continue;
+            grid = grid_for(vd, b, cap);
         }
-        CU(h, launch_forward(vd, K, KL, a, grid, st));
+        CU(h, launch_forward(vd, W, K, KL, a, grid, st));
         h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_end, st));
@@ -532,11 +600,7 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
             cudaEventCreate(&s.ev_end) != cudaSuccess || s.d_counters.reserve(kCounterWords) != cudaSuccess)
             return bail(PAIRHMM_ERR_CUDA);
     }
-    for (int v = 0; v < 4; ++v)
-        for (int k = 1; k <= kMaxRowsPerLane; ++k) {
-            h->blocks_per_sm[v][k] = forward_blocks_per_sm((Variant)v, k, k - 1);
-            if (h->blocks_per_sm[v][k] < 1) return bail(PAIRHMM_ERR_CUDA);
-        }
+    if (forward_blocks_per_sm(Variant::F32_GEN, 32, 1, 0) < 1) return bail(PAIRHMM_ERR_CUDA);   // kernels loadable?
     *out = h;
     return PAIRHMM_OK;
 }
@@ -825,16 +889,27 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
     return st;
 }
 
-// Raw FP32-pass sums (2^120-scaled, before log10) per UNIQUE pair, in region-major / unique-read-major
-// order (= pair order when no read is duplicated). For bit-exactness tests of the FP32 kernel.
+// Raw FP32-pass sums (2^120-scaled, before log10) of the last _resident_run for every input pair, in the
+// same order as the results (region-major, read-major). For bit-exactness tests of the FP32 kernel.
 int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n) {
     if (!h || !fres_out) return PAIRHMM_ERR_ARG;
     if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch_raw: nothing loaded");
     Slot &s = h->slots[0];
-    if (n != (int64_t)s.n_upairs) return fail(h, PAIRHMM_ERR_ARG, "resident_fetch_raw: n != unique pairs");
+    if (n != (int64_t)s.pairs) return fail(h, PAIRHMM_ERR_ARG, "resident_fetch_raw: n != number of pairs");
     CU(h, cudaSetDevice(h->device));
-    CU(h, cudaMemcpyAsync(fres_out, s.d_fres.p, sizeof(float) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
+    std::vector<float> tmp(s.n_upairs);
+    CU(h, cudaMemcpyAsync(tmp.data(), s.d_fres.p, sizeof(float) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
     CU(h, cudaStreamSynchronize(s.stream));
+    size_t off = 0;
+    for (size_t i = 0; i < s.regions.size(); ++i) {
+        const RegionView &rv = s.regions[i];
+        const RegionPlan &p = s.plans[i];
+        const size_t nh = (size_t)rv.n_haps;
+        for (int r = 0; r < rv.n_reads; ++r, off += nh) {
+            const uint32_t u = p.uniq_of_read[r];
+            for (size_t q = 0; q < nh; ++q) fres_out[off + q] = (u == kNoRead) ? 0.f : tmp[(size_t)p.upair_off + (size_t)u * nh + q];
+        }
+    }
     return PAIRHMM_OK;
 }
 

@@ -42,8 +42,10 @@ struct RegionPlan {
     uint32_t hap_list_off = 0;
     uint32_t group = 0, n_groups = 0;   // haplotypes per work unit / units per read
     uint32_t upair_off = 0;         // first unique-pair index
-    uint32_t unit_count[kNumBins] = {0};   // work units per (K,KL) bin
-    uint32_t unit_off[kNumBins] = {0};
+    // unique reads are ordered by kernel bin; a run = the reads of one (W,K,KL) bin
+    struct BinRun { uint16_t bin; uint32_t first, n_reads, unit_off; };
+    std::vector<BinRun> runs;
+    uint32_t pairs32[kNumBinsW32] = {0};   // unique pairs per W=32 bin (bounds that bin's FP64 rescue list)
     uint8_t gcp_min = 255, gcp_max = 0;    // range of the (masked) gap-continuation bytes of the unique reads
     std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
     std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
@@ -77,7 +79,9 @@ struct Slot {
     uint32_t n_uniq = 0, n_haps = 0, n_hap_words = 0, n_haplist = 0, n_upairs = 0;
     uint64_t hap_bytes = 0;
     uint32_t bin_start[kNumBins + 1] = {0};   // units of bin b are [bin_start[b], bin_start[b+1])
-    uint32_t rescue_base[kNumBins + 1] = {0}; // bin b appends its rescue units at d_rescue + rescue_base[b]
+    uint32_t rescue_base[kNumBinsW32 + 1] = {0}; // W=32 bin b appends its rescue units at d_rescue + rescue_base[b]
+    PinnedBuf<uint32_t> h_rescue_base;        // the same, staged for the device
+    Variant float_variant = Variant::F32_GEN; // kernels this chunk was binned for
     bool uniform_gcp = false;                 // every gcp byte of the chunk equals gcp_value -> UG kernels
     uint8_t gcp_value = 0;
     uint64_t cells = 0, pairs = 0, reads_in = 0;
@@ -98,7 +102,7 @@ struct pairhmm_cuda_handle {
     double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
     float log10_init_f = 0.f;
     double log10_init_d = 0.0;
-    int blocks_per_sm[4][phmm::kMaxRowsPerLane + 1] = {{0}};   // [Variant][K]
+    int blocks_per_sm[4][phmm::kNumBins] = {{0}};   // [Variant][bin], 0 = not queried yet
     int read_max_len = 0, hap_max_len = 0;
     phmm::Slot slots[2];
     int64_t next_ticket = 1;

@@ -1,10 +1,12 @@
 // PairHMM forward kernel template for sm_100a (no tensor cores: the M/X/Y recurrence is a wavefront).
 //
 // Work decomposition: one WARP sweeps one work unit = one read against a run of haplotypes.
-//   * lane l owns K consecutive rows of the DP matrix (read rows l*K .. l*K+K-1, top-aligned); rows past
-//     the end of the read are dead slots (all constants 0). The read's last row is slot KL of lane
-//     (R-1)/K; KL is a template parameter so that the two running sums of the last row stay in fixed
-//     registers.
+//   * a group of W lanes (W = 32, 16, 8; 32/W reads per warp, all against the same haplotype run)
+//     sweeps one read: lane l of the group owns K consecutive rows of the DP matrix (read rows l*K ..
+//     l*K+K-1, top-aligned); rows past the end of the read are dead slots (all constants 0). The read's
+//     last row is slot KL of lane (R-1)/K; KL is a template parameter so that the two running sums of
+//     the last row stay in fixed registers. Narrower groups = more rows per lane = the per-column
+//     overhead (2 shuffles, boundary selects, loop, loads) is amortised over more cells.
 //   * lanes are skewed by one tile (kTile columns): at step t lane l works on tile t-l of the unit's
 //     column stream. The only cross-lane traffic per column is two shuffles: the bottom row of lane l,
 //     pre-combined with the transition constants of the row below it (D = diagonal term of M, U = the
@@ -82,10 +84,11 @@ template <typename T> struct HapInfo { uint32_t tix; T initY; };
 #ifndef PHMM_MINB_F32
 #define PHMM_MINB_F32 6
 #endif
-#define PHMM_MINB(T, K) ((sizeof(T) == 4 && (K) <= 5) ? PHMM_MINB_F32 : 1)
+#define PHMM_MINB(T, W, K) ((sizeof(T) == 4 && (W) == 32 && (K) <= 5) ? PHMM_MINB_F32 : 1)
 
-template <typename T, int K, int KL, bool EXACT, bool UG>
-__global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(const KernelArgs a) {
+template <typename T, int W, int K, int KL, bool EXACT, bool UG>
+__global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(const KernelArgs a) {
+    static_assert(W == 32 || W == 16 || W == 8, "lane-group width");
     static_assert(KL >= 0 && KL < K, "last-row slot out of range");
     static_assert(!(EXACT && UG), "the exact mode uses the general path");
     using N = Num<T>;
@@ -96,7 +99,9 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
     constexpr int FIELD = code_field(K);
     constexpr int KR = UG ? 1 : K;              // per-row pXY/pGAPM registers only on the general path
     const int lane = threadIdx.x & 31;
-    const bool lane0 = lane == 0;
+    const int sl = lane & (W - 1);              // lane inside its group
+    const int seg = lane / W;                   // which of the warp's 32/W reads
+    const bool lane0 = sl == 0;
     const T *__restrict__ ph = static_cast<const T *>(a.ph2pr);
     const T *__restrict__ mmt = static_cast<const T *>(a.mm);
     const Tile *__restrict__ tiles = reinterpret_cast<const Tile *>(a.hapw);
@@ -106,11 +111,15 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
 
     for (;;) {
         uint32_t u = 0;
-        if (lane0) u = atomicAdd(a.queue, 1u);
+        if (lane == 0) u = atomicAdd(a.queue, 1u);
         u = __shfl_sync(kFull, u, 0);
         if (u >= n_units) break;
         const DevUnit unit = a.units[u];
-        const DevRead rr = a.reads[unit.read];
+        const uint32_t unit_nh = unit.shape & 0xffu, unit_nreads = (unit.shape >> 8) & 0xffu;
+        const bool seg_valid = (uint32_t)seg < unit_nreads;   // a partial unit leaves groups without a read: they
+        const uint32_t my_read = unit.read + (seg_valid ? seg : 0);   // recompute read 0 and emit nothing
+        const uint32_t my_out = unit.out + (uint32_t)seg * (unit.shape >> 16);
+        const DevRead rr = a.reads[my_read];
         const int last_lane = (rr.len - 1) / K;       // owns the read's last row, in slot KL
 
         // ---- per-slot constants (ReadForPairHMM.cpp:72-80; stripeINITIALIZATION template.h:150-152)
@@ -120,7 +129,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
         for (int i = 0; i < NG; ++i) mask[i] = 0;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            const int g = lane * K + k;               // 0-based read row
+            const int g = sl * K + k;                 // 0-based read row
             if (g < rr.len) {
                 const uint8_t *p = a.rd + rr.off + g;
                 const uint32_t rb = base_index(p[0]);
@@ -144,20 +153,20 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
             }
         }
         // transition constants of the row below this lane's last slot (= slot 0 of lane+1; 0 past lane 31)
-        T nMM = __shfl_down_sync(kFull, pMM[0], 1), nMX = __shfl_down_sync(kFull, pMX[0], 1);
+        T nMM = __shfl_down_sync(kFull, pMM[0], 1, W), nMX = __shfl_down_sync(kFull, pMX[0], 1, W);
         T nXXr = (T)0, nGAPMr = (T)0;
-        if constexpr (!UG) { nXXr = __shfl_down_sync(kFull, pXYr[0], 1); nGAPMr = __shfl_down_sync(kFull, pGAPMr[0], 1); }
-        if (lane == 31) { nMM = nMX = nXXr = nGAPMr = (T)0; }
+        if constexpr (!UG) { nXXr = __shfl_down_sync(kFull, pXYr[0], 1, W); nGAPMr = __shfl_down_sync(kFull, pGAPMr[0], 1, W); }
+        if (sl == W - 1) { nMM = nMX = nXXr = nGAPMr = (T)0; }
         // gap-continuation constants: constant bank (UG) or this row's registers
 #define PXY(k)   (UG ? N::uxy(a) : pXYr[UG ? 0 : (k)])
 #define PGAPM(k) (UG ? N::ugapm(a) : pGAPMr[UG ? 0 : (k)])
 #define NXX      (UG ? N::uxy(a) : nXXr)
 #define NGAPM    (UG ? N::ugapm(a) : nGAPMr)
 
-        // pipeline steps: 32 (fill) + sum over haplotypes of their tile count; hap table for the SEP handler
+        // pipeline steps: W (fill) + sum over haplotypes of their tile count; hap table for the SEP handler
         int steps = 0;
         __syncwarp();                                  // previous unit's readers are done with hap_info
-        if (lane < unit.nh) {                          // unit.nh <= kMaxUnitHaps == 32 (host guarantees)
+        if ((uint32_t)lane < unit_nh) {                // nh <= kMaxUnitHaps == 32 (host guarantees)
             const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
             steps = hp.len / C + 1;
             hap_info[lane] = HapInfo<T>{hp.off / C, N::div(N::init_const(), (T)hp.len)};   // template.h:115
@@ -165,7 +174,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
         __syncwarp();
 #pragma unroll
         for (int o = 16; o; o >>= 1) steps += __shfl_xor_sync(kFull, steps, o);
-        steps += 32;
+        steps += W;
 
         T M[K], X[K], Y[K];
 #pragma unroll
@@ -175,7 +184,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
 #pragma unroll
         for (int j = 0; j < C; ++j) { Din[j] = Uin[j] = (T)0; }
         int cur = -1;
-        uint32_t tix = 31 - lane;                      // tile index: lane l sees l PAD tiles, then [PAD..,SEP]
+        uint32_t tix = 31 - sl;                        // tile index: lane l sees l PAD tiles, then [PAD..,SEP]
         Tile w = tiles[tix];
 
         // one DP column for this lane's K rows (computeMXY, template.h:177-192): Dd = diagonal term and
@@ -232,25 +241,28 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
         // flagged word: column 0 of a haplotype (SEP) or fill/drain/alignment (PAD)
         auto flagged = [&](uint32_t cw, uint32_t &next_tix) {
             if (!(cw & 0x40000000u)) {
-                if (lane == last_lane && (uint32_t)cur < unit.nh) {
+                if (sl == last_lane && seg_valid && (uint32_t)cur < unit_nh) {
                     const T r = N::template add<EXACT>(sumM, sumX);              // template.h:339-343
                     if constexpr (sizeof(T) == 4) {
-                        a.fres[unit.out + cur] = r;
+                        a.fres[my_out + cur] = r;
                         if (r < 1e-28f) {                                          // IntelPairHmm.cc:342
-                            const uint32_t slot = atomicAdd(a.rescue_count, 1u);
-                            a.rescue_units[slot] = DevUnit{unit.read, unit.hap_list + (uint32_t)cur, 1u,
-                                                           unit.out + (uint32_t)cur};
+                            // the FP64 kernels run at W = 32: queue the pair on that bin's list
+                            const int k32 = (rr.len + 31) >> 5;
+                            const int bin = k32 * (k32 - 1) / 2 + (rr.len - 1) % k32;
+                            const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
+                            a.rescue_units[slot] = DevUnit{my_read, unit.hap_list + (uint32_t)cur, unit_shape(1u, 1u, 0u),
+                                                           my_out + (uint32_t)cur};
                         }
                     } else {
-                        a.out[unit.out + cur] = log10(r) - a.log10_init_d;        // IntelPairHmm.cc:344
-                        a.flag[unit.out + cur] = 1;
+                        a.out[my_out + cur] = log10(r) - a.log10_init_d;          // IntelPairHmm.cc:344
+                        a.flag[my_out + cur] = 1;
                     }
                 }
                 ++cur;
                 sumM = sumX = (T)0;
                 T initY = (T)0;
                 next_tix = 32;                                                    // drain PAD tiles
-                if ((uint32_t)cur < unit.nh) { const HapInfo<T> hi = hap_info[cur]; next_tix = hi.tix; initY = hi.initY; }
+                if ((uint32_t)cur < unit_nh) { const HapInfo<T> hi = hap_info[cur]; next_tix = hi.tix; initY = hi.initY; }
                 // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
                 Dbound = N::template mul<EXACT>(initY, PGAPM(0));
                 if (lane0) Din[C - 1] = Dbound;        // becomes Dprev of the next step's first column
@@ -284,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, K)) forward_kernel(cons
             Dprev = Din[C - 1];   // D of the last column of the PREVIOUS exchange: diagonal of next step's first column
 #pragma unroll
             for (int j = 0; j < C; ++j) {
-                const T dn = __shfl_up_sync(kFull, Dout[j], 1), un = __shfl_up_sync(kFull, Uout[j], 1);
+                const T dn = __shfl_up_sync(kFull, Dout[j], 1, W), un = __shfl_up_sync(kFull, Uout[j], 1, W);
                 Din[j] = lane0 ? Dbound : dn;
                 Uin[j] = lane0 ? (T)0 : un;
             }

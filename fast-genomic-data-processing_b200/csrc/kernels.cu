@@ -48,33 +48,24 @@ cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off,
     return cudaGetLastError();
 }
 
-cudaError_t launch_f32_ug(int, int, const KernelArgs &, int, cudaStream_t);
-cudaError_t launch_f32_gen(int, int, const KernelArgs &, int, cudaStream_t);
-cudaError_t launch_f32_exact(int, int, const KernelArgs &, int, cudaStream_t);
-cudaError_t launch_f64_gen(int, int, const KernelArgs &, int, cudaStream_t);
-int blocks_per_sm_f32_ug(int, int);
-int blocks_per_sm_f32_gen(int, int);
-int blocks_per_sm_f32_exact(int, int);
-int blocks_per_sm_f64_gen(int, int);
+#include "inst_dispatch.inc"
 
-cudaError_t launch_forward(Variant v, int K, int KL, const KernelArgs &a, int grid, cudaStream_t st) {
-    switch (v) {
-        case Variant::F32_UG: return launch_f32_ug(K, KL, a, grid, st);
-        case Variant::F32_GEN: return launch_f32_gen(K, KL, a, grid, st);
-        case Variant::F32_EXACT: return launch_f32_exact(K, KL, a, grid, st);
-        case Variant::F64_GEN: return launch_f64_gen(K, KL, a, grid, st);
-    }
-    return cudaErrorInvalidValue;
+static const InstUnit *find_unit(Variant v, int W, int K) {
+    for (const InstUnit &u : kInstUnits)
+        if (u.v == v && u.W == W && K >= u.k0 && K <= u.k1) return &u;
+    return nullptr;
 }
 
-int forward_blocks_per_sm(Variant v, int K, int KL) {
-    switch (v) {
-        case Variant::F32_UG: return blocks_per_sm_f32_ug(K, KL);
-        case Variant::F32_GEN: return blocks_per_sm_f32_gen(K, KL);
-        case Variant::F32_EXACT: return blocks_per_sm_f32_exact(K, KL);
-        case Variant::F64_GEN: return blocks_per_sm_f64_gen(K, KL);
-    }
-    return 0;
+bool forward_available(Variant v, int W, int K) { return find_unit(v, W, K) != nullptr; }
+
+cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid, cudaStream_t st) {
+    const InstUnit *u = find_unit(v, W, K);
+    return u ? u->launch(K, KL, a, grid, st) : cudaErrorInvalidValue;
+}
+
+int forward_blocks_per_sm(Variant v, int W, int K, int KL) {
+    const InstUnit *u = find_unit(v, W, K);
+    return u ? u->blocks(K, KL) : 0;
 }
 
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st) {

@@ -23,7 +23,11 @@ namespace phmm {
 
 struct DevRead { uint32_t off; int32_t len; };
 struct DevHap  { uint32_t off; int32_t len; };
-struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t nh; uint32_t out; };
+// One warp task: `nreads` consecutive unique reads (one per lane group of W lanes) against the same run of
+// nh haplotypes. shape = nh | nreads << 8 | out_stride << 16; result of (read j, hap i) goes to
+// out + j*out_stride + i.
+struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t shape; uint32_t out; };
+inline __host__ __device__ uint32_t unit_shape(uint32_t nh, uint32_t nreads, uint32_t stride) { return nh | (nreads << 8) | (stride << 16); }
 
 constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
 constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next haplotype
@@ -33,7 +37,7 @@ constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next ha
 constexpr int kTile = PHMM_TILE;             // columns a lane advances per pipeline step
 constexpr int kMaxUnitHaps = 32;             // haplotypes streamed by one work unit (one per lane in the per-warp table)
 constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1] SEP, rest PAD
-constexpr int kMaxRowsPerLane = 8;           // K; one warp covers reads up to 32*K-1 rows
+constexpr int kMaxRowsPerLane = 8;           // K at W = 32: one warp covers reads up to 256 rows
 constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition
 
 // words a haplotype of length H occupies in hapw (code words + alignment PADs + SEP)
@@ -41,7 +45,7 @@ inline uint32_t hap_words(int32_t H) { return ((uint32_t)H / kTile + 1u) * kTile
 
 // match-mask geometry of a rows-per-lane bucket: rows are split into groups of kGroupBits(K) rows, each
 // group keeps 5 (one per haplotype base) bit fields of that width in one 32-bit register
-__host__ __device__ constexpr int group_bits(int K) { return K <= 6 ? K : 4; }
+__host__ __device__ constexpr int group_bits(int K) { return K <= 6 ? K : 6; }
 // bit position inside a code word of the field that holds b * group_bits(K)
 __host__ __device__ constexpr int code_field(int K) {
     return group_bits(K) == 5 ? 0 : group_bits(K) == 4 ? 5 : group_bits(K) == 6 ? 10
@@ -67,7 +71,8 @@ struct KernelArgs {
     double u_xy_d, u_gapm_d;
     // FP32 pass outputs
     float *fres;                  // scaled forward sum per unique pair
-    DevUnit *rescue_units;        // pairs with fres < 1e-28f, appended
+    DevUnit *rescue_units;        // pairs with fres < 1e-28f are appended to the list of the read's W=32 bin:
+    const uint32_t *rescue_base;  //   rescue_units[rescue_base[bin] + atomicAdd(&rescue_count[bin], 1)]
     uint32_t *rescue_count;
     // FP64 pass outputs
     double *out;                  // log10 likelihood
@@ -83,22 +88,46 @@ struct FinalizeArgs {
     float log10_init_f;           // log10f(2^120), host libm (Context.h:184)
 };
 
-// Work bins: a read of length R goes to rows-per-lane bucket K = ceil(R/32) (1..kMaxRowsPerLane) and
-// its last row lands in slot KL = (R-1) % K of lane (R-1)/K. One kernel instantiation per (K, KL).
-constexpr int kNumBins = kMaxRowsPerLane * (kMaxRowsPerLane + 1) / 2;    // 36
-inline int rows_per_lane(int R) { int k = (R + 31) / 32; return k <= kMaxRowsPerLane ? k : 0; }
-inline int bin_of(int K, int KL) { return K * (K - 1) / 2 + KL; }
-inline int bin_of_read(int R) { const int K = rows_per_lane(R); return K ? bin_of(K, (R - 1) % K) : -1; }
-inline void bin_shape(int bin, int &K, int &KL) { K = 1; while (bin_of(K + 1, 0) <= bin) ++K; KL = bin - bin_of(K, 0); }
+// Work bins. A read of length R is swept by a group of W lanes (W = 32, 16 or 8; 32/W reads per warp),
+// K = ceil(R/W) rows per lane, its last row in slot KL = (R-1) % K of lane (R-1)/K of the group. One kernel
+// instantiation per (W, K, KL). Narrow groups mean more rows per lane, i.e. the per-column overhead
+// (shuffles, boundary selects, loop) is amortised over more cells, at the price of registers.
+constexpr int kNumWidths = 3;
+constexpr int kWidths[kNumWidths] = {32, 16, 8};
+constexpr int kMaxK[kNumWidths] = {8, 16, 20};           // rows per lane limit per width
+constexpr int tri(int k) { return k * (k + 1) / 2; }
+constexpr int kBinBase[kNumWidths + 1] = {0, tri(8), tri(8) + tri(16), tri(8) + tri(16) + tri(20)};
+constexpr int kNumBins = kBinBase[kNumWidths];           // 36 + 136 + 210 = 382
+constexpr int kNumBinsW32 = kBinBase[1];
+
+inline int width_index(int W) { return W == 32 ? 0 : W == 16 ? 1 : W == 8 ? 2 : -1; }
+inline int bin_of(int W, int K, int KL) { return kBinBase[width_index(W)] + K * (K - 1) / 2 + KL; }
+// bin of a read at a given width, -1 if it does not fit
+inline int bin_of_read(int R, int W) {
+    const int wi = width_index(W);
+    const int K = (R + W - 1) / W;
+    return (wi < 0 || R < 1 || K > kMaxK[wi]) ? -1 : bin_of(W, K, (R - 1) % K);
+}
+inline void bin_shape(int bin, int &W, int &K, int &KL) {
+    int wi = 0;
+    while (wi + 1 < kNumWidths && bin >= kBinBase[wi + 1]) ++wi;
+    W = kWidths[wi];
+    const int r = bin - kBinBase[wi];
+    K = 1;
+    while (tri(K) <= r) ++K;
+    KL = r - tri(K - 1);
+}
 
 enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3 };
 
 // Launchers. All asynchronous on `st`; return the cudaError of the launch.
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,
                              uint32_t n_haps, uint32_t *hapw, cudaStream_t st);
-cudaError_t launch_forward(Variant v, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
+cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
-int forward_blocks_per_sm(Variant v, int K, int KL);
+int forward_blocks_per_sm(Variant v, int W, int K, int KL);
+// whether (variant, W, K) was instantiated (the general / exact / FP64 kernels exist at W = 32 only)
+bool forward_available(Variant v, int W, int K);
 
 }  // namespace phmm

@@ -130,13 +130,14 @@ class Engine:
     """One libpairhmm_cuda handle (one per host thread, like one PairHMM per Mutect2Cpp worker)."""
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
-                 chunk_cells=0, force_general=False):
+                 chunk_cells=0, force_general=False, lane_group=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
         cfg.device = device; cfg.use_double = int(use_double); cfg.exact_fp32 = int(exact_fp32)
         cfg.dedup_reads = int(dedup_reads); cfg.pack_threads = int(pack_threads); cfg.chunk_cells = int(chunk_cells)
         cfg.reserved[0] = int(force_general)   # never pick the uniform-gcp kernels (testing)
+        cfg.reserved[1] = int(lane_group)      # 8 | 16 | 32: force that lane-group width where it fits
         self.h = C.c_void_p()
         st = self.lib.pairhmm_cuda_create(C.byref(cfg), C.byref(self.h))
         if st != 0:

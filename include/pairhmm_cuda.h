@@ -89,7 +89,8 @@ typedef struct pairhmm_cuda_config {
     int32_t dedup_reads;     /* 1 = de-duplicate identical reads per region (VLPH.cpp:83-103)       */
     int32_t pack_threads;    /* host threads used to pack a batch (0 = auto)                        */
     int64_t chunk_cells;     /* target DP cells per internal launch group (0 = default)             */
-    int32_t reserved[8];     /* [0] != 0: never use the uniform-gcp kernels (testing)                */
+    int32_t reserved[8];     /* [0] != 0: never use the uniform-gcp kernels (testing);               */
+                             /* [1] = 8|16|32: force that lane-group width where it fits (tuning)    */
 } pairhmm_cuda_config;
 
 typedef struct pairhmm_cuda_stats {
@@ -158,9 +159,9 @@ int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases
                                int64_t n_regions);
 int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms);
 int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out);
-/* Raw FP32-pass sums (2^120-scaled, before log10) of the last _resident_run, one per UNIQUE (read,hap)
- * pair in region-major, unique-read-major order; n must equal the unique pair count. Test hook for
- * bit-exactness of the FP32 kernel against compute_full_prob_avxs (avx-pairhmm-template.h:204-345). */
+/* Raw FP32-pass sums (2^120-scaled, before log10) of the last _resident_run, one per input pair in result
+ * order; n must equal the pair count. Test hook for bit-exactness of the FP32 kernel against
+ * compute_full_prob_avxs (avx-pairhmm-template.h:204-345). */
 int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n);
 
 int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);

@@ -67,30 +67,34 @@ def test_uniform_gcp_kernels_equal_general_kernels():
     b = synth.config2(5)
     assert b.gcp.min() == b.gcp.max() == 10
     raws = []
-    for force_general in (False, True):
-        e = fgdp_b200.Engine(force_general=force_general, dedup_reads=False)
+    for force_general, lane_group in ((False, 32), (True, 32), (False, 16), (False, 8)):
+        e = fgdp_b200.Engine(force_general=force_general, dedup_reads=False, lane_group=lane_group)
         try:
             e.resident_load(b); e.resident_run()
             raws.append(e.resident_fetch_raw())
         finally:
             e.close()
-    assert np.array_equal(raws[0].view(np.uint32), raws[1].view(np.uint32))
+    for r in raws[1:]:
+        assert np.array_equal(raws[0].view(np.uint32), r.view(np.uint32))
 
 
-def test_every_bin(engine, oracle):
-    """one region per read length 1..256: every (rows-per-lane, last-row slot) kernel instantiation runs,
-    on the uniform-gcp path (gcp == 10 everywhere) and, with gcp perturbed, on the general path"""
+@pytest.mark.parametrize("lane_group", [0, 8, 16, 32])
+def test_every_bin(oracle, lane_group):
+    """one region per read length 1..256: every (lane-group width, rows-per-lane, last-row slot) kernel
+    instantiation runs, on the uniform-gcp path (gcp == 10 everywhere) and, with gcp perturbed, on the
+    general path"""
     rng = np.random.default_rng(77)
-    for perturb in (False, True):
+    engine = fgdp_b200.Engine(lane_group=lane_group)
+    for perturb in ((False, True) if lane_group in (0, 32) else (False,)):
         lens = np.arange(1, 257)
         hls = [np.array([max(1, int(R * 1.3) + 7), 40]) for R in lens]
-        parts = [synth.make_batch(1000 + int(R), [2], [hl], int(R), "clean", foreign_frac=0.5) for R, hl in zip(lens, hls)]
+        parts = [synth.make_batch(1000 + int(R), [5], [hl], int(R), "clean", foreign_frac=0.4) for R, hl in zip(lens, hls)]
         b = parts[0].__class__(*[np.concatenate([getattr(p, f) for p in parts]) for f in
                                  ("read_bases", "base_q", "ins_q", "del_q", "gcp")],
                                None, np.concatenate([p.read_len for p in parts]),
                                np.concatenate([p.hap_bases for p in parts]), None,
                                np.concatenate([p.hap_len for p in parts]),
-                               np.arange(0, 2 * len(parts) + 1, 2, dtype=np.int64),
+                               np.arange(0, 5 * len(parts) + 1, 5, dtype=np.int64),
                                np.arange(0, 2 * len(parts) + 1, 2, dtype=np.int64), "allbins")
         b.read_off = synth._offsets(b.read_len); b.hap_off = synth._offsets(b.hap_len)
         if perturb:
@@ -98,6 +102,7 @@ def test_every_bin(engine, oracle):
         want, wresc, _ = oracle.compute(b.as_flat(), threads=8)
         got, gresc = engine.compute_batch(b)
         assert_parity(got, gresc, want, wresc, what="all bins, perturb=%s" % perturb)
+    engine.close()
 
 
 def test_config3_rescue_heavy(engine, oracle):

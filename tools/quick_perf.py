@@ -9,12 +9,13 @@ which = sys.argv[1] if len(sys.argv) > 1 else "c2"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 400
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 exact = "--exact" in sys.argv
+lg = int(os.environ.get("LANE_GROUP", "0"))
 t = time.time()
 b = {"c1": lambda: synth.config1(), "c2": lambda: synth.config2(n), "c3": lambda: synth.config3(),
      "c4": lambda: synth.config4(), "c5": lambda: synth.config5(n)}[which]()
 cells = b.cells()
 print("gen %.1fs  %s pairs=%d cells=%.3g" % (time.time() - t, b.name, b.n_pairs, cells), flush=True)
-e = fgdp_b200.Engine(exact_fp32=exact)
+e = fgdp_b200.Engine(exact_fp32=exact, lane_group=lg)
 t = time.time(); e.resident_load(b); print("load %.2fs" % (time.time() - t), flush=True)
 res = []
 for i in range(reps):
