@@ -1,0 +1,280 @@
+#!/usr/bin/env python3
+"""PairHMM GCUPS benchmark (BASELINE.json metric) for the B200-native engine and for the reference CPU arm.
+
+  python bench.py --gpus N --steps K --warmup W             # this repo's CUDA engine
+  python bench.py --impl reference --gpus N --steps K ...    # the reference's own AVX PairHMM on the host cores
+
+A step = one pass of the hot path (FP32 forward -> <1e-28 -> FP64 rescue -> log10) over one batch of the
+synthetic WES-like workload (BASELINE.json configs[1]: 10k regions, ~200 reads x 4-16 haplotypes, 150 bp reads,
+250-500 bp haplotypes, ~2e7 pairs, ~1.1e12 DP cells). With N > 1 (torchrun, one rank per GPU) every rank owns
+its own shard of that size: pairs are independent, there is no collective on the data path (weak scaling);
+torch.distributed is used only for the barrier and the max-over-ranks of the device time.
+
+  value    : GCUPS with the batch resident in HBM (CUDA events around the kernels of every step)
+  e2e      : GCUPS through the C ABI from host arrays to host results (pack + H2D + kernels + D2H + scatter)
+  roofline : FP32 forward kernel against the FP32 FMA-pipe peak (8 pipe lane-ops per cell)
+  cpu_baseline : oracle/_ref (the reference's own sources compiled unmodified) on a bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+METRIC = "PairHMM GCUPS (DP cell updates per second, float pass + double rescue)"
+FP32_LANES_PER_SM = 128
+PIPE_OPS_PER_CELL = 8      # 4 FMUL + 4 FFMA (computeMXY contracted), SURVEY.md 8(d)
+FLOP_PER_CELL = 12
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--regions", type=int, default=10000, help="regions per rank (10000 = BASELINE configs[1])")
+    ap.add_argument("--cpu-sample-regions", type=int, default=0, help="regions in the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.rows = []
+        self.stop_flag = False
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def cpu_reference_run(batch, threads, want_seconds=None):
+    """times oracle/_ref (kind 'reference') or the C port (kind 'port') on `batch`; returns dict."""
+    import oracle_py
+    if oracle_py.reference_available():
+        lib, kind = oracle_py.load_reference(), "reference"
+        isa = "AVX-512" if lib.isa() == 512 else "AVX-256"
+    else:
+        lib, kind, isa = oracle_py.load_oracle(), "port", "scalar C"
+    flat = batch.as_flat()
+    _, _, secs = lib.compute(flat, threads=threads, tables_in_timed_region=True, want_rescued=False)
+    cells = batch.cells()
+    return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": threads, "kind": kind, "isa": isa,
+            "seconds": secs, "cells": cells,
+            "sample": "%d regions of the same workload (%d pairs, %.3g cells), per-read tables built inside the timed region"
+                      % (batch.n_regions, batch.n_pairs, cells)}
+
+
+def run_reference_arm(args, rank, world):
+    """--impl reference: the reference's CPU implementation on this box's host cores, bounded sample per step."""
+    if rank != 0:
+        return
+    from fgdp_b200 import synth
+    threads = os.cpu_count() or 1
+    n_reg = args.cpu_sample_regions or 160       # ~1.8e10 cells: a few seconds per step on 16 AVX-512 threads
+    sample = synth.config2(args.regions).subset(range(n_reg)) if args.regions <= 2000 else synth.config2(n_reg)
+    for _ in range(max(0, min(args.warmup, 1))):
+        cpu_reference_run(sample, threads)
+    secs, res = 0.0, None
+    for _ in range(args.steps):
+        res = cpu_reference_run(sample, threads)
+        secs += res["seconds"]
+    value = sample.cells() * args.steps / secs / 1e9
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64-rescue",
+            "data": "synthetic",
+            "config": {"workload": "BASELINE configs[1] synthetic WES-like batch (bounded CPU sample: %s)" % res["sample"],
+                       "regions_per_rank": args.regions},
+            "cpu_baseline": {"value": value, "unit": "GCUPS", "cores": threads, "kind": res["kind"], "isa": res["isa"],
+                             "sample": res["sample"]},
+            "e2e": {"value": value, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank, world, local = dist_env()
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import fgdp_b200
+    from fgdp_b200 import synth
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def reduce_max(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def reduce_sum(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # every rank owns its own shard of the named workload (weak scaling; rank 0's shard is BASELINE configs[1])
+    batch = synth.config2(args.regions, seed_extra=rank)
+    cells, pairs = batch.cells(), batch.n_pairs
+    eng = fgdp_b200.Engine(device=local)
+    eng.initialize(int(batch.read_len.max()), int(batch.hap_len.max()))
+
+    # ---- device-resident replay: `value` and the roofline of the FP32 forward kernel
+    eng.resident_load(batch)
+    for _ in range(args.warmup):
+        eng.resident_run()
+    sampler = ClockSampler(local); sampler.start()
+    eng.stats_reset()
+    barrier()
+    ms_total = ms_float = 0.0
+    for _ in range(args.steps):
+        a, f = eng.resident_run()          # synchronises its stream; CUDA-event times of the step's kernels
+        ms_total += a; ms_float += f
+    barrier()
+    launches = eng.stats()["kernel_launches"]
+    got, resc = eng.resident_fetch()
+    ms_step = reduce_max(ms_total / args.steps)
+    total_cells = reduce_sum(float(cells))
+    value = total_cells / (ms_step * 1e-3) / 1e9
+
+    # ---- end to end through the C ABI: host arrays in, host results out, every step
+    out = np.zeros(pairs, np.float64); rs = np.zeros(pairs, np.uint8)
+    for _ in range(min(args.warmup, 2)):
+        eng.compute_batch(batch, out, rs)
+    eng.stats_reset()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.compute_batch(batch, out, rs)
+    e2e_s = reduce_max((time.perf_counter() - t0) / args.steps)
+    barrier()
+    sampler.stop()
+    st = eng.stats()
+    same = bool(np.array_equal(out, got) and np.array_equal(rs, resc))
+    e2e_value = total_cells / e2e_s / 1e9
+
+    if rank != 0:
+        return
+    # ---- roofline: FP32 FMA pipe (compute bound); HBM traffic only to show it is not the limit
+    import ctypes
+    peaks = measured_peaks()
+    sm_max_mhz = float(peaks.get("sm_max_mhz", 1965.0))
+    n_sm = 148
+    try:
+        import torch
+        n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+    except Exception:
+        pass
+    clocks = sampler.summary()
+    peak_ops = n_sm * FP32_LANES_PER_SM * sm_max_mhz * 1e6                    # FMA-pipe lane-ops / s
+    float_ms_step = ms_float / args.steps
+    achieved_ops = cells * PIPE_OPS_PER_CELL / (float_ms_step * 1e-3)
+    algo_bytes = int(batch.read_len.astype(np.int64).sum()) * 5 + int(batch.hap_len.astype(np.int64).sum()) * 4 + pairs * 4
+    roofline = {"bound": "fp32_fma", "kernel": "forward_kernel<float, W, K, KL, exact=0, uniform_gcp=1>",
+                "achieved": achieved_ops / 1e12, "peak": peak_ops / 1e12, "unit": "T FMA-pipe lane-ops/s",
+                "frac": achieved_ops / peak_ops,
+                "peak_source": "derived: %d SMs x 128 FP32 lanes x %.0f MHz (sm_max_mhz of MEASURED_PEAKS.json); "
+                               "MEASURED_PEAKS.json has no FP32 entry" % (n_sm, sm_max_mhz),
+                "frac_at_measured_clock": (achieved_ops / (n_sm * FP32_LANES_PER_SM * clocks["sm_mhz"] * 1e6)) if clocks.get("sm_mhz") else None,
+                "tflops_flop_form": cells * FLOP_PER_CELL / (float_ms_step * 1e-3) / 1e12,
+                "float_kernel_gcups": cells / (float_ms_step * 1e-3) / 1e9, "float_kernel_ms": float_ms_step,
+                "algorithmic_bytes": algo_bytes, "algorithmic_hbm_GBps": algo_bytes / (float_ms_step * 1e-3) / 1e9,
+                "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None}
+    cpu = None
+    if not args.no_cpu_baseline:
+        n_reg = args.cpu_sample_regions or min(args.regions, 160)
+        cpu = cpu_reference_run(batch.subset(range(n_reg)), os.cpu_count() or 1)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "isa", "sample")}
+    line = {"metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32+f64-rescue", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[1]: synthetic WES-like batch, %d regions, ~200 reads x 4-16 haps, "
+                                   "150 bp reads, 250-500 bp haps, per GPU" % args.regions,
+                       "pairs_per_gpu": pairs, "cells_per_gpu": cells, "rescued_frac": float(resc.mean()),
+                       "l2": "inputs (%.2f GB of read planes + haplotype words per GPU) exceed the 126 MB L2" %
+                             ((batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4) / 1e9),
+                       "parallelism": "%d independent rank(s), no collective" % world},
+            "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"] // args.steps,
+                    "d2h_bytes_per_step": st["d2h_bytes"] // args.steps, "ms_per_step": e2e_s * 1e3,
+                    "host_pack_ms_per_step": st["host_ms_pack"] / args.steps, "identical_to_resident_run": same},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    del ctypes
+
+
+if __name__ == "__main__":
+    main()

@@ -54,7 +54,7 @@ struct RegionPlan {
 // Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
 struct Slot {
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev_begin = nullptr, ev_float_done = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_fwd_done = nullptr, ev_float_done = nullptr, ev_end = nullptr;
     // host staging
     PinnedBuf<uint8_t> h_rd, h_hapbytes, h_flag;
     PinnedBuf<DevRead> h_reads;

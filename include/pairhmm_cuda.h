@@ -150,7 +150,8 @@ int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, i
 
 /* Device-resident replay, for measuring the kernels without host<->device traffic: stage a flat batch
  * once (H2D + layout), then run the float+rescue kernels on it any number of times; results stay on
- * the device until _resident_fetch. kernel_ms (nullable) receives the CUDA-event time of the run. */
+ * the device until _resident_fetch. kernel_ms (nullable) receives the CUDA-event time of the whole run
+ * (FP32 forward + finalize + FP64 rescue), float_kernel_ms that of the FP32 forward kernels alone. */
 int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
                                const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
                                const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
