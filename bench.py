@@ -187,8 +187,14 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    # every rank owns its own shard of the named workload (weak scaling; rank 0's shard is BASELINE configs[1])
-    batch = synth.config2(args.regions, seed_extra=rank)
+    # weak scaling: the job is world x BASELINE configs[1]; its regions are split over the ranks by cost
+    # (DP cells) with the LPT rule -- every rank derives the same split from the region shapes
+    # and generates only its own regions. With one rank this is exactly configs[1].
+    if world > 1:
+        _, _, cost = synth.config2_shapes(args.regions * world)
+        batch = synth.config2(args.regions * world, select=synth.lpt_shard(cost, world)[rank])
+    else:
+        batch = synth.config2(args.regions)
     cells, pairs = batch.cells(), batch.n_pairs
     eng = fgdp_b200.Engine(device=local)
     eng.initialize(int(batch.read_len.max()), int(batch.hap_len.max()))
@@ -267,7 +273,7 @@ def main():
                        "pairs_per_gpu": pairs, "cells_per_gpu": cells, "rescued_frac": float(resc.mean()),
                        "l2": "inputs (%.2f GB of read planes + haplotype words per GPU) exceed the 126 MB L2" %
                              ((batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4) / 1e9),
-                       "parallelism": "%d independent rank(s), no collective" % world},
+                       "parallelism": "%d rank(s), regions LPT-sharded by DP cells, no collective on the data path" % world},
             "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"] // args.steps,
                     "d2h_bytes_per_step": st["d2h_bytes"] // args.steps, "ms_per_step": e2e_s * 1e3,
                     "host_pack_ms_per_step": st["host_ms_pack"] / args.steps, "identical_to_resident_run": same},

@@ -214,11 +214,15 @@ def _region(rng, n_reads, hap_lens, R, profile, sub_rate=None, foreign_frac=0.0)
 
 
 def make_batch(seed, n_reads_per_region, hap_lens_per_region, R, profile="clean", sub_rate=None, name="",
-               foreign_frac=0.0):
-    rng = np.random.default_rng(seed)
+               foreign_frac=0.0, region_ids=None):
+    """Every region is generated from its own RNG stream (seed, region id), so any subset of a job can be
+    generated by any rank without generating the rest (used by the LPT sharding of bench.py)."""
     rb, bq, iq, dq, gc, hb, hl, rl = [], [], [], [], [], [], [], []
     rrs, rhs = [0], [0]
-    for nr, hls in zip(n_reads_per_region, hap_lens_per_region):
+    if region_ids is None:
+        region_ids = range(len(n_reads_per_region))
+    for gid, nr, hls in zip(region_ids, n_reads_per_region, hap_lens_per_region):
+        rng = np.random.default_rng([int(seed), int(gid)])
         haps, b, q, i, d, c = _region(rng, int(nr), hls, R, profile, sub_rate, foreign_frac)
         rb.append(b.reshape(-1)); bq.append(q.reshape(-1)); iq.append(i.reshape(-1))
         dq.append(d.reshape(-1)); gc.append(c.reshape(-1))
@@ -228,10 +232,10 @@ def make_batch(seed, n_reads_per_region, hap_lens_per_region, R, profile="clean"
             hl.append(len(h))
         rrs.append(rrs[-1] + int(nr))
         rhs.append(rhs[-1] + len(haps))
-    rl = np.concatenate(rl)
+    rl = np.concatenate(rl) if rl else np.zeros(0, np.int32)
     hl = np.asarray(hl, np.int32)
-    return RegionBatch(np.concatenate(rb), np.concatenate(bq), np.concatenate(iq), np.concatenate(dq),
-                       np.concatenate(gc), _offsets(rl), rl, np.concatenate(hb), _offsets(hl), hl,
+    cat = lambda xs: np.concatenate(xs) if xs else np.zeros(0, np.uint8)
+    return RegionBatch(cat(rb), cat(bq), cat(iq), cat(dq), cat(gc), _offsets(rl), rl, cat(hb), _offsets(hl), hl,
                        np.asarray(rrs, np.int64), np.asarray(rhs, np.int64), name)
 
 
@@ -243,15 +247,41 @@ def config1(profile="clean"):
     return make_batch(SEED0 + 1, [64], [np.full(8, 300)], 150, profile, name="C1-" + profile)
 
 
-def config2(n_regions=10000, profile="clean", seed_extra=0):
-    """C2: WES-like, ~200 reads x 4-16 haps per region, R=150, H in [250,500] (configs[1])."""
+def config2_shapes(n_regions, seed_extra=0):
+    """region shapes of C2 without generating any bases: (reads per region, list of haplotype lengths, cost)
+    with cost = sum(read lengths) * sum(haplotype lengths) = DP cells of the region."""
     rng = np.random.default_rng(SEED0 + 2 + 7919 * seed_extra)
     nr = np.clip(rng.poisson(200, size=n_regions), 50, 400)
     nh = rng.integers(4, 17, size=n_regions)
     base = rng.integers(250, 501, size=n_regions)
     hls = [np.clip(b + rng.integers(-10, 11, size=k), 250, 500) for b, k in zip(base, nh)]
-    return make_batch(SEED0 + 2 + 104729 * seed_extra, nr, hls, 150, profile, name="C2-%s-%d" % (profile, n_regions),
-                      foreign_frac=0.02)
+    cost = np.array([int(n) * 150 * int(h.sum()) for n, h in zip(nr, hls)], np.int64)
+    return nr, hls, cost
+
+
+def config2(n_regions=10000, profile="clean", seed_extra=0, select=None):
+    """C2: WES-like, ~200 reads x 4-16 haps per region, R=150, H in [250,500] (configs[1]). `select` = indices
+    of the regions to actually generate (default all)."""
+    nr, hls, _ = config2_shapes(n_regions, seed_extra)
+    ids = np.arange(n_regions) if select is None else np.asarray(select, np.int64)
+    return make_batch(SEED0 + 2 + 104729 * seed_extra, nr[ids], [hls[i] for i in ids], 150, profile,
+                      name="C2-%s-%d" % (profile, len(ids)), foreign_frac=0.02, region_ids=ids)
+
+
+def lpt_shard(costs, n_shards):
+    """Longest-processing-time-first split of work items by cost: returns a list of index arrays, one per
+    shard (cell-count-balanced split of regions over GPUs, no collective)."""
+    import heapq
+    costs = np.asarray(costs, np.int64)
+    order = np.argsort(-costs, kind="stable")
+    heap = [(0, s) for s in range(n_shards)]
+    heapq.heapify(heap)
+    out = [[] for _ in range(n_shards)]
+    for i in order:
+        load, s = heapq.heappop(heap)
+        out[s].append(int(i))
+        heapq.heappush(heap, (load + int(costs[i]), s))
+    return [np.sort(np.asarray(o, np.int64)) for o in out]
 
 
 def config3(n_reads=2000, n_haps=32, profile="lowq"):

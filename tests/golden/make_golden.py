@@ -1,0 +1,49 @@
+#!/usr/bin/env python3
+"""Generates tests/golden/*.npz from the REFERENCE's own code (oracle/_ref/libref_pairhmm.so, built by
+oracle/Makefile from the unmodified sources under /root/reference). Run in the container that has
+/root/reference:   python tests/golden/make_golden.py
+
+Each fixture stores the input bytes and the reference's outputs (log10 likelihoods as float64, rescue flags), plus
+the build facts (ISA path the reference's CPUID test selected, compiler, flags). The reference ships no golden
+vectors of its own for this path, so these are what pins the oracle and the CUDA engine.
+"""
+import os
+import subprocess
+import sys
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import oracle_py            # noqa: E402
+import fgdp_b200            # noqa: E402
+from fgdp_b200 import synth  # noqa: E402
+
+FIELDS = ("read_bases", "base_q", "ins_q", "del_q", "gcp", "read_off", "read_len", "hap_bases", "hap_off", "hap_len",
+          "reg_read_start", "reg_hap_start")
+
+
+def main():
+    ref = oracle_py.load_reference()
+    gxx = subprocess.run(["g++", "--version"], capture_output=True, text=True).stdout.splitlines()[0]
+    meta = "reference ISA path: AVX-%d; %s; -O3, default -ffp-contract (see oracle/Makefile)" % (ref.isa(), gxx)
+    cases = {
+        "c1_clean": synth.config1("clean"),
+        "c1_lowq": synth.config1("lowq"),
+        "edge": synth.edge_cases(),
+        "c3_small": synth.config3(48, 6),
+        "c4_small": synth.config4(2, 6, 3),
+        "c2_small": synth.config2(3),
+    }
+    for name, b in cases.items():
+        out, resc, _ = ref.compute(b.as_flat(), threads=8)
+        out_d, _, _ = ref.compute(b.as_flat(), use_double=True, threads=8)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), log10=out, rescued=resc, log10_use_double=out_d,
+                            meta=np.array(meta), **{f: getattr(b, f) for f in FIELDS})
+        print(name, b.n_pairs, "pairs, rescued", int(resc.sum()))
+    pf, mf, pd, md = ref.tables()
+    np.savez_compressed(os.path.join(HERE, "tables.npz"), ph2pr_f=pf, mm_f=mf[:8256], ph2pr_d=pd, mm_d=md[:8256], meta=np.array(meta))
+
+
+if __name__ == "__main__":
+    main()

@@ -4,7 +4,7 @@ import pytest
 
 import fgdp_b200
 from fgdp_b200 import synth
-from util import assert_parity, TOL
+from util import assert_parity, load_golden, GOLDEN, TOL
 
 pytestmark = pytest.mark.gpu
 
@@ -30,6 +30,22 @@ def test_config1_region_call(engine, oracle, profile):
     got, gresc = engine.compute(reads, haps)
     assert got.shape == (64, 8)
     assert_parity(got, gresc, want, wresc, what="C1-" + profile)
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_vectors_from_the_reference(engine, name):
+    """committed outputs of the reference's own code (tests/golden/make_golden.py)"""
+    b, want, wresc, want_d = load_golden(name)
+    got, gresc = engine.compute_batch(b)
+    assert_parity(got, gresc, want, wresc, what="golden " + name)
+    e = fgdp_b200.Engine(use_double=True)
+    try:
+        got_d, resc_d = e.compute_batch(b)
+    finally:
+        e.close()
+    fin = np.isfinite(want_d)
+    assert resc_d.all() and np.array_equal(np.isfinite(got_d), fin)
+    assert np.abs(got_d[fin] - want_d[fin]).max() < 1e-9
 
 
 def test_edge_cases(engine, oracle):

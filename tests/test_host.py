@@ -1,0 +1,90 @@
+"""CPU tests: the C-ABI library loads and exports what include/pairhmm_cuda.h declares (no compute without a GPU),
+the engine's uploaded tables equal the reference's, host-side sharding logic, the bench's JSON contract."""
+import ctypes
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import fgdp_b200
+from fgdp_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "pairhmm_cuda.h")).read()
+    declared = sorted(set(re.findall(r"\b(pairhmm_cuda_[a-z_0-9]+)\s*\(", hdr)))
+    assert len(declared) >= 19
+    lib = fgdp_b200.load_library()
+    for name in declared:
+        assert hasattr(lib, name), "libpairhmm_cuda.so does not export %s" % name
+    assert sorted(fgdp_b200.EXPORTED_SYMBOLS) == declared
+    assert lib.pairhmm_cuda_abi_version() == 1
+
+
+def test_product_library_does_not_link_the_oracle():
+    out = subprocess.run(["ldd", fgdp_b200.lib_path()], capture_output=True, text=True).stdout
+    assert "oracle" not in out and "ref_pairhmm" not in out
+    syms = subprocess.run(["nm", "-D", fgdp_b200.lib_path()], capture_output=True, text=True).stdout
+    assert "oracle_" not in syms and "initNative" not in syms
+
+
+def test_engine_tables_match_reference_golden():
+    from fgdp_b200.pairhmm import host_tables
+    z = np.load(os.path.join(ROOT, "tests", "golden", "tables.npz"))
+    pf, mf, pd, md = host_tables()
+    for got, key in ((pf, "ph2pr_f"), (mf, "mm_f"), (pd, "ph2pr_d"), (md, "mm_d")):
+        assert np.array_equal(got.view(np.uint8), z[key].view(np.uint8)), key
+
+
+def test_no_cpu_fallback_without_gpu():
+    if fgdp_b200.device_count() > 0:
+        pytest.skip("a GPU is visible")
+    with pytest.raises(fgdp_b200.PairHMMError) as e:
+        fgdp_b200.Engine()
+    assert e.value.status == -3            # PAIRHMM_ERR_NO_DEVICE: loud failure, nothing routed to a CPU path
+    with pytest.raises(fgdp_b200.PairHMMError):
+        fgdp_b200.CudaPairHMM()
+
+
+def test_default_config_and_null_handling():
+    lib = fgdp_b200.load_library()
+    from fgdp_b200.pairhmm import Config
+    cfg = Config()
+    lib.pairhmm_cuda_default_config(ctypes.byref(cfg))
+    assert (cfg.device, cfg.use_double, cfg.exact_fp32, cfg.dedup_reads) == (-1, 0, 0, 1)
+    assert lib.pairhmm_cuda_create(ctypes.byref(cfg), None) == -1
+    assert lib.pairhmm_cuda_initialize(None, 10, 10) == -1
+    assert lib.pairhmm_cuda_destroy(None) == 0
+
+
+def test_lpt_shard_balances_cells():
+    _, _, cost = synth.config2_shapes(4000)
+    for n in (2, 4, 8):
+        shards = synth.lpt_shard(cost, n)
+        assert sorted(np.concatenate(shards).tolist()) == list(range(4000))
+        loads = np.array([cost[s].sum() for s in shards], np.float64)
+        assert loads.max() / loads.mean() < 1.001
+
+
+def test_select_generates_the_same_regions():
+    full = synth.config2(12)
+    part = synth.config2(12, select=[2, 5, 11])
+    sub = full.subset([2, 5, 11])
+    for f in ("read_bases", "base_q", "ins_q", "del_q", "gcp", "hap_bases", "read_len", "hap_len"):
+        assert np.array_equal(getattr(part, f), getattr(sub, f)), f
+
+
+def test_bench_reference_arm_json_contract():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
+                          "--warmup", "0", "--cpu-sample-regions", "3"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "GCUPS" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["higher_is_better"] is True

@@ -1,0 +1,75 @@
+"""CPU tests (run with -m "not gpu"): the oracle against the golden vectors made from the reference's own code,
+against the live reference build when oracle/_ref is present, and the lookup tables."""
+import numpy as np
+import pytest
+
+from fgdp_b200 import synth
+from util import assert_parity, load_golden, GOLDEN, TOL
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_oracle_matches_golden(oracle, name):
+    """fixtures hold outputs of the reference (AVX-512 path, FMA-contracted); the oracle is the unfused scalar
+    restatement: <= 1e-4 in log10 (observed <= 4e-6 = one float ulp at |log10| ~ 40), identical rescue set"""
+    b, want, wresc, want_d = load_golden(name)
+    got, resc, _ = oracle.compute(b.as_flat(), threads=4)
+    assert_parity(got, resc, want, wresc, what=name)
+    fin = np.isfinite(want)
+    assert np.abs(got[fin] - want[fin]).max() < 1e-5
+    got_d, resc_d, _ = oracle.compute(b.as_flat(), use_double=True, threads=4)
+    assert resc_d.all()
+    fin = np.isfinite(want_d)
+    assert np.array_equal(np.isfinite(got_d), fin)
+    assert np.abs(got_d[fin] - want_d[fin]).max() < 1e-9      # FP64 route: only FMA-vs-no-FMA rounding
+
+
+def test_golden_covers_both_routes():
+    tot = resc = 0
+    for name in GOLDEN:
+        _, want, wresc, _ = load_golden(name)
+        tot += wresc.size; resc += int(wresc.sum())
+    assert resc > 500 and tot - resc > 5000
+
+
+def test_tables_match_golden_bitwise(oracle):
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "tables.npz"))
+    pf, mf, pd, md = oracle.tables()
+    for got, key in ((pf, "ph2pr_f"), (mf[:8256], "mm_f"), (pd, "ph2pr_d"), (md[:8256], "mm_d")):
+        assert np.array_equal(got.view(np.uint8), z[key].view(np.uint8)), key
+
+
+def test_oracle_vs_live_reference(oracle, reference):
+    """when the reference build is present: fresh random inputs, not only the committed fixtures"""
+    for b in (synth.config2(2, seed_extra=5), synth.config3(40, 5), synth.edge_cases(seed=99)):
+        flat = b.as_flat()
+        want, wresc, _ = reference.compute(flat, threads=8)
+        got, resc, _ = oracle.compute(flat, threads=8)
+        assert_parity(got, resc, want, wresc, what=b.name)
+    to, tr = oracle.tables(), reference.tables()
+    for a, c in zip(to, tr):
+        assert np.array_equal(a.view(np.uint8), c.view(np.uint8))
+
+
+def test_oracle_edge_semantics(oracle):
+    """N matches everything, non-ACGTN bytes behave as 'A', quals are masked with &127"""
+    A = np.frombuffer(b"ACGTACGTAC", np.uint8)
+
+    def one(read, hap, q=30, i=45, d=45, c=10):
+        n = len(read)
+        b = synth.RegionBatch(np.asarray(read, np.uint8), np.full(n, q, np.uint8), np.full(n, i, np.uint8),
+                              np.full(n, d, np.uint8), np.full(n, c, np.uint8), np.zeros(1, np.int64),
+                              np.array([n], np.int32), np.asarray(hap, np.uint8), np.zeros(1, np.int64),
+                              np.array([len(hap)], np.int32), np.array([0, 1], np.int64), np.array([0, 1], np.int64))
+        return oracle.compute(b.as_flat())[0][0]
+
+    base = one(A, A)
+    n_read = A.copy(); n_read[3] = ord("N")
+    n_hap = A.copy(); n_hap[3] = ord("N")
+    assert one(n_read, A) == base and one(A, n_hap) == base          # N never costs a mismatch
+    lower = A.copy(); lower[0] = ord("a")
+    junk = A.copy(); junk[4] = ord("x")                               # position 4 is 'A'
+    assert one(lower, A) == base and one(junk, A) == base
+    assert one(A, A, q=30 | 0x80, i=45 | 0x80, d=45 | 0x80, c=10 | 0x80) == base
+    mism = A.copy(); mism[5] = ord("A")
+    assert one(mism, A) < base - 1.0
