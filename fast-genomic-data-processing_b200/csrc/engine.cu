@@ -196,9 +196,10 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
 // Lane-group width for a read of length R under the given FP32 variant. Narrow groups (more rows per
 // lane) exist for the uniform-gcp kernels only; forced_w (config.reserved[1]) overrides the choice.
 int choose_width(int R, Variant v, int forced_w) {
-    if (v != Variant::F32_UG) return 32;
+    if (v != Variant::F32_PK) return 32;
     if (forced_w && bin_of_read(R, forced_w) >= 0) return forced_w;
-    // measured on B200 (C2, R = 150): W=32 2.00, W=16 2.32, W=8 2.56 TCUPS -- the narrowest group that fits wins
+    // the narrowest group that fits wins: more rows per lane amortise the per-column overhead (shuffles,
+    // table address, loop) over more cells
     if (bin_of_read(R, 8) >= 0) return 8;
     if (bin_of_read(R, 16) >= 0) return 16;
     return 32;
@@ -269,8 +270,10 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     for (size_t i = 0; i < n_regs; ++i) { gmin = std::min(gmin, s.plans[i].gcp_min); gmax = std::max(gmax, s.plans[i].gcp_max); }
     s.uniform_gcp = gmin == gmax;
     s.gcp_value = gmin;
+    // use_double bins at W = 32 for the FP64 kernels; reserved[2] selects the scalar uniform-gcp kernel (cross-check)
     s.float_variant = (h->cfg.use_double || h->cfg.exact_fp32) ? (h->cfg.exact_fp32 ? Variant::F32_EXACT : Variant::F32_GEN)
-                      : (s.uniform_gcp && !h->cfg.reserved[0]) ? Variant::F32_UG : Variant::F32_GEN;
+                      : (s.uniform_gcp && !h->cfg.reserved[0]) ? (h->cfg.reserved[2] ? Variant::F32_UG : Variant::F32_PK)
+                      : Variant::F32_GEN;
     const int forced_w = h->cfg.reserved[1];
     parallel_for(n_regs, threads, 8, [&](size_t i) { bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w); });
 
@@ -285,7 +288,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         p.hap_word_off = hw; p.hap_list_off = hl; p.upair_off = up;
         for (auto &run : p.runs) {
             int W, K, KL; bin_shape(run.bin, W, K, KL);
-            const uint32_t per_warp = 32u / (uint32_t)W;
+            const uint32_t per_warp = (uint32_t)reads_per_warp(s.float_variant, W);
             run.unit_off = bin_count[run.bin];
             bin_count[run.bin] += (run.n_reads + per_warp - 1) / per_warp * p.n_groups;
         }
@@ -320,7 +323,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     std::memcpy(s.h_rescue_base.p, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
     RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
     RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
-    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 2 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
 #undef RES
 
     // pass B: copy bytes, fill descriptors and units
@@ -341,7 +344,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         const uint32_t nhap = (uint32_t)rv.n_haps;
         for (const auto &run : p.runs) {
             int W, K, KL; bin_shape(run.bin, W, K, KL);
-            const uint32_t per_warp = 32u / (uint32_t)W;
+            const uint32_t per_warp = (uint32_t)reads_per_warp(s.float_variant, W);
             DevUnit *ud = s.h_units.p + s.bin_start[run.bin] + run.unit_off;
             for (uint32_t j = 0; j < run.n_reads; j += per_warp) {
                 const uint32_t nr = std::min(per_warp, run.n_reads - j), first = run.first + j;
@@ -412,6 +415,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     // uniform gap-continuation constants, computed exactly as the per-row path does (ph2pr[c], 1 - ph2pr[c])
     const int gc = s.gcp_value & 127;
     a.u_xy_f = t.ph2pr_f[gc]; a.u_gapm_f = 1.0f - t.ph2pr_f[gc];
+    std::memcpy(&a.u_xy_bits, &a.u_xy_f, sizeof a.u_xy_bits);
     a.u_xy_d = t.ph2pr_d[gc]; a.u_gapm_d = 1.0 - t.ph2pr_d[gc];
     const bool all_double = h->cfg.use_double != 0;
     const Variant vf = s.float_variant, vd = Variant::F64_GEN;

@@ -102,7 +102,7 @@ struct pairhmm_cuda_handle {
     double *d_ph2pr_d = nullptr, *d_mm_d = nullptr;
     float log10_init_f = 0.f;
     double log10_init_d = 0.0;
-    int blocks_per_sm[4][phmm::kNumBins] = {{0}};   // [Variant][bin], 0 = not queried yet
+    int blocks_per_sm[phmm::kNumVariants][phmm::kNumBins] = {{0}};   // [Variant][bin], 0 = not queried yet
     int read_max_len = 0, hap_max_len = 0;
     phmm::Slot slots[2];
     int64_t next_ticket = 1;

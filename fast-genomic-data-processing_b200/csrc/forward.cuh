@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
         __syncwarp();                                  // previous unit's readers are done with hap_info
         if ((uint32_t)lane < unit_nh) {                // nh <= kMaxUnitHaps == 32 (host guarantees)
             const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
-            steps = hp.len / C + 1;
+            steps = (int)hap_tiles(hp.len);
             hap_info[lane] = HapInfo<T>{hp.off / C, N::div(N::init_const(), (T)hp.len)};   // template.h:115
         }
         __syncwarp();

@@ -1,7 +1,7 @@
 // Auxiliary kernels (haplotype byte -> column-word expansion, FP32 result finalisation) and the
 // dispatch from (variant, K, KL) to the forward_kernel instantiations of inst_*.cu. The forward kernel
 // itself is in forward.cuh.
-#include "forward.cuh"
+#include "forward2.cuh"
 
 namespace phmm {
 namespace {
@@ -12,7 +12,7 @@ __device__ __forceinline__ uint32_t code_word(uint32_t b) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// haplotype bytes -> code words + SEP (+ PADs up to the tile boundary); block per haplotype; block 0 also
+// haplotype bytes -> code words (+ PADs up to the tile boundary) + the [SEP, PAD..] tile; block per haplotype; block 0 also
 // writes the fill/drain words.
 __global__ void prep_haps_kernel(const uint8_t *__restrict__ hap_bytes, const uint64_t *__restrict__ byte_off,
                                  const DevHap *__restrict__ haps, uint32_t n_haps, uint32_t *__restrict__ hapw) {
@@ -22,9 +22,9 @@ __global__ void prep_haps_kernel(const uint8_t *__restrict__ hap_bytes, const ui
         const DevHap d = haps[h];
         const uint8_t *src = hap_bytes + byte_off[h];
         uint32_t *dst = hapw + d.off;
-        const int nw = (d.len / kTile + 1) * kTile;
+        const int nw = (int)hap_tiles(d.len) * kTile, sep = nw - kTile;
         for (int c = threadIdx.x; c < nw; c += blockDim.x)
-            dst[c] = (c < d.len) ? code_word(base_index(src[c])) : (c == d.len ? kWordSep : kWordPad);
+            dst[c] = (c < d.len) ? code_word(base_index(src[c])) : (c == sep ? kWordSep : kWordPad);
     }
 }
 

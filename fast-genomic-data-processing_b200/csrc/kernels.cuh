@@ -6,8 +6,9 @@
 //   DevRead      {off,len}              byte offset of a read inside every plane
 //   hap words    uint32 hapw[]          one word per DP column, in tiles of kTile columns. Words
 //                                       [0,kLeadWords) = pipeline fill (PAD.. + one SEP) and drain (PAD..);
-//                                       then per haplotype: H code words, one SEP, and PADs up to the next
-//                                       tile boundary (a PAD after a SEP is a no-op column). A code word holds the
+//                                       then per haplotype: H code words, PADs up to the next tile boundary, and
+//                                       one tile [SEP, PAD..] (a SEP is always followed by a PAD: two flagged
+//                                       columns in a row reset a lane's state, forward2.cuh). A code word holds the
 //                                       base index b (A0 C1 T2 G3 N4) pre-multiplied for every rows-per-lane
 //                                       bucket (see code_word()), so a lane turns it into K match bits with
 //                                       one funnel shift of its per-base row masks.
@@ -29,8 +30,10 @@ struct DevHap  { uint32_t off; int32_t len; };
 struct alignas(16) DevUnit { uint32_t read; uint32_t hap_list; uint32_t shape; uint32_t out; };
 inline __host__ __device__ uint32_t unit_shape(uint32_t nh, uint32_t nreads, uint32_t stride) { return nh | (nreads << 8) | (stride << 16); }
 
-constexpr uint32_t kWordPad = 0xC0000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
-constexpr uint32_t kWordSep = 0x80000000u;   // flagged, column 0 of the next haplotype
+// flagged words carry base index 5 in bits 25..27: the packed kernel runs them through its column code with the
+// all-zero row of its match-factor table (forward2.cuh); the scalar kernels ignore those bits
+constexpr uint32_t kWordPad = 0xCA000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
+constexpr uint32_t kWordSep = 0x8A000000u;   // flagged, column 0 of the next haplotype
 #ifndef PHMM_TILE
 #define PHMM_TILE 2
 #endif
@@ -40,8 +43,10 @@ constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1
 constexpr int kMaxRowsPerLane = 8;           // K at W = 32: one warp covers reads up to 256 rows
 constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition
 
-// words a haplotype of length H occupies in hapw (code words + alignment PADs + SEP)
-inline uint32_t hap_words(int32_t H) { return ((uint32_t)H / kTile + 1u) * kTile; }
+// words a haplotype of length H occupies in hapw (code words + alignment PADs + the [SEP, PAD..] tile)
+static_assert(PHMM_TILE >= 2, "a SEP needs a PAD behind it in its own tile");
+inline __host__ __device__ uint32_t hap_tiles(int32_t H) { return ((uint32_t)H + kTile - 1u) / kTile + 1u; }
+inline uint32_t hap_words(int32_t H) { return hap_tiles(H) * kTile; }
 
 // match-mask geometry of a rows-per-lane bucket: rows are split into groups of kGroupBits(K) rows, each
 // group keeps 5 (one per haplotype base) bit fields of that width in one 32-bit register
@@ -68,6 +73,7 @@ struct KernelArgs {
     const void *mm;               // T[8256]
     // uniform gap-continuation constants (UG kernels): ph2pr[gcp] and 1 - ph2pr[gcp]
     float u_xy_f, u_gapm_f;
+    uint32_t u_xy_bits;           // bit pattern of u_xy_f again (packed kernel: source of the per-column Y coefficient)
     double u_xy_d, u_gapm_d;
     // FP32 pass outputs
     float *fres;                  // scaled forward sum per unique pair
@@ -94,10 +100,10 @@ struct FinalizeArgs {
 // (shuffles, boundary selects, loop) is amortised over more cells, at the price of registers.
 constexpr int kNumWidths = 3;
 constexpr int kWidths[kNumWidths] = {32, 16, 8};
-constexpr int kMaxK[kNumWidths] = {8, 16, 20};           // rows per lane limit per width
+constexpr int kMaxK[kNumWidths] = {8, 12, 12};           // rows per lane limit per width
 constexpr int tri(int k) { return k * (k + 1) / 2; }
-constexpr int kBinBase[kNumWidths + 1] = {0, tri(8), tri(8) + tri(16), tri(8) + tri(16) + tri(20)};
-constexpr int kNumBins = kBinBase[kNumWidths];           // 36 + 136 + 210 = 382
+constexpr int kBinBase[kNumWidths + 1] = {0, tri(8), tri(8) + tri(12), tri(8) + tri(12) + tri(12)};
+constexpr int kNumBins = kBinBase[kNumWidths];           // 36 + 78 + 78 = 192
 constexpr int kNumBinsW32 = kBinBase[1];
 
 inline int width_index(int W) { return W == 32 ? 0 : W == 16 ? 1 : W == 8 ? 2 : -1; }
@@ -118,7 +124,13 @@ inline void bin_shape(int bin, int &W, int &K, int &KL) {
     KL = r - tri(K - 1);
 }
 
-enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3 };
+// F32_PK: packed (two reads per lane, FFMA2) uniform-gcp kernel of forward2.cuh -- the production FP32 path;
+// F32_UG: scalar uniform-gcp kernel (W = 32 only; kept as the cross-check of the packed one);
+// F32_GEN / F32_EXACT / F64_GEN: per-row gap-continuation registers, W = 32 only.
+enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3, F32_PK = 4 };
+constexpr int kNumVariants = 5;
+// reads swept by one warp
+inline int reads_per_warp(Variant v, int W) { return (v == Variant::F32_PK ? 2 : 1) * (32 / W); }
 
 // Launchers. All asynchronous on `st`; return the cudaError of the launch.
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,

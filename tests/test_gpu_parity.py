@@ -79,12 +79,15 @@ def test_exact_mode_is_bit_identical_to_the_unfused_oracle(oracle):
 
 
 def test_uniform_gcp_kernels_equal_general_kernels():
-    """the constant-bank (uniform gcp) kernels do the same FMAs as the per-row-register kernels"""
+    """the packed (two reads per lane, FFMA2) and the scalar constant-bank uniform-gcp kernels do the same IEEE
+    operations as the per-row-register kernels: raw FP32 sums identical to the last bit at every lane-group width"""
     b = synth.config2(5)
     assert b.gcp.min() == b.gcp.max() == 10
     raws = []
-    for force_general, lane_group in ((False, 32), (True, 32), (False, 16), (False, 8)):
-        e = fgdp_b200.Engine(force_general=force_general, dedup_reads=False, lane_group=lane_group)
+    for force_general, lane_group, scalar_uniform in ((True, 32, False), (False, 32, True), (False, 32, False),
+                                                      (False, 16, False), (False, 8, False), (False, 0, False)):
+        e = fgdp_b200.Engine(force_general=force_general, dedup_reads=False, lane_group=lane_group,
+                             scalar_uniform=scalar_uniform)
         try:
             e.resident_load(b); e.resident_run()
             raws.append(e.resident_fetch_raw())
