@@ -88,3 +88,15 @@ def test_bench_reference_arm_json_contract():
     assert line["impl"] == "reference" and line["unit"] == "GCUPS" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["higher_is_better"] is True
+
+
+def test_reference_side_adapter_compiles():
+    """integration/CudaPairHMM.cpp (the class a Mutect2Cpp maintainer adds) compiles against the
+    reference's real PairHMM.h; skipped where /root/reference does not exist (the GPU box)."""
+    import subprocess
+    import pytest
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([os.path.join(root, "integration", "check.sh")], capture_output=True, text=True)
+    if r.returncode == 77:
+        pytest.skip("reference tree absent")
+    assert r.returncode == 0, r.stdout + r.stderr
