@@ -250,7 +250,7 @@ def main():
     float_ms_step = ms_float / args.steps
     achieved_ops = cells * PIPE_OPS_PER_CELL / (float_ms_step * 1e-3)
     algo_bytes = int(batch.read_len.astype(np.int64).sum()) * 5 + int(batch.hap_len.astype(np.int64).sum()) * 4 + pairs * 4
-    roofline = {"bound": "fp32_fma", "kernel": "forward_kernel<float, W, K, KL, exact=0, uniform_gcp=1>",
+    roofline = {"bound": "fp32_fma", "kernel": "forward2_kernel<W, K, KL> (packed FP32: two reads per lane, FFMA2/FMUL2)",
                 "achieved": achieved_ops / 1e12, "peak": peak_ops / 1e12, "unit": "T FMA-pipe lane-ops/s",
                 "frac": achieved_ops / peak_ops,
                 "peak_source": "derived: %d SMs x 128 FP32 lanes x %.0f MHz (sm_max_mhz of MEASURED_PEAKS.json); "
