@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <mutex>
@@ -61,6 +62,12 @@ using clk = std::chrono::steady_clock;
 inline double ms_since(clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); }
 
 std::mutex g_err_mutex;   // plan_region runs on several threads and may report through fail()
+// PAIRHMM_CUDA_TRACE=1: per-chunk timeline of a batch on stderr (host ms since the batch began; GPU ms since the
+// base event recorded at the same moment)
+bool trace_on() { static const bool on = std::getenv("PAIRHMM_CUDA_TRACE") != nullptr; return on; }
+clk::time_point g_trace_t0;
+cudaEvent_t g_trace_base = nullptr;
+
 int fail(pairhmm_cuda_handle *h, int status, const std::string &msg) {
     if (h) { std::lock_guard<std::mutex> lk(g_err_mutex); h->last_error = msg; }
     return status;
@@ -406,6 +413,10 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kZeroedWords, st));
     CU(h, cudaMemcpyAsync(s.d_counters.p + kRescueBaseDev, s.h_rescue_base.p, sizeof(uint32_t) * (kNumBinsW32 + 1),
                           cudaMemcpyHostToDevice, st));
+    // The two slots' kernels must not share the GPU: run side by side they finish together, both slots come free at the
+    // same moment and the GPU idles while the host packs. Chained on the previous chunk's end event, chunk i is done
+    // (and its slot reusable) while chunk i+1 still computes; the copies in front of this point are not held back.
+    if (h->prev_end && h->prev_end != s.ev_end) CU(h, cudaStreamWaitEvent(st, h->prev_end, 0));
     CU(h, cudaEventRecord(s.ev_begin, st));
     const HostTables &t = host_tables();
     KernelArgs a{};
@@ -467,6 +478,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_end, st));
+    h->prev_end = s.ev_end;
     return PAIRHMM_OK;
 }
 
@@ -491,6 +503,12 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     float ms_f = 0.f, ms_all = 0.f;
     cudaEventElapsedTime(&ms_f, s.ev_begin, s.ev_float_done);
     cudaEventElapsedTime(&ms_all, s.ev_begin, s.ev_end);
+    if (trace_on() && g_trace_base) {
+        float b0 = 0.f, b1 = 0.f;
+        cudaEventElapsedTime(&b0, g_trace_base, s.ev_begin); cudaEventElapsedTime(&b1, g_trace_base, s.ev_end);
+        std::fprintf(stderr, "[trace] chunk done: host %.1f ms | gpu kernels %.1f .. %.1f ms (%.1f) | cells %.3g\n",
+                     ms_since(g_trace_t0), b0, b1, b1 - b0, (double)s.cells);
+    }
     h->stats.gpu_ms_float += ms_f; h->stats.gpu_ms_double += ms_all - ms_f; h->stats.gpu_ms_total += ms_all;
     auto t0 = clk::now();
     std::atomic<uint64_t> rescued{0}, uniq_pairs{0};
@@ -699,13 +717,23 @@ int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *region
     for (int si = 0; si < 2; ++si)
         if (h->slots[si].busy) { int st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
     const int threads = pack_threads(h);
+    if (trace_on()) {
+        if (!g_trace_base) cudaEventCreate(&g_trace_base);
+        g_trace_t0 = clk::now();
+        cudaEventRecord(g_trace_base, h->slots[0].stream);
+    }
     const int64_t chunk_cells = h->cfg.chunk_cells > 0 ? h->cfg.chunk_cells : (int64_t)100000000000ll;
     std::vector<RegionView> views;
     int64_t i = 0;
     int si = 0;
     int status = PAIRHMM_OK;
+    int chunk_no = 0;
     while (i < n_regions && status == PAIRHMM_OK) {
         views.clear();
+        // the GPU idles while the first chunk is packed: start small (packing is ~3x faster than the kernels, so each
+        // chunk may be 3x the previous one without starving the GPU)
+        const int64_t chunk_limit = chunk_no == 0 ? chunk_cells / 8 : chunk_no == 1 ? chunk_cells * 3 / 8 : chunk_cells;
+        ++chunk_no;
         int64_t cells = 0;
         uint64_t pairs = 0, rbytes = 0;
         while (i < n_regions) {
@@ -714,14 +742,17 @@ int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *region
             for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.reads[q].len);
             for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
             const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
-            if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_cells || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
+            if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_limit || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
             views.push_back(RegionView{r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out});
             cells += (int64_t)(rl * hl); pairs += p; rbytes += rl;
             ++i;
         }
         Slot &s = h->slots[si];
+        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: chunk of %zu regions cut\n", ms_since(g_trace_t0), views.size());
         if (s.busy) status = finish_chunk(h, s, threads);
+        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: slot free, packing\n", ms_since(g_trace_t0));
         if (status == PAIRHMM_OK) status = submit_chunk(h, s, views.data(), views.size(), threads);
+        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: submitted\n", ms_since(g_trace_t0));
         si ^= 1;
     }
     for (int k = 0; k < 2; ++k) {
@@ -757,10 +788,10 @@ int build_flat_views(pairhmm_cuda_handle *h, FlatViews &v, const uint8_t *read_b
     if (n_haps && (!hap_bases || !hap_off || !hap_len)) return fail(h, PAIRHMM_ERR_ARG, "null haplotype array");
     if (n_regions && (!reg_read_start || !reg_hap_start)) return fail(h, PAIRHMM_ERR_ARG, "null region array");
     v.reads.resize(n_reads); v.haps.resize(n_haps); v.regions.resize(n_regions);
-    for (int64_t i = 0; i < n_reads; ++i) {
+    parallel_for((size_t)n_reads, pack_threads(h), 65536, [&](size_t i) {
         const int64_t o = read_off[i];
         v.reads[i] = phmm_read{read_bases + o, base_q + o, ins_q + o, del_q + o, gcp + o, read_len[i]};
-    }
+    });
     for (int64_t i = 0; i < n_haps; ++i) v.haps[i] = phmm_hap{hap_bases + hap_off[i], hap_len[i]};
     int64_t out_off = 0;
     for (int64_t r = 0; r < n_regions; ++r) {
@@ -786,7 +817,7 @@ int pairhmm_cuda_compute_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases,
                               int64_t n_regions, double *log10_out, uint8_t *rescued_out) {
     if (!h) return PAIRHMM_ERR_ARG;
     auto t0 = clk::now();
-    FlatViews v;
+    static thread_local FlatViews v;     // kept between calls: 48 B per read, page-faulting it in every call costs more than filling it
     int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
                               hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, log10_out, rescued_out);
     if (st != PAIRHMM_OK) return st;

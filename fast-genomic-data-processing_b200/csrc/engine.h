@@ -107,5 +107,6 @@ struct pairhmm_cuda_handle {
     phmm::Slot slots[2];
     int64_t next_ticket = 1;
     int64_t slot_ticket[2] = {0, 0};
+    cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk (kernels of the next one wait on it)
     bool resident_loaded = false;
 };
