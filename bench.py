@@ -160,6 +160,10 @@ def main():
 
     import fgdp_b200
     from fgdp_b200 import synth
+    # stdout carries exactly one JSON line: anything libraries print meanwhile (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist = None
     if world > 1:
         import torch
@@ -233,6 +237,11 @@ def main():
     same = bool(np.array_equal(out, got) and np.array_equal(rs, resc))
     e2e_value = total_cells / e2e_s / 1e9
 
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     if rank != 0:
         return
     # ---- roofline: FP32 FMA pipe (compute bound); HBM traffic only to show it is not the limit
@@ -249,7 +258,9 @@ def main():
     peak_ops = n_sm * FP32_LANES_PER_SM * sm_max_mhz * 1e6                    # FMA-pipe lane-ops / s
     float_ms_step = ms_float / args.steps
     achieved_ops = cells * PIPE_OPS_PER_CELL / (float_ms_step * 1e-3)
-    algo_bytes = int(batch.read_len.astype(np.int64).sum()) * 5 + int(batch.hap_len.astype(np.int64).sum()) * 4 + pairs * 4
+    # 4 read planes (the uniform-gcp kernel never touches the gcp plane), one 4-byte column word per haplotype base,
+    # one float per pair
+    algo_bytes = int(batch.read_len.astype(np.int64).sum()) * 4 + int(batch.hap_len.astype(np.int64).sum()) * 4 + pairs * 4
     roofline = {"bound": "fp32_fma", "kernel": "forward2_kernel<W, K, KL> (packed FP32: two reads per lane, FFMA2/FMUL2)",
                 "achieved": achieved_ops / 1e12, "peak": peak_ops / 1e12, "unit": "T FMA-pipe lane-ops/s",
                 "frac": achieved_ops / peak_ops,
@@ -260,6 +271,13 @@ def main():
                 "float_kernel_gcups": cells / (float_ms_step * 1e-3) / 1e9, "float_kernel_ms": float_ms_step,
                 "algorithmic_bytes": algo_bytes, "algorithmic_hbm_GBps": algo_bytes / (float_ms_step * 1e-3) / 1e9,
                 "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None}
+    try:    # DRAM bytes of one launch of that kernel over this workload, from the committed ncu capture (profiles/)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tr.get("regions") == args.regions and world == 1:
+            roofline["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+            roofline["traffic_source"] = tr["source"]
+    except Exception:
+        pass
     cpu = None
     if not args.no_cpu_baseline:
         n_reg = args.cpu_sample_regions or min(args.regions, 160)
