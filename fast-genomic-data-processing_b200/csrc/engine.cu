@@ -405,6 +405,7 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
 static int blocks_for(pairhmm_cuda_handle *h, Variant v, int bin) {
     int &n = h->blocks_per_sm[(int)v][bin];
     if (n == 0) { int W, K, KL; bin_shape(bin, W, K, KL); n = std::max(1, forward_blocks_per_sm(v, W, K, KL)); }
+    if (h->cfg.reserved[3] > 0) return std::min(n, h->cfg.reserved[3]);   // tuning: cap the resident CTAs per SM
     return n;
 }
 

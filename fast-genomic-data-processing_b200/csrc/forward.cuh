@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
     static_assert(KL >= 0 && KL < K, "last-row slot out of range");
     static_assert(!(EXACT && UG), "the exact mode uses the general path");
     using N = Num<T>;
-    constexpr int C = kTile;
+    constexpr int C = kScalarTile;              // columns per step of these kernels (the word layout is aligned to kTile)
     using Tile = typename TileWord<C>::type;
     constexpr int GB = group_bits(K);           // rows per match-mask register
     constexpr int NG = (K + GB - 1) / GB;
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
         __syncwarp();                                  // previous unit's readers are done with hap_info
         if ((uint32_t)lane < unit_nh) {                // nh <= kMaxUnitHaps == 32 (host guarantees)
             const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
-            steps = (int)hap_tiles(hp.len);
+            steps = (int)(hap_tiles(hp.len) * (kTile / C));
             hap_info[lane] = HapInfo<T>{hp.off / C, N::div(N::init_const(), (T)hp.len)};   // template.h:115
         }
         __syncwarp();
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
 #pragma unroll
         for (int j = 0; j < C; ++j) { Din[j] = Uin[j] = (T)0; }
         int cur = -1;
-        uint32_t tix = 31 - sl;                        // tile index: lane l sees l PAD tiles, then [PAD..,SEP]
+        uint32_t tix = 32 * kTile / C - 1 - sl;        // tile index: lane l sees l PAD tiles, then the lead-in's [PAD..,SEP]
         Tile w = tiles[tix];
 
         // one DP column for this lane's K rows (computeMXY, template.h:177-192): Dd = diagonal term and
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
                 ++cur;
                 sumM = sumX = (T)0;
                 T initY = (T)0;
-                next_tix = 32;                                                    // drain PAD tiles
+                next_tix = 32 * kTile / C;                                        // drain PAD tiles
                 if ((uint32_t)cur < unit_nh) { const HapInfo<T> hi = hap_info[cur]; next_tix = hi.tix; initY = hi.initY; }
                 // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
                 Dbound = N::template mul<EXACT>(initY, PGAPM(0));

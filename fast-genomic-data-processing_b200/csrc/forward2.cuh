@@ -72,8 +72,19 @@ __host__ __device__ constexpr int pk_row_pairs(int K) { return (K + 1) / 2; }
 __host__ __device__ constexpr size_t pk_etab_bytes(int K) { return (size_t)6 * pk_row_pairs(K) * 32 * 16; }
 // per-warp table of the unit's haplotypes for the SEP handler: first tile, 2^120/H, number of tiles
 struct PkHapInfo { uint32_t tix; float initY; int32_t tiles; };
+// PHMM_PK_XCHG = 1: lanes exchange the row boundary through shared memory (STS.128 + WARPSYNC + LDS.128 per column) instead of
+// four shuffles + four selects. Per warp 2 (column parity) x 36 slots x 16 B {D pair, U pair}; a group of W lanes owns W+1 slots:
+// slot 0 = the matrix's row-0 boundary {Dbound, 0}, lane l writes slot l+1 and reads slot l.
+#ifndef PHMM_PK_LDG_END
+#define PHMM_PK_LDG_END 1
+#endif
+#ifndef PHMM_PK_XCHG
+#define PHMM_PK_XCHG 0
+#endif
+constexpr int kXSlots = 36;
+__host__ __device__ constexpr size_t pk_xbuf_bytes() { return PHMM_PK_XCHG ? (size_t)2 * kXSlots * 16 : 0; }
 __host__ __device__ constexpr size_t pk_smem_bytes(int K) {
-    return (size_t)(kThreads / 32) * (pk_etab_bytes(K) + sizeof(PkHapInfo) * kMaxUnitHaps);
+    return (size_t)(kThreads / 32) * (pk_etab_bytes(K) + pk_xbuf_bytes() + sizeof(PkHapInfo) * kMaxUnitHaps);
 }
 
 // per-row constants of one read row (ReadForPairHMM.cpp:72-80; stripeINITIALIZATION template.h:150-152)
@@ -129,7 +140,9 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
     const uint32_t n_units = a.n_units_dev ? *a.n_units_dev : a.n_units;
     extern __shared__ __align__(16) unsigned char pk_smem[];
     Quad *etab = reinterpret_cast<Quad *>(pk_smem + (size_t)warp * pk_etab_bytes(K)) + lane;
-    PkHapInfo *hap_info = reinterpret_cast<PkHapInfo *>(pk_smem + (size_t)(kThreads / 32) * pk_etab_bytes(K)) + warp * kMaxUnitHaps;
+    constexpr size_t kEtabAll = (size_t)(kThreads / 32) * pk_etab_bytes(K), kXbufAll = (size_t)(kThreads / 32) * pk_xbuf_bytes();
+    Quad *xrd = reinterpret_cast<Quad *>(pk_smem + kEtabAll + (size_t)warp * pk_xbuf_bytes()) + lane + seg;   // slot this lane reads
+    PkHapInfo *hap_info = reinterpret_cast<PkHapInfo *>(pk_smem + kEtabAll + kXbufAll) + warp * kMaxUnitHaps;
     const u64 cXY = pk2(a.u_xy_f, a.u_xy_f), cG = pk2(a.u_gapm_f, a.u_gapm_f);   // broadcast uniform operands
 
     for (;;) {
@@ -189,6 +202,9 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
         u64 Din[C], Uin[C];
 #pragma unroll
         for (int j = 0; j < C; ++j) { Din[j] = Uin[j] = zero2(); }
+#if PHMM_PK_XCHG
+        if (lane0) { xrd[0] = Quad{zero2(), zero2()}; xrd[kXSlots] = Quad{zero2(), zero2()}; }   // row-0 boundary slots
+#endif
 
         int cur = -1;
         uint32_t tix1 = 32 - sl;                       // lane l sees l PAD tiles, then [PAD.., SEP] (tile 31)
@@ -271,7 +287,12 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
                 // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
                 const float db = initY * a.u_gapm_f;
                 Dbound = pk2(db, db);
-                if (lane0) Din[C - 1] = Dbound;        // becomes Dprev of the next step's first column
+                if (lane0) {
+                    Din[C - 1] = Dbound;               // becomes Dprev of the next step's first column
+#if PHMM_PK_XCHG
+                    xrd[0] = Quad{Dbound, zero2()}; xrd[kXSlots] = Quad{Dbound, zero2()};
+#endif
+                }
             }
         };
 
@@ -280,7 +301,6 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
         // CLEAN instance, whose body is a single basic block.
         auto step = [&](auto dirty_tag) {
             constexpr bool DIRTY = decltype(dirty_tag)::value;
-            uint32_t tix2 = tix1 + 1;
             if (DIRTY) {
                 bool sep = false;
 #pragma unroll
@@ -290,10 +310,34 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
                     next_haplotype(target);
                     // a unit's haplotypes lie back to back in hapw, so the sequential guess is right except after the
                     // lead-in and before the drain
-                    if (target != tix1) { tix1 = target; w1 = __ldg(tiles + tix1); tix2 = tix1 + 1; }
+                    if (target != tix1) { tix1 = target; w1 = __ldg(tiles + tix1); }
                 }
             }
-            const Tile w2 = __ldg(tiles + tix2);       // two steps ahead: an L2 miss stays hidden
+#if !PHMM_PK_LDG_END
+            const Tile w2 = __ldg(tiles + tix1 + 1);   // two steps ahead: an L2 miss stays hidden
+#endif
+#if PHMM_PK_XCHG
+            static_assert(C == 2, "the exchange buffers alternate with the column parity");
+            u64 Dd = Dprev;
+#pragma unroll
+            for (int j = 0; j < C; ++j) {
+                const u64 Dsave = Din[j];              // lane above's D of (this tile, column j): diagonal of column j+1
+                column(tw_get(w, j), Dd, Uin[j]);
+                u64 Dout, Uout;
+                emit_down(Dout, Uout);
+                // exchange right away -- its latency hides behind the next column, the values are first read one step
+                // later. One barrier per exchange is enough: the buffer of parity j is rewritten only after the barrier of
+                // the other parity, which every lane passes after its own read below.
+                Quad *xb = xrd + j * kXSlots;
+                xb[1] = Quad{Dout, Uout};
+                __syncwarp();
+                const Quad in = xb[0];
+                Din[j] = in.x;
+                Uin[j] = in.y;
+                Dd = Dsave;
+            }
+            Dprev = Dd;           // D of the last column of the previous exchange: diagonal of the next step's first column
+#else
             u64 Dout[C], Uout[C];
 #pragma unroll
             for (int j = 0; j < C; ++j) {
@@ -307,7 +351,16 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const 
                 Din[j] = sel2(lane0, Dbound, dn);
                 Uin[j] = sel2(lane0, zero2(), un);
             }
-            w = w1; w1 = w2; tix1 = tix2;
+#endif
+            // rotate the tile queue at the END of the step: w is dead by now, so the load can land in a free register and
+            // nothing waits for it here; it is consumed two steps later (a full step of latency hiding)
+            w = w1;
+            ++tix1;
+#if PHMM_PK_LDG_END
+            w1 = __ldg(tiles + tix1);
+#else
+            w1 = w2;
+#endif
         };
         // haplotype boundary h enters lane 0 at the start of segment h and leaves lane W-1 W steps later; segment nh
         // is the drain

@@ -35,9 +35,11 @@ inline __host__ __device__ uint32_t unit_shape(uint32_t nh, uint32_t nreads, uin
 constexpr uint32_t kWordPad = 0xCA000000u;   // flagged, no haplotype change (pipeline fill/drain, alignment)
 constexpr uint32_t kWordSep = 0x8A000000u;   // flagged, column 0 of the next haplotype
 #ifndef PHMM_TILE
-#define PHMM_TILE 2
+#define PHMM_TILE 4
 #endif
-constexpr int kTile = PHMM_TILE;             // columns a lane advances per pipeline step
+constexpr int kTile = PHMM_TILE;             // alignment of the word layout = columns per step of the packed kernel
+constexpr int kScalarTile = 2;               // columns per step of the scalar kernels (forward.cuh)
+static_assert(PHMM_TILE % 2 == 0, "the scalar kernels walk the layout two columns at a time");
 constexpr int kMaxUnitHaps = 32;             // haplotypes streamed by one work unit (one per lane in the per-warp table)
 constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1] SEP, rest PAD
 constexpr int kMaxRowsPerLane = 8;           // K at W = 32: one warp covers reads up to 256 rows

@@ -130,7 +130,7 @@ class Engine:
     """One libpairhmm_cuda handle (one per host thread, like one PairHMM per Mutect2Cpp worker)."""
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
-                 chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False):
+                 chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
@@ -138,6 +138,7 @@ class Engine:
         cfg.dedup_reads = int(dedup_reads); cfg.pack_threads = int(pack_threads); cfg.chunk_cells = int(chunk_cells)
         cfg.reserved[0] = int(force_general)   # never pick the uniform-gcp kernels (testing)
         cfg.reserved[1] = int(lane_group)      # 8 | 16 | 32: force that lane-group width where it fits
+        cfg.reserved[3] = int(max_ctas_per_sm) # tuning: cap on resident CTAs per SM
         cfg.reserved[2] = int(scalar_uniform)  # scalar instead of packed (FFMA2) uniform-gcp kernels (testing)
         self.h = C.c_void_p()
         st = self.lib.pairhmm_cuda_create(C.byref(cfg), C.byref(self.h))

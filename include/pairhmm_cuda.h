@@ -92,6 +92,7 @@ typedef struct pairhmm_cuda_config {
     int32_t reserved[8];     /* [0] != 0: never use the uniform-gcp kernels (testing);               */
                              /* [1] = 8|16|32: force that lane-group width where it fits (tuning)    */
                              /* [2] != 0: scalar instead of packed (FFMA2) uniform-gcp kernels (testing) */
+                             /* [3] > 0: at most that many resident CTAs per SM (tuning)              */
 } pairhmm_cuda_config;
 
 typedef struct pairhmm_cuda_stats {
