@@ -164,7 +164,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
         if (bin_of_read(r.len, 32) < 0)
-            return fail(h, PAIRHMM_ERR_ARG, "read longer than 256 bases: not supported by this build");
+            return fail(h, PAIRHMM_ERR_ARG, "read longer than 384 bases: not supported by this build");
         uint32_t u = kNoRead;
         if (!table.empty()) {
             const uint64_t hv = hash_read(r);

@@ -42,7 +42,8 @@ constexpr int kScalarTile = 2;               // columns per step of the scalar k
 static_assert(PHMM_TILE % 2 == 0, "the scalar kernels walk the layout two columns at a time");
 constexpr int kMaxUnitHaps = 32;             // haplotypes streamed by one work unit (one per lane in the per-warp table)
 constexpr int kLeadWords = 64 * kTile;       // [0, 32*kTile-1) PAD, [32*kTile-1] SEP, rest PAD
-constexpr int kMaxRowsPerLane = 8;           // K at W = 32: one warp covers reads up to 256 rows
+constexpr int kMaxRowsPerLane = 12;          // K at W = 32: one warp covers reads up to 384 rows (kMaxReadLen)
+constexpr int kMaxReadLen = 32 * kMaxRowsPerLane;
 constexpr int kThreads = 128;                // 4 warps per CTA, one per SM sub-partition
 
 // words a haplotype of length H occupies in hapw (code words + alignment PADs + the [SEP, PAD..] tile)
@@ -102,10 +103,10 @@ struct FinalizeArgs {
 // (shuffles, boundary selects, loop) is amortised over more cells, at the price of registers.
 constexpr int kNumWidths = 3;
 constexpr int kWidths[kNumWidths] = {32, 16, 8};
-constexpr int kMaxK[kNumWidths] = {8, 12, 12};           // rows per lane limit per width
+constexpr int kMaxK[kNumWidths] = {kMaxRowsPerLane, 12, 12};   // rows per lane limit per width
 constexpr int tri(int k) { return k * (k + 1) / 2; }
-constexpr int kBinBase[kNumWidths + 1] = {0, tri(8), tri(8) + tri(12), tri(8) + tri(12) + tri(12)};
-constexpr int kNumBins = kBinBase[kNumWidths];           // 36 + 78 + 78 = 192
+constexpr int kBinBase[kNumWidths + 1] = {0, tri(12), tri(12) + tri(12), tri(12) + tri(12) + tri(12)};
+constexpr int kNumBins = kBinBase[kNumWidths];           // 78 + 78 + 78 = 234
 constexpr int kNumBinsW32 = kBinBase[1];
 
 inline int width_index(int W) { return W == 32 ? 0 : W == 16 ? 1 : W == 8 ? 2 : -1; }

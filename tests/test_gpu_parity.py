@@ -99,13 +99,13 @@ def test_uniform_gcp_kernels_equal_general_kernels():
 
 @pytest.mark.parametrize("lane_group", [0, 8, 16, 32])
 def test_every_bin(oracle, lane_group):
-    """one region per read length 1..256: every (lane-group width, rows-per-lane, last-row slot) kernel
+    """one region per read length 1..384: every (lane-group width, rows-per-lane, last-row slot) kernel
     instantiation runs, on the uniform-gcp path (gcp == 10 everywhere) and, with gcp perturbed, on the
     general path"""
     rng = np.random.default_rng(77)
     engine = fgdp_b200.Engine(lane_group=lane_group)
     for perturb in ((False, True) if lane_group in (0, 32) else (False,)):
-        lens = np.arange(1, 257)
+        lens = np.arange(1, 385)
         hls = [np.array([max(1, int(R * 1.3) + 7), 40]) for R in lens]
         parts = [synth.make_batch(1000 + int(R), [5], [hl], int(R), "clean", foreign_frac=0.4) for R, hl in zip(lens, hls)]
         b = parts[0].__class__(*[np.concatenate([getattr(p, f) for p in parts]) for f in
@@ -208,9 +208,9 @@ def test_empty_and_errors(engine):
     assert out.shape == (0, 1)
     with pytest.raises(fgdp_b200.PairHMMError):
         engine.initialize(10, 0)
-    r = tuple(np.full(300, v, np.uint8) for v in (65, 30, 45, 45, 10))
+    r = tuple(np.full(385, v, np.uint8) for v in (65, 30, 45, 45, 10))
     with pytest.raises(fgdp_b200.PairHMMError):
-        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 256 rows: refused loudly, not faked
+        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 384 rows: refused loudly, not faked
     z = tuple(np.zeros(0, np.uint8) for _ in range(5))
     out, resc = engine.compute([z], [np.frombuffer(b"ACGT", np.uint8)])
     assert np.isneginf(out).all() and resc.all()
@@ -225,3 +225,30 @@ def test_resident_replay_matches(engine, oracle):
         assert ms > 0 and ms_f > 0
     got, gresc = engine.resident_fetch()
     assert_parity(got, gresc, want, wresc, what="resident")
+
+
+def test_long_reads_double_and_exact_paths(oracle):
+    """reads of 257..384 bases (rows-per-lane 9..12 at one read per warp): FP32 exact, FP64-only and rescue paths"""
+    rng = np.random.default_rng(5)
+    lens = [257, 288, 300, 301, 320, 351, 352, 383, 384]
+    parts = [synth.make_batch(4000 + R, [6], [np.array([R + 40, R - 30, 500])], R, "lowq" if i % 2 else "clean", foreign_frac=0.5)
+             for i, R in enumerate(lens)]
+    for p in parts:
+        flat = p.as_flat()
+        want, wresc, _ = oracle.compute(flat, threads=4)
+        for kw in ({}, {"exact_fp32": True}):
+            e = fgdp_b200.Engine(**kw)
+            try:
+                got, gresc = e.compute_batch(p)
+            finally:
+                e.close()
+            assert_parity(got, gresc, want, wresc, what="long reads %s %s" % (p.name, kw))
+        e = fgdp_b200.Engine(use_double=True)
+        try:
+            got_d, resc_d = e.compute_batch(p)
+        finally:
+            e.close()
+        assert resc_d.all()
+        m = wresc.astype(bool)                       # where the reference also took the double path: same numbers
+        if m.any():
+            assert np.abs(got_d[m] - want[m]).max() < 1e-9
