@@ -430,7 +430,10 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     std::memcpy(&a.u_xy_bits, &a.u_xy_f, sizeof a.u_xy_bits);
     a.u_xy_d = t.ph2pr_d[gc]; a.u_gapm_d = 1.0 - t.ph2pr_d[gc];
     const bool all_double = h->cfg.use_double != 0;
-    const Variant vf = s.float_variant, vd = Variant::F64_GEN;
+    // FP64 pass: the wide kernel when the chunk's gap-continuation penalty is uniform (what lets the FP32 pass use its
+    // packed or scalar uniform kernel), else the general scalar one
+    const Variant vf = s.float_variant;
+    const Variant vd = (s.uniform_gcp && !h->cfg.reserved[2] && !h->cfg.reserved[0] && !h->cfg.exact_fp32) ? Variant::F64_PK : Variant::F64_GEN;
     auto grid_for = [&](Variant v, int bin, uint64_t work_items) {
         const uint64_t full = (uint64_t)h->sm_count * (uint64_t)blocks_for(h, v, bin);
         return (int)std::min<uint64_t>(full, (work_items + 3) / 4);
@@ -438,9 +441,6 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     if (all_double) CU(h, cudaEventRecord(s.ev_fwd_done, st));
     if (!all_double) {
         a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
-        a.rescue_units = s.d_rescue.p;
-        a.rescue_base = s.d_counters.p + kRescueBaseDev;
-        a.rescue_count = s.d_counters.p + kRescueCount;
         for (int b = 0; b < kNumBins; ++b) {
             const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
             if (!n) continue;
@@ -454,10 +454,14 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f};
         CU(h, launch_finalize(f, st));
         if (s.n_upairs) h->stats.kernel_launches += 1;
+        RescueScanArgs r{s.d_units.p, s.bin_start[kNumBins], s.d_reads.p, s.d_fres.p, s.d_rescue.p,
+                         s.d_counters.p + kRescueBaseDev, s.d_counters.p + kRescueCount};
+        CU(h, launch_rescue_scan(r, st));
+        if (r.n_units) h->stats.kernel_launches += 1;
     }
     CU(h, cudaEventRecord(s.ev_float_done, st));
     a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
-    a.rescue_units = nullptr; a.rescue_base = nullptr; a.rescue_count = nullptr;
+    a.rescue_filter = all_double ? 0u : 1u;
     for (int b = 0; b < kNumBinsW32; ++b) {
         int W, K, KL; bin_shape(b, W, K, KL);
         a.queue = s.d_counters.p + kQueueD + b;

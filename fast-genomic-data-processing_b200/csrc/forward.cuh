@@ -77,7 +77,8 @@ __device__ __forceinline__ uint32_t tw_or(const uint4 &t) { return t.x | t.y | t
 
 // per-warp table of the unit's haplotypes (first tile, 2^s/H), filled once per unit so that the SEP
 // handler -- which runs divergently, one lane at a time -- needs no global loads and no division
-template <typename T> struct HapInfo { uint32_t tix; T initY; };
+// idx = the haplotype's position in the unit (rescue units sweep only the underflowed ones, see below)
+template <typename T> struct HapInfo { uint32_t tix; uint32_t idx; T initY; };
 
 // minimum resident CTAs per SM requested from ptxas (caps registers): the FP32 kernels are issue-bound
 // and want >= 5-6 warps per scheduler; the FP64 kernels need their registers
@@ -115,7 +116,8 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
         u = __shfl_sync(kFull, u, 0);
         if (u >= n_units) break;
         const DevUnit unit = a.units[u];
-        const uint32_t unit_nh = unit.shape & 0xffu, unit_nreads = (unit.shape >> 8) & 0xffu;
+        uint32_t unit_nh = unit.shape & 0xffu;
+        const uint32_t unit_nreads = (unit.shape >> 8) & 0xffu;
         const bool seg_valid = (uint32_t)seg < unit_nreads;   // a partial unit leaves groups without a read: they
         const uint32_t my_read = unit.read + (seg_valid ? seg : 0);   // recompute read 0 and emit nothing
         const uint32_t my_out = unit.out + (uint32_t)seg * (unit.shape >> 16);
@@ -166,10 +168,19 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
         // pipeline steps: W (fill) + sum over haplotypes of their tile count; hap table for the SEP handler
         int steps = 0;
         __syncwarp();                                  // previous unit's readers are done with hap_info
-        if ((uint32_t)lane < unit_nh) {                // nh <= kMaxUnitHaps == 32 (host guarantees)
-            const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
-            steps = (int)(hap_tiles(hp.len) * (kTile / C));
-            hap_info[lane] = HapInfo<T>{hp.off / C, N::div(N::init_const(), (T)hp.len)};   // template.h:115
+        {
+            bool keep = (uint32_t)lane < unit_nh;          // nh <= kMaxUnitHaps == 32 (host guarantees)
+            // FP64 launch over rescue units: a unit names the read's whole haplotype run, only the pairs whose FP32 sum
+            // fell below the reference's threshold (IntelPairHmm.cc:342) are swept, back to back
+            if constexpr (sizeof(T) == 8) if (a.rescue_filter && keep) keep = a.fres[unit.out + lane] < 1e-28f;
+            const uint32_t km = __ballot_sync(kFull, keep);
+            unit_nh = (uint32_t)__popc(km);
+            if (keep) {
+                const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
+                steps = (int)(hap_tiles(hp.len) * (kTile / C));
+                hap_info[__popc(km & ((1u << lane) - 1u))] =
+                    HapInfo<T>{hp.off / C, (uint32_t)lane, N::div(N::init_const(), (T)hp.len)};   // template.h:115
+            }
         }
         __syncwarp();
 #pragma unroll
@@ -245,17 +256,10 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
                     const T r = N::template add<EXACT>(sumM, sumX);              // template.h:339-343
                     if constexpr (sizeof(T) == 4) {
                         a.fres[my_out + cur] = r;
-                        if (r < 1e-28f) {                                          // IntelPairHmm.cc:342
-                            // the FP64 kernels run at W = 32: queue the pair on that bin's list
-                            const int k32 = (rr.len + 31) >> 5;
-                            const int bin = k32 * (k32 - 1) / 2 + (rr.len - 1) % k32;
-                            const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
-                            a.rescue_units[slot] = DevUnit{my_read, unit.hap_list + (uint32_t)cur, unit_shape(1u, 1u, 0u),
-                                                           my_out + (uint32_t)cur};
-                        }
                     } else {
-                        a.out[my_out + cur] = log10(r) - a.log10_init_d;          // IntelPairHmm.cc:344
-                        a.flag[my_out + cur] = 1;
+                        const uint32_t o = my_out + hap_info[cur].idx;
+                        a.out[o] = log10(r) - a.log10_init_d;                      // IntelPairHmm.cc:344
+                        a.flag[o] = 1;
                     }
                 }
                 ++cur;

@@ -1,4 +1,4 @@
-// Auxiliary kernels (haplotype byte -> column-word expansion, FP32 result finalisation) and the
+// Auxiliary kernels (haplotype byte -> column-word expansion, FP32 result finalisation, rescue-unit scan) and the
 // dispatch from (variant, K, KL) to the forward_kernel instantiations of inst_*.cu. The forward kernel
 // itself is in forward.cuh.
 #include "forward2.cuh"
@@ -39,6 +39,26 @@ __global__ void finalize_kernel(const FinalizeArgs a) {
     a.flag[i] = 0;
 }
 
+// One thread per (FP32 work unit, read of the unit): any pair of the read below the threshold -> one FP64 unit.
+__global__ void rescue_scan_kernel(const RescueScanArgs a) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t u = t / kMaxUnitReads, j = t % kMaxUnitReads;
+    if (u >= a.n_units) return;
+    const DevUnit unit = a.units[u];
+    const uint32_t nh = unit.shape & 0xffu, nreads = (unit.shape >> 8) & 0xffu, stride = unit.shape >> 16;
+    if (j >= nreads) return;
+    const uint32_t out = unit.out + j * stride;
+    bool any = false;
+    for (uint32_t i = 0; i < nh; ++i) any |= a.fres[out + i] < 1e-28f;
+    if (!any) return;
+    const int len = a.reads[unit.read + j].len;
+    if (len < 1) return;
+    const int k32 = (len + 31) >> 5;                   // the FP64 kernels run at W = 32
+    const int bin = k32 * (k32 - 1) / 2 + (len - 1) % k32;
+    const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
+    a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list, unit_shape(nh, 1u, 0u), out};
+}
+
 }  // namespace
 
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,
@@ -61,6 +81,13 @@ bool forward_available(Variant v, int W, int K) { return find_unit(v, W, K) != n
 cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid, cudaStream_t st) {
     const InstUnit *u = find_unit(v, W, K);
     return u ? u->launch(K, KL, a, grid, st) : cudaErrorInvalidValue;
+}
+
+cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st) {
+    if (a.n_units == 0) return cudaSuccess;
+    const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
+    rescue_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
 }
 
 int forward_blocks_per_sm(Variant v, int W, int K, int KL) {

@@ -78,16 +78,30 @@ struct KernelArgs {
     float u_xy_f, u_gapm_f;
     uint32_t u_xy_bits;           // bit pattern of u_xy_f again (packed kernel: source of the per-column Y coefficient)
     double u_xy_d, u_gapm_d;
-    // FP32 pass outputs
+    // FP32 pass output
     float *fres;                  // scaled forward sum per unique pair
-    DevUnit *rescue_units;        // pairs with fres < 1e-28f are appended to the list of the read's W=32 bin:
-    const uint32_t *rescue_base;  //   rescue_units[rescue_base[bin] + atomicAdd(&rescue_count[bin], 1)]
-    uint32_t *rescue_count;
     // FP64 pass outputs
     double *out;                  // log10 likelihood
     uint8_t *flag;                // 1 = went through the FP64 kernel
     double log10_init_d;          // log10(2^1020), host libm (Context.h:143)
+    uint32_t rescue_filter;       // FP64 launches over rescue units: a unit names a read and its whole haplotype run, only
+                                  // the pairs with fres < 1e-28f are swept
 };
+
+// Between the passes: every read with at least one pair below the reference's threshold (fres < 1e-28f,
+// IntelPairHmm.cc:342) becomes ONE unit of the FP64 pass -- the read against its unit's whole haplotype run, the FP64
+// kernel sweeps only the underflowed haplotypes (KernelArgs::rescue_filter). Units go to the list of the read's W = 32
+// bin: rescue_units[rescue_base[bin] + atomicAdd(&rescue_count[bin], 1)].
+struct RescueScanArgs {
+    const DevUnit *units;         // every FP32 work unit of the chunk
+    uint32_t n_units;
+    const DevRead *reads;
+    const float *fres;
+    DevUnit *rescue_units;
+    const uint32_t *rescue_base;
+    uint32_t *rescue_count;
+};
+constexpr int kMaxUnitReads = 8;  // reads of one work unit: 2 * 32 / 8 (packed kernel, 8-lane groups)
 
 struct FinalizeArgs {
     const float *fres;
@@ -129,9 +143,10 @@ inline void bin_shape(int bin, int &W, int &K, int &KL) {
 
 // F32_PK: packed (two reads per lane, FFMA2) uniform-gcp kernel of forward2.cuh -- the production FP32 path;
 // F32_UG: scalar uniform-gcp kernel (W = 32 only; kept as the cross-check of the packed one);
-// F32_GEN / F32_EXACT / F64_GEN: per-row gap-continuation registers, W = 32 only.
-enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3, F32_PK = 4 };
-constexpr int kNumVariants = 5;
+// F32_GEN / F32_EXACT / F64_GEN: per-row gap-continuation registers, W = 32 only;
+// F64_PK: the wide kernel of forward2.cuh on doubles (uniform gcp, W = 32) -- the production FP64 rescue path.
+enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3, F32_PK = 4, F64_PK = 5 };
+constexpr int kNumVariants = 6;
 // reads swept by one warp
 inline int reads_per_warp(Variant v, int W) { return (v == Variant::F32_PK ? 2 : 1) * (32 / W); }
 
@@ -140,6 +155,7 @@ cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off,
                              uint32_t n_haps, uint32_t *hapw, cudaStream_t st);
 cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
+cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
 int forward_blocks_per_sm(Variant v, int W, int K, int KL);
 // whether (variant, W, K) was instantiated (the general / exact / FP64 kernels exist at W = 32 only)
