@@ -43,6 +43,7 @@ template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; 
 void Slot::release() {
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
     h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release(); h_rescue_base.release();
+    h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
     d_rescue.release(); d_fres.release(); d_out.release();
@@ -331,6 +332,8 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
     RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
     RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+    s.ep_on = h->ep_on; s.ep = h->ep;
+    if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
     // pass B: copy bytes, fill descriptors and units
@@ -345,6 +348,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
             std::memcpy(d + 4 * s.plane, r.gcp, r.len);
             s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
+            if (s.ep_on) s.h_rows.p[p.first_uniq + j] = RowInfo{p.upair_off + j * (uint32_t)rv.n_haps, (uint32_t)rv.n_haps};
             ro += (uint64_t)r.len;
         }
         // work units: per bin run, 32/W consecutive reads per warp, one unit per haplotype group
@@ -393,6 +397,10 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, cudaMemcpyAsync(s.d_haplist.p, s.h_haplist.p, sizeof(uint32_t) * s.n_haplist, cudaMemcpyHostToDevice, st));
     }
     if (n_units) CU(h, cudaMemcpyAsync(s.d_units.p, s.h_units.p, sizeof(DevUnit) * n_units, cudaMemcpyHostToDevice, st));
+    if (s.ep_on && s.n_uniq) {
+        CU(h, cudaMemcpyAsync(s.d_rows.p, s.h_rows.p, sizeof(RowInfo) * s.n_uniq, cudaMemcpyHostToDevice, st));
+        h->stats.h2d_bytes += sizeof(RowInfo) * (uint64_t)s.n_uniq;
+    }
     CU(h, launch_prep_haps(s.d_hapbytes.p, s.d_hapoff.p, s.d_haps.p, s.n_haps, s.d_hapw.p, st));
     h->stats.kernel_launches += 1;
     h->stats.h2d_bytes += s.plane * 5 + sizeof(DevRead) * (uint64_t)s.n_uniq + s.hap_bytes +
@@ -482,6 +490,12 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, launch_forward(vd, W, K, KL, a, grid, st));
         h->stats.kernel_launches += 1;
     }
+    if (s.ep_on && s.n_uniq) {       // fused per-read epilogue on the finished matrix
+        EpilogueArgs e{s.d_out.p, s.d_rows.p, s.d_reads.p, s.d_summ.p, s.n_uniq, s.ep.likelihood_cap, s.ep.max_error_per_base,
+                       std::log(10.0), std::isinf(s.ep.likelihood_cap) ? 0 : 1, s.ep.natural_log ? 1 : 0};
+        CU(h, launch_epilogue(e, st));
+        h->stats.kernel_launches += 1;
+    }
     CU(h, cudaEventRecord(s.ev_end, st));
     h->prev_end = s.ev_end;
     return PAIRHMM_OK;
@@ -497,6 +511,10 @@ int download_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, cudaMemcpyAsync(s.h_out.p, s.d_out.p, sizeof(double) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
         CU(h, cudaMemcpyAsync(s.h_flag.p, s.d_flag.p, s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
         h->stats.d2h_bytes += (sizeof(double) + 1) * (uint64_t)s.n_upairs;
+    }
+    if (s.ep_on && s.n_uniq) {
+        CU(h, cudaMemcpyAsync(s.h_summ.p, s.d_summ.p, sizeof(phmm_read_summary) * s.n_uniq, cudaMemcpyDeviceToHost, s.stream));
+        h->stats.d2h_bytes += sizeof(phmm_read_summary) * (uint64_t)s.n_uniq;
     }
     return PAIRHMM_OK;
 }
@@ -529,8 +547,13 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
             if (u == kNoRead) {   // zero-length read: no alignment exists
                 for (size_t q = 0; q < nh; ++q) o[q] = -std::numeric_limits<double>::infinity();
                 if (f) std::memset(f, 1, nh);
+                if (s.ep_on && rv.summ) {
+                    const double ninf = -std::numeric_limits<double>::infinity();
+                    rv.summ[r] = phmm_read_summary{ninf, ninf, nh ? 0 : -1, 1, {0, 0, 0}};
+                }
                 continue;
             }
+            if (s.ep_on && rv.summ) rv.summ[r] = s.h_summ.p[p.first_uniq + u];
             const size_t src = (size_t)p.upair_off + (size_t)u * nh;
             std::memcpy(o, s.h_out.p + src, nh * sizeof(double));
             if (f) std::memcpy(f, s.h_flag.p + src, nh);
@@ -715,7 +738,9 @@ int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_r
     return pairhmm_cuda_wait(h, t);
 }
 
-int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions) {
+// the batch pipeline; summaries (nullable) = per region the [n_reads] epilogue results, used when h->ep_on
+static int compute_batch_impl(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions,
+                              phmm_read_summary *const *summaries) {
     if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
     auto t0 = clk::now();
     CU(h, cudaSetDevice(h->device));
@@ -748,7 +773,8 @@ int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *region
             for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
             const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
             if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_limit || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
-            views.push_back(RegionView{r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out});
+            views.push_back(RegionView{r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out,
+                                       summaries ? summaries[i] : nullptr});
             cells += (int64_t)(rl * hl); pairs += p; rbytes += rl;
             ++i;
         }
@@ -767,6 +793,43 @@ int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *region
     h->stats.calls += 1;
     h->stats.host_ms_total += ms_since(t0);
     return status;
+}
+
+int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions) {
+    return compute_batch_impl(h, regions, n_regions, nullptr);
+}
+
+static int check_epilogue(pairhmm_cuda_handle *h, const pairhmm_cuda_epilogue *ep) {
+    // AlleleLikelihoods.h:373: the cap is a log10 difference below the best allele, i.e. negative; -inf switches it off
+    if (!ep || std::isnan(ep->likelihood_cap) || !(ep->likelihood_cap < 0.0))
+        return fail(h, PAIRHMM_ERR_ARG, "epilogue: likelihood_cap must be negative (or -inf)");
+    if (std::isnan(ep->max_error_per_base) || ep->max_error_per_base < 0.0)
+        return fail(h, PAIRHMM_ERR_ARG, "epilogue: max_error_per_base must be >= 0");
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_compute_batch_normalized(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions,
+                                          const pairhmm_cuda_epilogue *ep, phmm_read_summary *const *summary_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    int st = check_epilogue(h, ep);
+    if (st != PAIRHMM_OK) return st;
+    // chunks of earlier plain submits must not pick the epilogue up: retire them first
+    for (int si = 0; si < 2; ++si)
+        if (h->slots[si].busy) { CU(h, cudaSetDevice(h->device)); st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    h->ep_on = true; h->ep = *ep;
+    st = compute_batch_impl(h, regions, n_regions, summary_out);
+    h->ep_on = false;
+    return st;
+}
+
+int pairhmm_cuda_compute_normalized(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
+                                    int n_haps, const pairhmm_cuda_epilogue *ep, double *log10_out, uint8_t *rescued_out,
+                                    phmm_read_summary *summary_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (n_reads == 0) return check_epilogue(h, ep);   // VectorLoglessPairHMM.cpp:46-47
+    const phmm_region r{reads, n_reads, haps, n_haps, log10_out, rescued_out};
+    phmm_read_summary *const sp = summary_out;
+    return pairhmm_cuda_compute_batch_normalized(h, &r, 1, ep, summary_out ? &sp : nullptr);
 }
 
 }  // extern "C"
@@ -830,6 +893,28 @@ int pairhmm_cuda_compute_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases,
         if ((int64_t)r.n_reads * r.n_haps > 0 && !r.log10_out) return fail(h, PAIRHMM_ERR_ARG, "null output");
     h->stats.host_ms_total += ms_since(t0);   // view building counts as host time of the call
     return pairhmm_cuda_compute_batch(h, v.regions.data(), n_regions);
+}
+
+int pairhmm_cuda_compute_flat_normalized(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                         const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                                         const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                         const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                                         int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                                         int64_t n_regions, const pairhmm_cuda_epilogue *ep, double *log10_out,
+                                         uint8_t *rescued_out, phmm_read_summary *summary_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    static thread_local FlatViews v;
+    int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
+                              hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, log10_out, rescued_out);
+    if (st != PAIRHMM_OK) return st;
+    for (auto &r : v.regions)
+        if ((int64_t)r.n_reads * r.n_haps > 0 && !r.log10_out) return fail(h, PAIRHMM_ERR_ARG, "null output");
+    std::vector<phmm_read_summary *> sp;
+    if (summary_out) {
+        sp.resize((size_t)n_regions);
+        for (int64_t r = 0; r < n_regions; ++r) sp[r] = summary_out + reg_read_start[r];
+    }
+    return pairhmm_cuda_compute_batch_normalized(h, v.regions.data(), n_regions, ep, summary_out ? sp.data() : nullptr);
 }
 
 int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,

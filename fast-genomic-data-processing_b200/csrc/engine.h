@@ -29,6 +29,7 @@ struct RegionView {
     const phmm_read *reads; int32_t n_reads;
     const phmm_hap *haps; int32_t n_haps;
     double *out; uint8_t *resc;
+    phmm_read_summary *summ;          // per-read epilogue results (nullable; only with an active epilogue)
 };
 
 // Sizes/offsets of one region inside a packed chunk (filled by pass A + prefix sums).
@@ -63,6 +64,8 @@ struct Slot {
     PinnedBuf<uint32_t> h_haplist;
     PinnedBuf<DevUnit> h_units;
     PinnedBuf<double> h_out;
+    PinnedBuf<RowInfo> h_rows;        // epilogue: row of every unique read in the result matrix
+    PinnedBuf<phmm_read_summary> h_summ;
     // device
     DevBuf<uint8_t> d_rd, d_hapbytes, d_flag;
     DevBuf<DevRead> d_reads;
@@ -72,6 +75,8 @@ struct Slot {
     DevBuf<DevUnit> d_units, d_rescue;
     DevBuf<float> d_fres;
     DevBuf<double> d_out;
+    DevBuf<RowInfo> d_rows;
+    DevBuf<phmm_read_summary> d_summ;
     // shape of the packed chunk
     std::vector<RegionView> regions;
     std::vector<RegionPlan> plans;
@@ -86,6 +91,8 @@ struct Slot {
     uint8_t gcp_value = 0;
     uint64_t cells = 0, pairs = 0, reads_in = 0;
     bool busy = false;
+    bool ep_on = false;               // this chunk runs the fused epilogue (pairhmm_cuda_compute_*_normalized)
+    pairhmm_cuda_epilogue ep{};
     void release();
 };
 
@@ -109,4 +116,6 @@ struct pairhmm_cuda_handle {
     int64_t slot_ticket[2] = {0, 0};
     cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk (kernels of the next one wait on it)
     bool resident_loaded = false;
+    bool ep_on = false;               // set for the duration of a *_normalized call
+    pairhmm_cuda_epilogue ep{};
 };

@@ -59,6 +59,43 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list, unit_shape(nh, 1u, 0u), out};
 }
 
+// Per-read epilogue. The operations and their order are those of the reference's host code, so that the result equals
+// oracle_epilogue() (oracle/pairhmm_oracle.c) bit for bit on the same input matrix.
+__global__ void epilogue_kernel(const EpilogueArgs a) {
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= a.n) return;
+    const RowInfo row = a.rows[u];
+    double *v = a.out + row.off;
+    const double ninf = -__longlong_as_double(0x7ff0000000000000ll);
+    phmm_read_summary s;
+    s.best = ninf; s.second_best = ninf; s.best_hap = -1; s.poorly_modeled = 1; s.pad[0] = s.pad[1] = s.pad[2] = 0;
+    if (row.nh) {
+        // searchBestAllele(canBeReference = true, priorities = null), AlleleLikelihoods.h:92-117
+        double best = v[0], second = ninf;
+        int bi = 0;
+        for (uint32_t i = 1; i < row.nh; ++i) {
+            const double c = v[i];
+            if (c > best) { second = best; best = c; bi = (int)i; }
+            else if (c > second) second = c;
+        }
+        // normalizeLikelihoodsPerEvidence, AlleleLikelihoods.h:150-166 (skipped for <= 1 allele or an infinite cap, :375-380)
+        if (a.do_cap && row.nh > 1) {
+            const double worst = best + a.cap;
+            for (uint32_t i = 0; i < row.nh; ++i) if (v[i] < worst) v[i] = worst;
+            if (second < worst) second = worst;
+        }
+        // filterPoorlyModeledEvidence's predicate, AlleleLikelihoods.h:413 with PairHMMLikelihoodCalculationEngine.cpp:294-299
+        const double max_err = fmin(2.0, ceil((double)a.reads[u].len * a.err_rate));
+        s.poorly_modeled = best < max_err * -4.0 ? 1 : 0;
+        if (a.natural_log) {                                // switchToNaturalLog, AlleleLikelihoods.h:462-476
+            for (uint32_t i = 0; i < row.nh; ++i) v[i] = __dmul_rn(v[i], a.ln10);
+            best = __dmul_rn(best, a.ln10); second = __dmul_rn(second, a.ln10);
+        }
+        s.best = best; s.second_best = second; s.best_hap = bi;
+    }
+    a.summ[u] = s;
+}
+
 }  // namespace
 
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,
@@ -87,6 +124,12 @@ cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st) {
     if (a.n_units == 0) return cudaSuccess;
     const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
     rescue_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st) {
+    if (a.n == 0) return cudaSuccess;
+    epilogue_kernel<<<(a.n + 127) / 128, 128, 0, st>>>(a);
     return cudaGetLastError();
 }
 

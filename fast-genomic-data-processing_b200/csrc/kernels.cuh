@@ -20,6 +20,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "../../include/pairhmm_cuda.h"
+
 namespace phmm {
 
 struct DevRead { uint32_t off; int32_t len; };
@@ -103,6 +105,21 @@ struct RescueScanArgs {
 };
 constexpr int kMaxUnitReads = 8;  // reads of one work unit: 2 * 32 / 8 (packed kernel, 8-lane groups)
 
+// Fused per-read epilogue (include/pairhmm_cuda.h, pairhmm_cuda_epilogue): one thread per unique read normalises its
+// row of the result matrix in place and writes the read's summary.
+struct RowInfo { uint32_t off, nh; };      // first unique-pair index of the read's row, haplotypes in the row
+struct EpilogueArgs {
+    double *out;                  // result matrix, rows of nh doubles
+    const RowInfo *rows;
+    const DevRead *reads;
+    phmm_read_summary *summ;
+    uint32_t n;                   // unique reads
+    double cap;                   // likelihood_cap
+    double err_rate;              // max_error_per_base
+    double ln10;                  // std::log(10) of the host libm
+    int32_t do_cap, natural_log;
+};
+
 struct FinalizeArgs {
     const float *fres;
     double *out;
@@ -156,6 +173,7 @@ cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off,
 cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
+cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
 int forward_blocks_per_sm(Variant v, int W, int K, int KL);
 // whether (variant, W, K) was instantiated (the general / exact / FP64 kernels exist at W = 32 only)

@@ -18,6 +18,7 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_wait", "pairhmm_cuda_compute_batch", "pairhmm_cuda_compute_flat", "pairhmm_cuda_compute_pairs",
     "pairhmm_cuda_resident_load", "pairhmm_cuda_resident_run", "pairhmm_cuda_resident_fetch",
     "pairhmm_cuda_resident_fetch_raw",
+    "pairhmm_cuda_compute_normalized", "pairhmm_cuda_compute_batch_normalized", "pairhmm_cuda_compute_flat_normalized",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
 ]
 MM_COUNT = 8256
@@ -62,6 +63,21 @@ class PhmmRegion(C.Structure):
                 ("n_haps", C.c_int32), ("log10_out", C.c_void_p), ("rescued_out", C.c_void_p)]
 
 
+class Epilogue(C.Structure):
+    """pairhmm_cuda_epilogue: normalizeLikelihoods cap, filterPoorlyModeledEvidence rate, switchToNaturalLog"""
+    _fields_ = [("likelihood_cap", C.c_double), ("max_error_per_base", C.c_double), ("natural_log", C.c_int32),
+                ("reserved", C.c_int32)]
+
+    def __init__(self, likelihood_cap=-4.5, max_error_per_base=0.02, natural_log=False):
+        super().__init__(float(likelihood_cap), float(max_error_per_base), 1 if natural_log else 0, 0)
+
+
+# phmm_read_summary as a numpy record
+SUMMARY_DTYPE = np.dtype([("best", np.float64), ("second_best", np.float64), ("best_hap", np.int32),
+                          ("poorly_modeled", np.uint8), ("pad", np.uint8, (3,))])
+assert SUMMARY_DTYPE.itemsize == 24
+
+
 def lib_path():
     # PAIRHMM_CUDA_LIB selects another build of the same library (kernel-variant experiments)
     return os.environ.get("PAIRHMM_CUDA_LIB") or os.path.join(_HERE, "libpairhmm_cuda.so")
@@ -95,6 +111,10 @@ def load_library():
     lib.pairhmm_cuda_compute_flat.argtypes = [vp] + flat + [vp, vp]
     lib.pairhmm_cuda_compute_pairs.argtypes = [vp, C.POINTER(PhmmRead), i32, C.POINTER(PhmmHap), i32, vp, vp,
                                                C.c_size_t, vp, vp]
+    lib.pairhmm_cuda_compute_normalized.argtypes = [vp, C.POINTER(PhmmRead), i32, C.POINTER(PhmmHap), i32,
+                                                    C.POINTER(Epilogue), vp, vp, vp]
+    lib.pairhmm_cuda_compute_batch_normalized.argtypes = [vp, C.POINTER(PhmmRegion), i64, C.POINTER(Epilogue), vp]
+    lib.pairhmm_cuda_compute_flat_normalized.argtypes = [vp] + flat + [C.POINTER(Epilogue), vp, vp, vp]
     lib.pairhmm_cuda_resident_load.argtypes = [vp] + flat
     lib.pairhmm_cuda_resident_run.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.pairhmm_cuda_resident_fetch.argtypes = [vp, vp, vp]
@@ -226,6 +246,26 @@ class Engine:
         resc = np.zeros(n, np.uint8) if resc is None else resc
         self._check(self.lib.pairhmm_cuda_compute_flat(self.h, *self._flat_args(b), out.ctypes.data, resc.ctypes.data))
         return out, resc
+
+    def compute_normalized(self, reads, haps, epilogue=None):
+        """one region through the fused epilogue -> (normalised matrix, rescued, per-read summary records)"""
+        ep = epilogue or Epilogue()
+        ra, ha, keep = self._structs(reads, haps)
+        out = np.zeros((len(reads), len(haps)), np.float64)
+        resc = np.zeros((len(reads), len(haps)), np.uint8)
+        summ = np.zeros(len(reads), SUMMARY_DTYPE)
+        self._check(self.lib.pairhmm_cuda_compute_normalized(self.h, ra, len(reads), ha, len(haps), C.byref(ep),
+                                                             out.ctypes.data, resc.ctypes.data, summ.ctypes.data))
+        return out, resc, summ
+
+    def compute_batch_normalized(self, b, epilogue=None):
+        """b: synth.RegionBatch -> (normalised[n_pairs], rescued[n_pairs], summary[n_reads])"""
+        ep = epilogue or Epilogue()
+        out = np.zeros(b.n_pairs, np.float64); resc = np.zeros(b.n_pairs, np.uint8)
+        summ = np.zeros(b.n_reads, SUMMARY_DTYPE)
+        self._check(self.lib.pairhmm_cuda_compute_flat_normalized(self.h, *self._flat_args(b), C.byref(ep),
+                                                                  out.ctypes.data, resc.ctypes.data, summ.ctypes.data))
+        return out, resc, summ
 
     def resident_load(self, b):
         self._check(self.lib.pairhmm_cuda_resident_load(self.h, *self._flat_args(b)))

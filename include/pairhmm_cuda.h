@@ -167,6 +167,48 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
  * compute_full_prob_avxs (avx-pairhmm-template.h:204-345). */
 int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n);
 
+/* ---- fused per-read epilogue ---------------------------------------------------------
+ * What PairHMMLikelihoodCalculationEngine::computeReadLikelihoods does to the matrix right after the PairHMM
+ * (PairHMMLikelihoodCalculationEngine.cpp:93-94) and Mutect2Engine does before genotyping (Mutect2Engine.cpp:224),
+ * done on the device on the rows of the result matrix before they are copied back:
+ *   1. AlleleLikelihoods::normalizeLikelihoods(likelihood_cap)  (AlleleLikelihoods.h:372-390,150-166): per read, every
+ *      value below best + likelihood_cap is raised to it (skipped for one haplotype or an infinite cap);
+ *   2. the predicate of filterPoorlyModeledEvidence (AlleleLikelihoods.h:404-419): best < log10MinTrueLikelihood(read)
+ *      = min(2, ceil(len * max_error_per_base)) * -4  (PairHMMLikelihoodCalculationEngine.cpp:294-299) -- reported
+ *      as a flag, the caller removes the evidence;
+ *   3. searchBestAllele(canBeReference = true, no priorities) on the normalised row (AlleleLikelihoods.h:92-148);
+ *   4. optionally switchToNaturalLog (AlleleLikelihoods.h:462-476): every value * std::log(10). */
+typedef struct pairhmm_cuda_epilogue {
+    double likelihood_cap;      /* log10globalReadMismappingRate, < 0 (default -4.5 = phred 45); -inf = no cap      */
+    double max_error_per_base;  /* EXPECTED_ERROR_RATE_PER_BASE = 0.02 (PairHMMLikelihoodCalculationEngine.cpp:20)  */
+    int32_t natural_log;        /* 1 = matrix, best and second_best returned as natural logs                         */
+    int32_t reserved;
+} pairhmm_cuda_epilogue;
+
+typedef struct phmm_read_summary {
+    double best;                /* likelihood of the best haplotype                                                  */
+    double second_best;         /* of the runner-up on the normalised row (-inf with one haplotype)                  */
+    int32_t best_hap;           /* index of the best haplotype (first maximum)                                       */
+    uint8_t poorly_modeled;     /* 1 = filterPoorlyModeledEvidence would remove this read                            */
+    uint8_t pad[3];
+} phmm_read_summary;
+
+/* One region, blocking: log10_out receives the NORMALISED matrix, summary_out[n_reads] (nullable) the per-read results. */
+int pairhmm_cuda_compute_normalized(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads,
+                                    const phmm_hap *haps, int n_haps, const pairhmm_cuda_epilogue *ep,
+                                    double *log10_out, uint8_t *rescued_out, phmm_read_summary *summary_out);
+/* Many regions: summary_out[r] (nullable, as the array itself) points at region r's [n_reads] summaries. */
+int pairhmm_cuda_compute_batch_normalized(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions,
+                                          const pairhmm_cuda_epilogue *ep, phmm_read_summary *const *summary_out);
+/* Flat form: summary_out[n_reads] in input read order. */
+int pairhmm_cuda_compute_flat_normalized(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                         const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
+                                         const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                         const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                                         int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                                         int64_t n_regions, const pairhmm_cuda_epilogue *ep, double *log10_out,
+                                         uint8_t *rescued_out, phmm_read_summary *summary_out);
+
 int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);
 int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h);
 const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h);

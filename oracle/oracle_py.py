@@ -69,6 +69,19 @@ class Oracle(_Lib):
         self.lib.oracle_forward_float_pairs.argtypes = [_u8p, _u8p, _u8p, _u8p, _u8p, _i64p, _i32p, _u8p, _i64p,
                                                         _i32p, _u32p, _u32p, C.c_int64, C.c_void_p]
         self.lib.oracle_forward_float_pairs.restype = None
+        self.lib.oracle_epilogue.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_double, C.c_double, C.c_int,
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.oracle_epilogue.restype = None
+
+    def epilogue(self, m, read_len, likelihood_cap=-4.5, max_error_per_base=0.02, natural_log=False):
+        """m[n_reads, n_haps] (copied) -> (normalised m, best, second_best, best_hap, poorly_modeled)"""
+        m = np.array(m, dtype=np.float64, order="C", copy=True)
+        n, nh = m.shape
+        rl = np.ascontiguousarray(read_len, np.int32)
+        best = np.zeros(n); second = np.zeros(n); bh = np.zeros(n, np.int32); pm = np.zeros(n, np.uint8)
+        self.lib.oracle_epilogue(m.ctypes.data, n, nh, rl.ctypes.data, float(likelihood_cap), float(max_error_per_base),
+                                 int(natural_log), best.ctypes.data, second.ctypes.data, bh.ctypes.data, pm.ctypes.data)
+        return m, best, second, bh, pm
 
     def forward_float(self, b):
         """raw 2^120-scaled FP32 sums (FTZ on, no FMA) for every pair of a FlatPairs"""
@@ -87,6 +100,30 @@ class Reference(_Lib):
 
     def isa(self):
         return int(self.lib.ref_pairhmm_isa())
+
+
+class ReferenceEpilogue:
+    """oracle/_ref/libref_epilogue.so: the reference's own AlleleLikelihoods<E, A> (normalizeLikelihoods,
+    filterPoorlyModeledEvidence, switchToNaturalLog) behind oracle/ref_epilogue_driver.cpp"""
+
+    def __init__(self):
+        self.lib = C.CDLL(os.path.join(HERE, "_ref", "libref_epilogue.so"))
+        self.lib.ref_epilogue.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_double, C.c_double, C.c_int,
+                                          C.c_void_p]
+
+    def epilogue(self, m, read_len, likelihood_cap=-4.5, max_error_per_base=0.02, natural_log=False):
+        """-> (matrix after normalisation [and log conversion], removed[n_reads])"""
+        m = np.array(m, dtype=np.float64, order="C", copy=True)
+        n, nh = m.shape
+        rl = np.ascontiguousarray(read_len, np.int32)
+        removed = np.zeros(n, np.uint8)
+        self.lib.ref_epilogue(m.ctypes.data, n, nh, rl.ctypes.data, float(likelihood_cap), float(max_error_per_base),
+                              int(natural_log), removed.ctypes.data)
+        return m, removed
+
+
+def reference_epilogue_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_epilogue.so"))
 
 
 def load_oracle():

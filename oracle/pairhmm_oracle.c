@@ -218,3 +218,46 @@ void oracle_forward_float_pairs(const uint8_t *read_bases, const uint8_t *base_q
     }
     FTZ_RESTORE();
 }
+
+/* ---- per-read epilogue (see pairhmm_oracle.h) ---- */
+void oracle_epilogue(double *m, int64_t n_reads, int32_t n_haps, const int32_t *read_len, double likelihood_cap,
+                     double max_error_per_base, int natural_log, double *best_out, double *second_out,
+                     int32_t *best_hap, uint8_t *poorly_modeled) {
+    const double ln10 = log(10.0);                         /* MathUtils.cpp:17 */
+    for (int64_t r = 0; r < n_reads; r++) {
+        double *v = m + r * (int64_t)n_haps;
+        double best = -INFINITY, second = -INFINITY;
+        int bi = -1;
+        uint8_t poorly = 1;
+        if (n_haps > 0) {
+            /* searchBestAllele, AlleleLikelihoods.h:101-117: strict '>' keeps the first maximum */
+            best = v[0]; bi = 0;
+            for (int a = 1; a < n_haps; a++) {
+                const double c = v[a];
+                if (c > best) { second = best; best = c; bi = a; }
+                else if (c > second) second = c;
+            }
+            /* normalizeLikelihoods returns early for an infinite cap or <= 1 allele (:375-380); otherwise every value
+             * below best + cap is raised to it (:155-165) */
+            if (!isinf(likelihood_cap) && n_haps > 1) {
+                const double worst = best + likelihood_cap;
+                for (int a = 0; a < n_haps; a++) if (v[a] < worst) v[a] = worst;
+                if (second < worst) second = worst;
+            }
+            /* maximumLikelihoodOverAllAlleles(s, e) < log10MinTrueLikelihood(read, rate), :413 */
+            {
+                double max_err = ceil((double)read_len[r] * max_error_per_base);
+                if (max_err > 2.0) max_err = 2.0;          /* min(2.0, ceil(...)), PHLCE.cpp:296 */
+                poorly = best < max_err * -4.0 ? 1 : 0;    /* log10QualPerBase = -4.0, PHLCE.cpp:297-298 */
+            }
+            if (natural_log) {
+                for (int a = 0; a < n_haps; a++) v[a] = v[a] * ln10;
+                best = best * ln10; second = second * ln10;
+            }
+        }
+        if (best_out) best_out[r] = best;
+        if (second_out) second_out[r] = second;
+        if (best_hap) best_hap[r] = bi;
+        if (poorly_modeled) poorly_modeled[r] = poorly;
+    }
+}

@@ -31,6 +31,16 @@ double oracle_compute(const uint8_t *read_bases, const uint8_t *base_q, const ui
                       const uint32_t *pair_read, const uint32_t *pair_hap, int64_t n_pairs,
                       int use_double, int n_threads, int tables_in_timed_region, double *out,
                       uint8_t *rescued);
+/* Per-read epilogue on a read-major matrix m[n_reads][n_haps] (in place), restating what the reference's host code
+ * does to the PairHMM's result: AlleleLikelihoods::normalizeLikelihoods (AlleleLikelihoods.h:372-390 with
+ * normalizeLikelihoodsPerEvidence :150-166 and searchBestAllele :92-148, canBeReference = true, no priorities), the
+ * predicate of filterPoorlyModeledEvidence (:404-419) with PairHMMLikelihoodCalculationEngine::log10MinTrueLikelihood
+ * (PairHMMLikelihoodCalculationEngine.cpp:294-299), and switchToNaturalLog (:462-476, MathUtils.cpp:16-18).
+ * Outputs per read (each nullable): best / second_best value (second on the normalised row), index of the best
+ * haplotype, poorly-modelled flag. */
+void oracle_epilogue(double *m, int64_t n_reads, int32_t n_haps, const int32_t *read_len, double likelihood_cap,
+                     double max_error_per_base, int natural_log, double *best, double *second_best,
+                     int32_t *best_hap, uint8_t *poorly_modeled);
 #ifdef __cplusplus
 }
 #endif

@@ -41,6 +41,41 @@ def main():
         np.savez_compressed(os.path.join(HERE, name + ".npz"), log10=out, rescued=resc, log10_use_double=out_d,
                             meta=np.array(meta), **{f: getattr(b, f) for f in FIELDS})
         print(name, b.n_pairs, "pairs, rescued", int(resc.sum()))
+    # per-read epilogue: the reference's AlleleLikelihoods code on the reference's own matrices and
+    # on synthetic rows with ties, -inf and single-haplotype regions
+    rep = oracle_py.ReferenceEpilogue()
+    rng = np.random.default_rng(0xB200)
+    ep = {}
+    k = 0
+    for name in ("c1_clean", "c1_lowq", "c3_small"):
+        b = cases[name]
+        out, _, _ = ref.compute(b.as_flat(), threads=8)
+        for r in range(b.n_regions):
+            r0, r1 = int(b.reg_read_start[r]), int(b.reg_read_start[r + 1])
+            nh = int(b.reg_hap_start[r + 1] - b.reg_hap_start[r])
+            o0 = int(b.region_out_offsets()[r])
+            m = out[o0:o0 + (r1 - r0) * nh].reshape(r1 - r0, nh)
+            for cap, rate, nl in ((-4.5, 0.02, 0), (-4.5, 0.02, 1), (-np.inf, 0.02, 0), (-1.0, 0.0, 0)):
+                mo, removed = rep.epilogue(m, b.read_len[r0:r1], cap, rate, nl)
+                ep["m%d" % k] = m; ep["len%d" % k] = b.read_len[r0:r1]; ep["par%d" % k] = np.array([cap, rate, nl])
+                ep["out%d" % k] = mo; ep["rem%d" % k] = removed
+                k += 1
+    for t in range(40):
+        n, nh = int(rng.integers(1, 30)), int(rng.integers(1, 12))
+        m = -rng.random((n, nh)) * float(rng.choice([1, 10, 100]))
+        if t % 3 == 0:
+            m = np.round(m)
+        if t % 7 == 0:
+            m[int(rng.integers(0, n))] = -np.inf
+        rl = rng.integers(1, 300, n).astype(np.int32)
+        cap, rate, nl = float(rng.choice([-4.5, -1.0, -np.inf])), float(rng.choice([0.02, 0.0, 0.01])), t % 2
+        mo, removed = rep.epilogue(m, rl, cap, rate, nl)
+        ep["m%d" % k] = m; ep["len%d" % k] = rl; ep["par%d" % k] = np.array([cap, rate, nl])
+        ep["out%d" % k] = mo; ep["rem%d" % k] = removed
+        k += 1
+    np.savez_compressed(os.path.join(HERE, "epilogue.npz"), n_cases=np.array(k), meta=np.array(
+        "reference AlleleLikelihoods.h via oracle/ref_epilogue_driver.cpp; " + gxx), **ep)
+    print("epilogue", k, "cases")
     pf, mf, pd, md = ref.tables()
     np.savez_compressed(os.path.join(HERE, "tables.npz"), ph2pr_f=pf, mm_f=mf[:8256], ph2pr_d=pd, mm_d=md[:8256], meta=np.array(meta))
 

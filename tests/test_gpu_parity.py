@@ -252,3 +252,52 @@ def test_long_reads_double_and_exact_paths(oracle):
         m = wresc.astype(bool)                       # where the reference also took the double path: same numbers
         if m.any():
             assert np.abs(got_d[m] - want[m]).max() < 1e-9
+
+
+def _rows(b, flat, g):
+    """region g of a flat result array as [n_reads, n_haps]"""
+    r0, r1 = int(b.reg_read_start[g]), int(b.reg_read_start[g + 1])
+    nh = int(b.reg_hap_start[g + 1] - b.reg_hap_start[g])
+    o0 = int(b.region_out_offsets()[g])
+    return flat[o0:o0 + (r1 - r0) * nh].reshape(r1 - r0, nh), r0, r1
+
+
+@pytest.mark.parametrize("cap,rate,nl", [(-4.5, 0.02, False), (-4.5, 0.02, True), (-np.inf, 0.02, False), (-1.0, 0.0, False)])
+def test_fused_epilogue_equals_oracle_on_the_same_matrix(engine, oracle, cap, rate, nl):
+    """pairhmm_cuda_compute_flat_normalized = PairHMM + normalizeLikelihoods + filterPoorlyModeledEvidence's predicate
+    [+ switchToNaturalLog] on the device. Applied to the engine's own raw matrix, the oracle's epilogue (pinned against
+    the reference's AlleleLikelihoods.h, tests/test_oracle.py) must give the same bits; the raw matrix itself is held to
+    the usual parity bar by the other tests."""
+    for b in (synth.config1("lowq"), synth.config3(96, 7), synth.config2(4), synth.edge_cases()):
+        raw, resc = engine.compute_batch(b)
+        ep = fgdp_b200.pairhmm.Epilogue(cap, rate, nl)
+        got, gresc, summ = engine.compute_batch_normalized(b, ep)
+        assert np.array_equal(gresc, resc)
+        for g in range(b.n_regions):
+            m, r0, r1 = _rows(b, raw, g)
+            want, best, second, bh, pm = oracle.epilogue(m, b.read_len[r0:r1], cap, rate, nl)
+            gm, _, _ = _rows(b, got, g)
+            assert np.array_equal(gm, want), (b.name, g)
+            s = summ[r0:r1]
+            assert np.array_equal(s["best"], best) and np.array_equal(s["second_best"], second)
+            assert np.array_equal(s["best_hap"], bh) and np.array_equal(s["poorly_modeled"], pm)
+
+
+def test_fused_epilogue_region_call_duplicates_and_empty_reads(engine, oracle):
+    """single-region entry point; duplicate reads share their unique read's row, a zero-length read reports -inf"""
+    b = synth.config1("lowq")
+    reads, haps = _region_lists(b)
+    reads = reads[:10] + [reads[3]] + [tuple(a[:0] for a in reads[0])] + reads[10:20]
+    raw, _ = engine.compute(reads, haps)
+    got, _, summ = engine.compute_normalized(reads, haps)
+    lens = np.array([len(r[0]) for r in reads], np.int32)
+    want, best, second, bh, pm = oracle.epilogue(raw, lens)
+    assert np.array_equal(got, want)
+    assert np.array_equal(summ["best"], best) and np.array_equal(summ["best_hap"], bh)
+    assert np.array_equal(summ["poorly_modeled"], pm) and np.array_equal(summ["second_best"], second)
+    assert np.array_equal(got[10], got[3]) and summ[11]["poorly_modeled"] == 1 and np.isneginf(got[11]).all()
+    with pytest.raises(fgdp_b200.PairHMMError):
+        engine.compute_normalized(reads, haps, fgdp_b200.pairhmm.Epilogue(likelihood_cap=1.0))
+    # the plain entry points are unaffected by an earlier normalised call
+    again, _ = engine.compute(reads, haps)
+    assert np.array_equal(again, raw)

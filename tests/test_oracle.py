@@ -73,3 +73,55 @@ def test_oracle_edge_semantics(oracle):
     assert one(A, A, q=30 | 0x80, i=45 | 0x80, d=45 | 0x80, c=10 | 0x80) == base
     mism = A.copy(); mism[5] = ord("A")
     assert one(mism, A) < base - 1.0
+
+
+def _check_derived(m_in, mo, best, second, bh, pm, rl, cap, rate, nl):
+    """best / second_best / best_hap / poorly_modeled against plain numpy on the same rows"""
+    n, nh = m_in.shape
+    scale = np.log(10.0) if nl else 1.0
+    for r in range(n):
+        row = m_in[r]
+        assert bh[r] == int(np.argmax(row))                       # first maximum
+        assert best[r] == row.max() * scale
+        if nh > 1:
+            srt = np.sort(mo[r])[::-1]
+            assert second[r] == srt[1]                            # runner-up on the normalised row
+        else:
+            assert second[r] == -np.inf
+        assert pm[r] == (row.max() < min(2.0, np.ceil(rl[r] * rate)) * -4.0)
+
+
+def test_epilogue_oracle_matches_reference_golden(oracle):
+    """oracle_epilogue() vs tests/golden/epilogue.npz = outputs of the reference's own AlleleLikelihoods.h
+    (normalizeLikelihoods, filterPoorlyModeledEvidence, switchToNaturalLog): bit for bit, removal set identical."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "epilogue.npz"))
+    n = int(z["n_cases"])
+    assert n >= 50
+    for k in range(n):
+        m, rl, (cap, rate, nl) = z["m%d" % k], z["len%d" % k], z["par%d" % k]
+        mo, best, second, bh, pm = oracle.epilogue(m, rl, cap, rate, bool(nl))
+        assert np.array_equal(mo, z["out%d" % k]), k
+        assert np.array_equal(pm, z["rem%d" % k]), k
+        _check_derived(m, mo, best, second, bh, pm, rl, cap, rate, nl)
+
+
+def test_epilogue_oracle_vs_live_reference(oracle):
+    """the same against oracle/_ref/libref_epilogue.so run here, on fresh random matrices"""
+    import oracle_py
+    if not oracle_py.reference_epilogue_available():
+        pytest.skip("oracle/_ref/libref_epilogue.so not built (no /root/reference on this machine)")
+    ref = oracle_py.ReferenceEpilogue()
+    rng = np.random.default_rng(7)
+    for t in range(200):
+        n, nh = int(rng.integers(1, 50)), int(rng.integers(1, 33))
+        m = -rng.random((n, nh)) * float(rng.choice([1, 10, 100]))
+        if t % 3 == 0:
+            m = np.round(m)
+        if t % 5 == 0:
+            m[int(rng.integers(0, n))] = -np.inf
+        rl = rng.integers(1, 385, n).astype(np.int32)
+        cap, rate, nl = float(rng.choice([-4.5, -0.5, -np.inf])), float(rng.choice([0.02, 0.0, 0.005])), t % 2
+        mo, best, second, bh, pm = oracle.epilogue(m, rl, cap, rate, bool(nl))
+        mr, removed = ref.epilogue(m, rl, cap, rate, bool(nl))
+        assert np.array_equal(mo, mr) and np.array_equal(pm, removed), t
