@@ -15,7 +15,7 @@ b = {"c1": lambda: synth.config1(), "c2": lambda: synth.config2(n), "c3": lambda
      "c4": lambda: synth.config4(), "c5": lambda: synth.config5(n)}[which]()
 cells = b.cells()
 print("gen %.1fs  %s pairs=%d cells=%.3g" % (time.time() - t, b.name, b.n_pairs, cells), flush=True)
-e = fgdp_b200.Engine(exact_fp32=exact, lane_group=lg, max_ctas_per_sm=int(os.environ.get("MAX_CTAS", "0")))
+e = fgdp_b200.Engine(exact_fp32=exact, use_double=bool(int(os.environ.get("USE_DOUBLE", "0"))), lane_group=lg, max_ctas_per_sm=int(os.environ.get("MAX_CTAS", "0")))
 t = time.time(); e.resident_load(b); print("load %.2fs" % (time.time() - t), flush=True)
 res = []
 for i in range(reps):
