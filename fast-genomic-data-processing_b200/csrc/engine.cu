@@ -43,7 +43,7 @@ template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; 
 void Slot::release() {
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
     h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release(); h_rescue_base.release();
-    h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release();
+    h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
     d_rescue.release(); d_fres.release(); d_out.release();
@@ -123,24 +123,41 @@ uint64_t hash_bytes(const uint8_t *p, size_t n, uint64_t h) {
     if (i < n) std::memcpy(&w, p + i, n - i);
     return mix64(h ^ w ^ (uint64_t)n);
 }
-uint64_t hash_read(const phmm_read &r) {
-    uint64_t h = 0x243f6a8885a308d3ull ^ (uint64_t)r.len;
-    h = hash_bytes(r.bases, r.len, h); h = hash_bytes(r.base_q, r.len, h); h = hash_bytes(r.ins_q, r.len, h);
-    h = hash_bytes(r.del_q, r.len, h); h = hash_bytes(r.gcp, r.len, h);
+// a read of either kind: processed (five arrays) or raw (bases, base_q, optional ins_q / del_q, mapping quality)
+struct ReadRef { const uint8_t *bases, *base_q, *ins_q, *del_q, *gcp; int32_t len, mapq; };
+inline ReadRef read_ref(const RegionView &rv, size_t i) {
+    if (rv.raw) { const phmm_raw_read &r = rv.raw[i]; return ReadRef{r.bases, r.base_q, r.ins_q, r.del_q, nullptr, r.len, r.mapq}; }
+    const phmm_read &r = rv.reads[i];
+    return ReadRef{r.bases, r.base_q, r.ins_q, r.del_q, r.gcp, r.len, 0};
+}
+uint64_t hash_read(const ReadRef &r) {
+    uint64_t h = 0x243f6a8885a308d3ull ^ (uint64_t)r.len ^ ((uint64_t)(uint32_t)r.mapq << 32);
+    h = hash_bytes(r.bases, r.len, h); h = hash_bytes(r.base_q, r.len, h);
+    if (r.ins_q) h = hash_bytes(r.ins_q, r.len, h);
+    if (r.del_q) h = hash_bytes(r.del_q, r.len, h);
+    if (r.gcp) h = hash_bytes(r.gcp, r.len, h);
     return h;
 }
-bool same_read(const phmm_read &a, const phmm_read &b) {
-    return a.len == b.len && !std::memcmp(a.bases, b.bases, a.len) && !std::memcmp(a.base_q, b.base_q, a.len) &&
-           !std::memcmp(a.ins_q, b.ins_q, a.len) && !std::memcmp(a.del_q, b.del_q, a.len) &&
-           !std::memcmp(a.gcp, b.gcp, a.len);
+inline bool same_plane(const uint8_t *a, const uint8_t *b, int32_t n) { return (!a || !b) ? a == b || (!a && !b) : !std::memcmp(a, b, n); }
+bool same_read(const ReadRef &a, const ReadRef &b) {
+    return a.len == b.len && a.mapq == b.mapq && !std::memcmp(a.bases, b.bases, a.len) && !std::memcmp(a.base_q, b.base_q, a.len) &&
+           same_plane(a.ins_q, b.ins_q, a.len) && same_plane(a.del_q, b.del_q, a.len) && same_plane(a.gcp, b.gcp, a.len);
 }
 
 constexpr uint32_t kNoRead = 0xffffffffu;
 
+// getErrorModelAdjustedQual (PairHMMLikelihoodCalculationEngine.cpp:45-48; MathUtils::fastRound MathUtils.cpp:65-68;
+// INITIAL_QSCORE 40, MIN_ADJUSTED_QSCORE 10), host libm as in the reference
+uint8_t pcr_adjusted_qual(int repeat_length, int rate_factor) {
+    const double d = 40.0 - std::exp((double)repeat_length / ((double)rate_factor * M_PI));
+    const int r = d > 0.0 ? (int)(d + 0.5) : (int)(d - 0.5);
+    return (uint8_t)(char)std::max(10, r + 1);
+}
+
 // Pass A for one region: read de-duplication (VectorLoglessPairHMM.cpp:83-103) and sizes.
 int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, uint32_t group_hint) {
     pl = RegionPlan();
-    if (rv.n_reads < 0 || rv.n_haps < 0 || (rv.n_reads > 0 && !rv.reads) || (rv.n_haps > 0 && !rv.haps))
+    if (rv.n_reads < 0 || rv.n_haps < 0 || (rv.n_reads > 0 && !rv.reads && !rv.raw) || (rv.n_haps > 0 && !rv.haps))
         return fail(h, PAIRHMM_ERR_ARG, "null pointer or negative count in region");
     pl.uniq_of_read.assign(rv.n_reads, kNoRead);
     const bool dedup = h->cfg.dedup_reads != 0;
@@ -160,8 +177,8 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         hmax = std::max(hmax, hp.len);
     }
     for (int i = 0; i < rv.n_reads; ++i) {
-        const phmm_read &r = rv.reads[i];
-        if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || !r.ins_q || !r.del_q || !r.gcp)))
+        const ReadRef r = read_ref(rv, (size_t)i);
+        if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || (!rv.raw && (!r.ins_q || !r.del_q || !r.gcp)))))
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
         if (bin_of_read(r.len, 32) < 0)
@@ -172,7 +189,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             size_t s = (size_t)hv & mask;
             while (table[s]) {
                 const uint32_t cand = table[s] - 1;
-                if (hashes[cand] == hv && same_read(rv.reads[pl.uniq_src[cand]], r)) { u = cand; break; }
+                if (hashes[cand] == hv && same_read(read_ref(rv, pl.uniq_src[cand]), r)) { u = cand; break; }
                 s = (s + 1) & mask;
             }
             if (u == kNoRead) { table[s] = (uint32_t)pl.uniq_src.size() + 1; hashes.push_back(hv); }
@@ -181,7 +198,10 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             u = (uint32_t)pl.uniq_src.size();
             pl.uniq_src.push_back((uint32_t)i);
             pl.read_bytes += (uint64_t)r.len;
-            for (int q = 0; q < r.len; ++q) {       // gap-continuation range, as the kernel sees it (&127)
+            if (rv.raw) {                           // constant by construction (buildGapContinuationPenalties)
+                pl.gcp_min = pl.gcp_max = (uint8_t)(h->model.constant_gcp & 127);
+                pl.any_indel_q |= r.ins_q != nullptr || r.del_q != nullptr;
+            } else for (int q = 0; q < r.len; ++q) {       // gap-continuation range, as the kernel sees it (&127)
                 const uint8_t c = r.gcp[q] & 127;
                 pl.gcp_min = std::min(pl.gcp_min, c); pl.gcp_max = std::max(pl.gcp_max, c);
             }
@@ -219,7 +239,7 @@ void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w) {
     const uint32_t n = pl.n_uniq;
     std::vector<uint16_t> bin(n);
     for (uint32_t j = 0; j < n; ++j) {
-        const int R = rv.reads[pl.uniq_src[j]].len;
+        const int R = read_ref(rv, pl.uniq_src[j]).len;
         bin[j] = (uint16_t)bin_of_read(R, choose_width(R, v, forced_w));
         pl.pairs32[bin_of_read(R, 32)] += (uint32_t)rv.n_haps;
     }
@@ -309,7 +329,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         nu += p.n_uniq; rbytes += p.read_bytes; nh += (uint32_t)s.regions[i].n_haps; hbytes += p.hap_bytes;
         hw += p.hap_words; hl += (uint32_t)s.regions[i].n_haps; up = (uint32_t)up_next;
         uint64_t rl = 0;
-        for (int r = 0; r < s.regions[i].n_reads; ++r) rl += (uint64_t)s.regions[i].reads[r].len;
+        for (int r = 0; r < s.regions[i].n_reads; ++r) rl += (uint64_t)read_ref(s.regions[i], (size_t)r).len;
         cells += rl * p.hap_bytes;
         pairs += (uint64_t)s.regions[i].n_reads * (uint64_t)s.regions[i].n_haps;
         reads_in += (uint64_t)s.regions[i].n_reads;
@@ -333,6 +353,13 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
     RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
     s.ep_on = h->ep_on; s.ep = h->ep;
+    s.raw_on = n_regs > 0 && s.regions[0].raw != nullptr; s.model = h->model; s.raw_indel_q = false;
+    for (size_t i = 0; i < n_regs; ++i) {
+        if ((s.regions[i].raw != nullptr) != s.raw_on && s.regions[i].n_reads > 0)
+            return fail(h, PAIRHMM_ERR_ARG, "raw and processed reads mixed in one call");
+        s.raw_indel_q |= s.plans[i].any_indel_q;
+    }
+    if (s.raw_on) { RES(h_mapq, nu + 1); RES(d_mapq, nu + 1); }
     if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
@@ -342,11 +369,20 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         const RegionPlan &p = s.plans[i];
         uint64_t ro = p.read_byte_off;
         for (uint32_t j = 0; j < p.n_uniq; ++j) {
-            const phmm_read &r = rv.reads[p.uniq_src[j]];
+            const ReadRef r = read_ref(rv, p.uniq_src[j]);
             uint8_t *d = s.h_rd.p + ro;
             std::memcpy(d, r.bases, r.len); std::memcpy(d + s.plane, r.base_q, r.len);
-            std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
-            std::memcpy(d + 4 * s.plane, r.gcp, r.len);
+            if (!s.raw_on) {
+                std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
+                std::memcpy(d + 4 * s.plane, r.gcp, r.len);
+            } else {
+                // planes 2-4 are filled on the device unless some read of the chunk has its own indel qualities
+                if (s.raw_indel_q) {
+                    if (r.ins_q) std::memcpy(d + 2 * s.plane, r.ins_q, r.len); else std::memset(d + 2 * s.plane, 45, r.len);
+                    if (r.del_q) std::memcpy(d + 3 * s.plane, r.del_q, r.len); else std::memset(d + 3 * s.plane, 45, r.len);
+                }
+                s.h_mapq.p[p.first_uniq + j] = r.mapq;
+            }
             s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
             if (s.ep_on) s.h_rows.p[p.first_uniq + j] = RowInfo{p.upair_off + j * (uint32_t)rv.n_haps, (uint32_t)rv.n_haps};
             ro += (uint64_t)r.len;
@@ -386,9 +422,27 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
     const uint32_t n_units = s.bin_start[kNumBins];
-    if (s.n_uniq) {
+    uint64_t plane_bytes = s.plane * 5;
+    if (s.n_uniq && !s.raw_on) {
         CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * 5, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
+    }
+    if (s.n_uniq && s.raw_on) {
+        // raw reads: bases + base qualities (+ insertion / deletion qualities if any read has them) cross PCIe; the default
+        // indel qualities (ReadUtils.h:40) and the constant gap-continuation plane are written here
+        const int np = s.raw_indel_q ? 4 : 2;
+        plane_bytes = s.plane * (uint64_t)np + sizeof(int32_t) * (uint64_t)s.n_uniq;
+        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * (uint64_t)np, cudaMemcpyHostToDevice, st));
+        if (!s.raw_indel_q) CU(h, cudaMemsetAsync(s.d_rd.p + 2 * s.plane, 45, 2 * s.plane, st));
+        CU(h, cudaMemsetAsync(s.d_rd.p + 4 * s.plane, s.model.constant_gcp & 0xff, s.plane, st));
+        CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_mapq.p, s.h_mapq.p, sizeof(int32_t) * s.n_uniq, cudaMemcpyHostToDevice, st));
+        PrepReadsArgs pa{};
+        pa.rd = s.d_rd.p; pa.plane = s.plane; pa.reads = s.d_reads.p; pa.mapq = s.d_mapq.p; pa.n = s.n_uniq;
+        pa.pcr_on = s.model.pcr_rate_factor > 0; pa.base_q_threshold = s.model.base_quality_threshold;
+        for (int i = 0; i <= 20 && pa.pcr_on; ++i) pa.pcr_table[i] = pcr_adjusted_qual(i, s.model.pcr_rate_factor);
+        CU(h, launch_prep_reads(pa, h->sm_count, st));
+        h->stats.kernel_launches += 1;
     }
     if (s.n_haps) {
         if (s.hap_bytes) CU(h, cudaMemcpyAsync(s.d_hapbytes.p, s.h_hapbytes.p, s.hap_bytes, cudaMemcpyHostToDevice, st));
@@ -403,7 +457,7 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     }
     CU(h, launch_prep_haps(s.d_hapbytes.p, s.d_hapoff.p, s.d_haps.p, s.n_haps, s.d_hapw.p, st));
     h->stats.kernel_launches += 1;
-    h->stats.h2d_bytes += s.plane * 5 + sizeof(DevRead) * (uint64_t)s.n_uniq + s.hap_bytes +
+    h->stats.h2d_bytes += plane_bytes + sizeof(DevRead) * (uint64_t)s.n_uniq + s.hap_bytes +
                           (sizeof(uint64_t) + sizeof(DevHap) + sizeof(uint32_t)) * (uint64_t)s.n_haps +
                           sizeof(DevUnit) * (uint64_t)n_units;
     return PAIRHMM_OK;
@@ -704,7 +758,7 @@ int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_re
         if (st != PAIRHMM_OK) return st;
         h->slot_ticket[si] = 0;
     }
-    RegionView rv{reads, n_reads, haps, n_haps, log10_out, rescued_out};
+    RegionView rv{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr};
     int st = submit_chunk(h, h->slots[si], &rv, 1, 1);
     if (st != PAIRHMM_OK) { h->slots[si].busy = false; return st; }
     h->slot_ticket[si] = *ticket = h->next_ticket++;
@@ -738,9 +792,8 @@ int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_r
     return pairhmm_cuda_wait(h, t);
 }
 
-// the batch pipeline; summaries (nullable) = per region the [n_reads] epilogue results, used when h->ep_on
-static int compute_batch_impl(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions,
-                              phmm_read_summary *const *summaries) {
+// the batch pipeline over regions of either read kind (RegionView::reads or ::raw)
+static int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions) {
     if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
     auto t0 = clk::now();
     CU(h, cudaSetDevice(h->device));
@@ -767,14 +820,15 @@ static int compute_batch_impl(pairhmm_cuda_handle *h, const phmm_region *regions
         int64_t cells = 0;
         uint64_t pairs = 0, rbytes = 0;
         while (i < n_regions) {
-            const phmm_region &r = regions[i];
+            const RegionView &r = regions[i];
+            if (r.n_reads > 0 && !r.reads && !r.raw) { status = fail(h, PAIRHMM_ERR_ARG, "null read array"); break; }
+            if (r.n_haps > 0 && !r.haps) { status = fail(h, PAIRHMM_ERR_ARG, "null haplotype array"); break; }
             uint64_t rl = 0, hl = 0;
-            for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.reads[q].len);
+            for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
             for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
             const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
             if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_limit || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
-            views.push_back(RegionView{r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out,
-                                       summaries ? summaries[i] : nullptr});
+            views.push_back(r);
             cells += (int64_t)(rl * hl); pairs += p; rbytes += rl;
             ++i;
         }
@@ -795,8 +849,19 @@ static int compute_batch_impl(pairhmm_cuda_handle *h, const phmm_region *regions
     return status;
 }
 
+static std::vector<RegionView> views_of(const phmm_region *regions, int64_t n_regions, phmm_read_summary *const *summaries) {
+    std::vector<RegionView> v((size_t)std::max<int64_t>(0, n_regions));
+    for (int64_t i = 0; i < n_regions; ++i) {
+        const phmm_region &r = regions[i];
+        v[i] = RegionView{r.reads, nullptr, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out, summaries ? summaries[i] : nullptr};
+    }
+    return v;
+}
+
 int pairhmm_cuda_compute_batch(pairhmm_cuda_handle *h, const phmm_region *regions, int64_t n_regions) {
-    return compute_batch_impl(h, regions, n_regions, nullptr);
+    if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
+    const std::vector<RegionView> v = views_of(regions, n_regions, nullptr);
+    return compute_batch_impl(h, v.data(), n_regions);
 }
 
 static int check_epilogue(pairhmm_cuda_handle *h, const pairhmm_cuda_epilogue *ep) {
@@ -816,8 +881,10 @@ int pairhmm_cuda_compute_batch_normalized(pairhmm_cuda_handle *h, const phmm_reg
     // chunks of earlier plain submits must not pick the epilogue up: retire them first
     for (int si = 0; si < 2; ++si)
         if (h->slots[si].busy) { CU(h, cudaSetDevice(h->device)); st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    if (n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
+    const std::vector<RegionView> v = views_of(regions, n_regions, summary_out);
     h->ep_on = true; h->ep = *ep;
-    st = compute_batch_impl(h, regions, n_regions, summary_out);
+    st = compute_batch_impl(h, v.data(), n_regions);
     h->ep_on = false;
     return st;
 }
@@ -917,6 +984,129 @@ int pairhmm_cuda_compute_flat_normalized(pairhmm_cuda_handle *h, const uint8_t *
     return pairhmm_cuda_compute_batch_normalized(h, v.regions.data(), n_regions, ep, summary_out ? sp.data() : nullptr);
 }
 
+// ---- raw reads: quality pre-pass on the device ----
+void pairhmm_cuda_default_read_model(pairhmm_cuda_read_model *m) {
+    if (!m) return;
+    m->pcr_rate_factor = 3;           // CONSERVATIVE, LikelihoodEngineArgumentCollection.h:30
+    m->base_quality_threshold = 18;   // BASE_QUALITY_SCORE_THRESHOLD
+    m->constant_gcp = 10;             // gcpHMM
+    m->reserved = 0;
+}
+
+static int check_read_model(pairhmm_cuda_handle *h, const pairhmm_cuda_read_model *m) {
+    if (!m || m->pcr_rate_factor < 0 || m->pcr_rate_factor > 3)
+        return fail(h, PAIRHMM_ERR_ARG, "read model: pcr_rate_factor must be 0 (none), 1, 2 or 3");
+    if (m->base_quality_threshold < 6 || m->base_quality_threshold > 127)       // PHLCE.cpp:39
+        return fail(h, PAIRHMM_ERR_ARG, "read model: base_quality_threshold must be in [6, 127]");
+    if (m->constant_gcp < 0 || m->constant_gcp > 127) return fail(h, PAIRHMM_ERR_ARG, "read model: constant_gcp must be in [0, 127]");
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_compute_batch_raw(pairhmm_cuda_handle *h, const phmm_raw_region *regions, int64_t n_regions,
+                                   const pairhmm_cuda_read_model *model) {
+    if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
+    int st = check_read_model(h, model);
+    if (st != PAIRHMM_OK) return st;
+    std::vector<RegionView> v((size_t)n_regions);
+    for (int64_t i = 0; i < n_regions; ++i) {
+        const phmm_raw_region &r = regions[i];
+        v[i] = RegionView{nullptr, r.reads, r.n_reads, r.haps, r.n_haps, r.log10_out, r.rescued_out, nullptr};
+    }
+    h->model = *model;
+    return compute_batch_impl(h, v.data(), n_regions);
+}
+
+int pairhmm_cuda_compute_raw(pairhmm_cuda_handle *h, const phmm_raw_read *reads, int n_reads, const phmm_hap *haps,
+                             int n_haps, const pairhmm_cuda_read_model *model, double *log10_out, uint8_t *rescued_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (n_reads == 0) return check_read_model(h, model);   // VectorLoglessPairHMM.cpp:46-47
+    const phmm_raw_region r{reads, n_reads, haps, n_haps, log10_out, rescued_out};
+    return pairhmm_cuda_compute_batch_raw(h, &r, 1, model);
+}
+
+int pairhmm_cuda_compute_flat_raw(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                  const uint8_t *ins_q, const uint8_t *del_q, const int32_t *mapq,
+                                  const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                  const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                                  int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                                  int64_t n_regions, const pairhmm_cuda_read_model *model, double *log10_out,
+                                  uint8_t *rescued_out) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    if (n_reads < 0 || n_haps < 0 || n_regions < 0) return fail(h, PAIRHMM_ERR_ARG, "negative count");
+    if (n_reads && (!read_bases || !base_q || !mapq || !read_off || !read_len)) return fail(h, PAIRHMM_ERR_ARG, "null read array");
+    if (n_haps && (!hap_bases || !hap_off || !hap_len)) return fail(h, PAIRHMM_ERR_ARG, "null haplotype array");
+    if (n_regions && (!reg_read_start || !reg_hap_start)) return fail(h, PAIRHMM_ERR_ARG, "null region array");
+    static thread_local std::vector<phmm_raw_read> reads;
+    static thread_local std::vector<phmm_hap> haps;
+    reads.resize((size_t)n_reads); haps.resize((size_t)n_haps);
+    phmm_raw_read *rp = reads.data();   // a worker thread naming `reads` would get ITS thread_local instance
+    parallel_for((size_t)n_reads, pack_threads(h), 65536, [&, rp](size_t i) {
+        const int64_t o = read_off[i];
+        rp[i] = phmm_raw_read{read_bases + o, base_q + o, ins_q ? ins_q + o : nullptr, del_q ? del_q + o : nullptr, read_len[i], mapq[i]};
+    });
+    for (int64_t i = 0; i < n_haps; ++i) haps[i] = phmm_hap{hap_bases + hap_off[i], hap_len[i]};
+    std::vector<phmm_raw_region> regs((size_t)n_regions);
+    int64_t out_off = 0;
+    for (int64_t r = 0; r < n_regions; ++r) {
+        const int64_t r0 = reg_read_start[r], r1 = reg_read_start[r + 1], h0 = reg_hap_start[r], h1 = reg_hap_start[r + 1];
+        if (r0 < 0 || r1 < r0 || r1 > n_reads || h0 < 0 || h1 < h0 || h1 > n_haps || r1 - r0 > 0x7fffffff || h1 - h0 > 0x7fffffff)
+            return fail(h, PAIRHMM_ERR_ARG, "region bounds out of range");
+        if ((r1 - r0) * (h1 - h0) > 0 && !log10_out) return fail(h, PAIRHMM_ERR_ARG, "null output");
+        regs[r] = phmm_raw_region{reads.data() + r0, (int32_t)(r1 - r0), haps.data() + h0, (int32_t)(h1 - h0),
+                                  log10_out ? log10_out + out_off : nullptr, rescued_out ? rescued_out + out_off : nullptr};
+        out_off += (r1 - r0) * (h1 - h0);
+    }
+    return pairhmm_cuda_compute_batch_raw(h, regs.data(), n_regions, model);
+}
+
+// The pre-pass alone: pack the reads as one haplotype-less region, run prep_reads_kernel, copy the planes back.
+int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                    const uint8_t *ins_q, const uint8_t *del_q, const int32_t *mapq,
+                                    const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                    const pairhmm_cuda_read_model *model, uint8_t *out_base_q, uint8_t *out_ins_q,
+                                    uint8_t *out_del_q, uint8_t *out_gcp) {
+    if (!h) return PAIRHMM_ERR_ARG;
+    int st = check_read_model(h, model);
+    if (st != PAIRHMM_OK) return st;
+    if (n_reads < 0 || n_reads > 0x7fffffff) return fail(h, PAIRHMM_ERR_ARG, "bad read count");
+    if (n_reads == 0) return PAIRHMM_OK;
+    if (!read_bases || !base_q || !mapq || !read_off || !read_len || !out_base_q || !out_ins_q || !out_del_q || !out_gcp)
+        return fail(h, PAIRHMM_ERR_ARG, "null array");
+    CU(h, cudaSetDevice(h->device));
+    for (int si = 0; si < 2; ++si)
+        if (h->slots[si].busy) { st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    std::vector<phmm_raw_read> reads((size_t)n_reads);
+    for (int64_t i = 0; i < n_reads; ++i) {
+        const int64_t o = read_off[i];
+        reads[i] = phmm_raw_read{read_bases + o, base_q + o, ins_q ? ins_q + o : nullptr, del_q ? del_q + o : nullptr, read_len[i], mapq[i]};
+    }
+    const bool dedup = h->cfg.dedup_reads != 0;
+    h->cfg.dedup_reads = 0;               // every read keeps its own row: unique index == input index
+    h->model = *model;
+    h->resident_loaded = false;
+    RegionView rv{nullptr, reads.data(), (int32_t)n_reads, nullptr, 0, nullptr, nullptr, nullptr};
+    Slot &s = h->slots[0];
+    st = pack_chunk(h, s, &rv, 1, pack_threads(h));
+    h->cfg.dedup_reads = dedup ? 1 : 0;
+    if (st != PAIRHMM_OK) return st;
+    if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
+    std::vector<uint8_t> tmp((size_t)s.plane * 4);
+    if (s.n_uniq) CU(h, cudaMemcpyAsync(tmp.data(), s.d_rd.p + s.plane, s.plane * 4, cudaMemcpyDeviceToHost, s.stream));
+    CU(h, cudaStreamSynchronize(s.stream));
+    const RegionPlan &p = s.plans[0];
+    for (int64_t i = 0; i < n_reads; ++i) {
+        const uint32_t u = p.uniq_of_read[(size_t)i];
+        if (u == 0xffffffffu) continue;   // zero-length read
+        const DevRead dr = s.h_reads.p[p.first_uniq + u];
+        const int64_t o = read_off[i];
+        std::memcpy(out_base_q + o, tmp.data() + dr.off, dr.len);
+        std::memcpy(out_ins_q + o, tmp.data() + s.plane + dr.off, dr.len);
+        std::memcpy(out_del_q + o, tmp.data() + 2 * s.plane + dr.off, dr.len);
+        std::memcpy(out_gcp + o, tmp.data() + 3 * s.plane + dr.off, dr.len);
+    }
+    return PAIRHMM_OK;
+}
+
 int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
                                int n_haps, const uint32_t *read_idx, const uint32_t *hap_idx, size_t n_pairs,
                                double *log10_out, uint8_t *rescued_out) {
@@ -969,7 +1159,7 @@ int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases
     if (st != PAIRHMM_OK) return st;
     std::vector<RegionView> views(n_regions);
     for (int64_t i = 0; i < n_regions; ++i)
-        views[i] = RegionView{v.regions[i].reads, v.regions[i].n_reads, v.regions[i].haps, v.regions[i].n_haps, nullptr, nullptr};
+        views[i] = RegionView{v.regions[i].reads, nullptr, v.regions[i].n_reads, v.regions[i].haps, v.regions[i].n_haps, nullptr, nullptr, nullptr};
     Slot &s = h->slots[0];
     if ((st = pack_chunk(h, s, views.data(), views.size(), pack_threads(h))) != PAIRHMM_OK) return st;
     if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;

@@ -26,7 +26,9 @@ template <class T> struct DevBuf {
 
 // One region as the packer sees it (pointers borrowed from the caller).
 struct RegionView {
-    const phmm_read *reads; int32_t n_reads;
+    const phmm_read *reads;           // processed reads (the kernels' input), or
+    const phmm_raw_read *raw;         // reads as the BAM record holds them: the device runs the quality pre-pass (exactly one is set)
+    int32_t n_reads;
     const phmm_hap *haps; int32_t n_haps;
     double *out; uint8_t *resc;
     phmm_read_summary *summ;          // per-read epilogue results (nullable; only with an active epilogue)
@@ -50,6 +52,7 @@ struct RegionPlan {
     uint8_t gcp_min = 255, gcp_max = 0;    // range of the (masked) gap-continuation bytes of the unique reads
     std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
     std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
+    bool any_indel_q = false;            // raw reads: some read has its own insertion / deletion qualities
 };
 
 // Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
@@ -64,6 +67,7 @@ struct Slot {
     PinnedBuf<uint32_t> h_haplist;
     PinnedBuf<DevUnit> h_units;
     PinnedBuf<double> h_out;
+    PinnedBuf<int32_t> h_mapq;        // raw reads: mapping quality per unique read
     PinnedBuf<RowInfo> h_rows;        // epilogue: row of every unique read in the result matrix
     PinnedBuf<phmm_read_summary> h_summ;
     // device
@@ -75,6 +79,7 @@ struct Slot {
     DevBuf<DevUnit> d_units, d_rescue;
     DevBuf<float> d_fres;
     DevBuf<double> d_out;
+    DevBuf<int32_t> d_mapq;
     DevBuf<RowInfo> d_rows;
     DevBuf<phmm_read_summary> d_summ;
     // shape of the packed chunk
@@ -93,6 +98,9 @@ struct Slot {
     bool busy = false;
     bool ep_on = false;               // this chunk runs the fused epilogue (pairhmm_cuda_compute_*_normalized)
     pairhmm_cuda_epilogue ep{};
+    bool raw_on = false;              // this chunk holds raw reads: quality pre-pass on the device (pairhmm_cuda_compute_*_raw)
+    bool raw_indel_q = false;         //   ... and at least one of them brings its own insertion / deletion qualities
+    pairhmm_cuda_read_model model{};
     void release();
 };
 
@@ -118,4 +126,5 @@ struct pairhmm_cuda_handle {
     bool resident_loaded = false;
     bool ep_on = false;               // set for the duration of a *_normalized call
     pairhmm_cuda_epilogue ep{};
+    pairhmm_cuda_read_model model{};  // of the current *_raw call
 };

@@ -1,6 +1,8 @@
 // Auxiliary kernels (haplotype byte -> column-word expansion, FP32 result finalisation, rescue-unit scan) and the
 // dispatch from (variant, K, KL) to the forward_kernel instantiations of inst_*.cu. The forward kernel
 // itself is in forward.cuh.
+#include <algorithm>
+
 #include "forward2.cuh"
 
 namespace phmm {
@@ -57,6 +59,75 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     const int bin = k32 * (k32 - 1) / 2 + (len - 1) % k32;
     const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
     a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list, unit_shape(nh, 1u, 0u), out};
+}
+
+// ---------------------------------------------------------------------------------------------
+// Read quality pre-pass. Device restatement of GATKVariantContextUtils::findNumberOfRepetitions
+// (GATKVariantContextUtils.cpp:59-100) and PairHMMLikelihoodCalculationEngine::findTandemRepeatUnits (PHLCE.cpp:177-254).
+__device__ __forceinline__ bool equal_range(const uint8_t *a, const uint8_t *b, int n) {
+    for (int i = 0; i < n; ++i) if (a[i] != b[i]) return false;
+    return true;
+}
+__device__ int count_repetitions(const uint8_t *unit, int unit_len, const uint8_t *test, int test_len, bool leading) {
+    if (test_len == 0) return 0;
+    const int diff = test_len - unit_len;
+    int n = 0;
+    if (leading) {
+        for (int start = 0; start <= diff; start += unit_len) { if (equal_range(test + start, unit, unit_len)) ++n; else return n; }
+    } else {
+        for (int start = diff; start >= 0; start -= unit_len) { if (equal_range(test + start, unit, unit_len)) ++n; else return n; }
+    }
+    return n;
+}
+__device__ int tandem_repeat_length(const uint8_t *bases, int len, int offset) {
+    int max_bw = 0, bw_off = offset, bw_len = 1;              // bestBWRepeatUnit = {readBases[offset]}
+    for (int str = 1; str <= 8; ++str) {                      // MAX_STR_UNIT_LENGTH
+        if (offset + 1 - str < 0) break;
+        max_bw = count_repetitions(bases + offset - str + 1, str, bases, offset + 1, false);
+        if (max_bw > 1) { bw_off = offset - str + 1; bw_len = str; break; }
+    }
+    int max_rl = max_bw;
+    if (offset < len - 1) {
+        int max_fw = 0, fw_off = offset + 1, fw_len = 1;      // bestFWRepeatUnit = {readBases[offset+1]}
+        for (int str = 1; str <= 8; ++str) {
+            if (offset + str + 1 > len) break;
+            max_fw = count_repetitions(bases + offset + 1, str, bases + offset + 1, len - offset - 1, true);
+            if (max_fw > 1) { fw_off = offset + 1; fw_len = str; break; }
+        }
+        if (fw_len == bw_len && equal_range(bases + fw_off, bases + bw_off, fw_len)) {
+            max_rl = max_fw + max_bw;                          // in the middle of a tandem repeat
+        } else {
+            max_bw = count_repetitions(bases + fw_off, fw_len, bases, offset + 1, false);   // PHLCE.cpp:244-247
+            max_rl = max_fw + max_bw;
+        }
+    }
+    return max_rl > 20 ? 20 : max_rl;                          // MAX_REPEAT_LENGTH
+}
+
+// applyPCRErrorModel (PHLCE.cpp:150-158: positions 0 .. len-2) + capMinimumReadQualities (:256-267), in place
+__global__ void prep_reads_kernel(const PrepReadsArgs a) {
+    __shared__ uint8_t sb[kMaxReadLen];
+    for (uint32_t r = blockIdx.x; r < a.n; r += gridDim.x) {
+        const DevRead rr = a.reads[r];
+        const int mapq = a.mapq[r];
+        uint8_t *p = a.rd + rr.off;
+        __syncthreads();
+        for (int i = threadIdx.x; i < rr.len; i += blockDim.x) sb[i] = p[i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < rr.len; i += blockDim.x) {
+            int iq = p[2 * a.plane + i], dq = p[3 * a.plane + i];
+            if (a.pcr_on && i < rr.len - 1) {
+                const int q = a.pcr_table[tandem_repeat_length(sb, rr.len, i)];
+                iq = min(iq, q); dq = min(dq, q);
+            }
+            int bq = min((int)p[a.plane + i], mapq);
+            bq = (int)(uint8_t)bq;
+            if (bq < (int)(uint8_t)a.base_q_threshold) bq = 6;   // QualityUtils::MIN_USABLE_Q_SCORE
+            if (iq < 6) iq = 6;
+            if (dq < 6) dq = 6;
+            p[a.plane + i] = (uint8_t)bq; p[2 * a.plane + i] = (uint8_t)iq; p[3 * a.plane + i] = (uint8_t)dq;
+        }
+    }
 }
 
 // Per-read epilogue. The operations and their order are those of the reference's host code, so that the result equals
@@ -124,6 +195,13 @@ cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st) {
     if (a.n_units == 0) return cudaSuccess;
     const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
     rescue_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prep_reads(const PrepReadsArgs &a, int sm_count, cudaStream_t st) {
+    if (a.n == 0) return cudaSuccess;
+    const uint32_t grid = std::min<uint32_t>(a.n, (uint32_t)sm_count * 16u);
+    prep_reads_kernel<<<grid, 128, 0, st>>>(a);
     return cudaGetLastError();
 }
 

@@ -120,6 +120,18 @@ struct EpilogueArgs {
     int32_t do_cap, natural_log;
 };
 
+// Read quality pre-pass on the device (include/pairhmm_cuda.h, phmm_raw_read): rewrites the base / insertion / deletion
+// quality planes in place from the raw bytes; one CTA per read at a time, one thread per base.
+struct PrepReadsArgs {
+    uint8_t *rd;                  // read planes (bases | base_q | ins_q | del_q | gcp)
+    uint64_t plane;
+    const DevRead *reads;
+    const int32_t *mapq;          // per read
+    uint32_t n;
+    int32_t pcr_on, base_q_threshold;
+    uint8_t pcr_table[24];        // getErrorModelAdjustedQual(repeat length 0..20), host libm
+};
+
 struct FinalizeArgs {
     const float *fres;
     double *out;
@@ -174,6 +186,7 @@ cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a,
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
 cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st);
+cudaError_t launch_prep_reads(const PrepReadsArgs &a, int sm_count, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
 int forward_blocks_per_sm(Variant v, int W, int K, int KL);
 // whether (variant, W, K) was instantiated (the general / exact / FP64 kernels exist at W = 32 only)

@@ -19,6 +19,8 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_resident_load", "pairhmm_cuda_resident_run", "pairhmm_cuda_resident_fetch",
     "pairhmm_cuda_resident_fetch_raw",
     "pairhmm_cuda_compute_normalized", "pairhmm_cuda_compute_batch_normalized", "pairhmm_cuda_compute_flat_normalized",
+    "pairhmm_cuda_default_read_model", "pairhmm_cuda_compute_raw", "pairhmm_cuda_compute_batch_raw",
+    "pairhmm_cuda_compute_flat_raw", "pairhmm_cuda_prepare_reads_flat",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
 ]
 MM_COUNT = 8256
@@ -72,6 +74,15 @@ class Epilogue(C.Structure):
         super().__init__(float(likelihood_cap), float(max_error_per_base), 1 if natural_log else 0, 0)
 
 
+class ReadModel(C.Structure):
+    """pairhmm_cuda_read_model: PCR error model (rate factor), base quality threshold, constant gap-continuation penalty"""
+    _fields_ = [("pcr_rate_factor", C.c_int32), ("base_quality_threshold", C.c_int32), ("constant_gcp", C.c_int32),
+                ("reserved", C.c_int32)]
+
+    def __init__(self, pcr_rate_factor=3, base_quality_threshold=18, constant_gcp=10):
+        super().__init__(int(pcr_rate_factor), int(base_quality_threshold), int(constant_gcp), 0)
+
+
 # phmm_read_summary as a numpy record
 SUMMARY_DTYPE = np.dtype([("best", np.float64), ("second_best", np.float64), ("best_hap", np.int32),
                           ("poorly_modeled", np.uint8), ("pad", np.uint8, (3,))])
@@ -115,6 +126,10 @@ def load_library():
                                                     C.POINTER(Epilogue), vp, vp, vp]
     lib.pairhmm_cuda_compute_batch_normalized.argtypes = [vp, C.POINTER(PhmmRegion), i64, C.POINTER(Epilogue), vp]
     lib.pairhmm_cuda_compute_flat_normalized.argtypes = [vp] + flat + [C.POINTER(Epilogue), vp, vp, vp]
+    lib.pairhmm_cuda_default_read_model.argtypes = [C.POINTER(ReadModel)]
+    lib.pairhmm_cuda_default_read_model.restype = None
+    lib.pairhmm_cuda_compute_flat_raw.argtypes = [vp] + flat + [C.POINTER(ReadModel), vp, vp]
+    lib.pairhmm_cuda_prepare_reads_flat.argtypes = [vp] * 6 + [vp, vp, i64, C.POINTER(ReadModel), vp, vp, vp, vp]
     lib.pairhmm_cuda_resident_load.argtypes = [vp] + flat
     lib.pairhmm_cuda_resident_run.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.pairhmm_cuda_resident_fetch.argtypes = [vp, vp, vp]
@@ -266,6 +281,34 @@ class Engine:
         self._check(self.lib.pairhmm_cuda_compute_flat_normalized(self.h, *self._flat_args(b), C.byref(ep),
                                                                   out.ctypes.data, resc.ctypes.data, summ.ctypes.data))
         return out, resc, summ
+
+    # ---- raw reads: quality pre-pass on the device ----
+    def prepare_reads(self, b, base_q_raw, mapq, ins_q=None, del_q=None, model=None):
+        """the pre-pass alone on the reads of RegionBatch b (its bases / offsets) with raw qualities ->
+        (base_q, ins_q, del_q, gcp) as the kernels will see them"""
+        m = model or ReadModel()
+        bq = _u8(base_q_raw); mq = np.ascontiguousarray(mapq, np.int32)
+        iq = None if ins_q is None else _u8(ins_q); dq = None if del_q is None else _u8(del_q)
+        outs = [np.zeros(bq.shape[0], np.uint8) for _ in range(4)]
+        self._check(self.lib.pairhmm_cuda_prepare_reads_flat(
+            self.h, b.read_bases.ctypes.data, bq.ctypes.data, None if iq is None else iq.ctypes.data,
+            None if dq is None else dq.ctypes.data, mq.ctypes.data, b.read_off.ctypes.data, b.read_len.ctypes.data,
+            b.n_reads, C.byref(m), *[o.ctypes.data for o in outs]))
+        return tuple(outs)
+
+    def compute_batch_raw(self, b, base_q_raw, mapq, ins_q=None, del_q=None, model=None):
+        """RegionBatch b (bases, offsets, haplotypes, regions) with raw qualities -> (log10[n_pairs], rescued[n_pairs])"""
+        m = model or ReadModel()
+        bq = _u8(base_q_raw); mq = np.ascontiguousarray(mapq, np.int32)
+        iq = None if ins_q is None else _u8(ins_q); dq = None if del_q is None else _u8(del_q)
+        out = np.zeros(b.n_pairs, np.float64); resc = np.zeros(b.n_pairs, np.uint8)
+        self._check(self.lib.pairhmm_cuda_compute_flat_raw(
+            self.h, b.read_bases.ctypes.data, bq.ctypes.data, None if iq is None else iq.ctypes.data,
+            None if dq is None else dq.ctypes.data, mq.ctypes.data, b.read_off.ctypes.data, b.read_len.ctypes.data,
+            b.n_reads, b.hap_bases.ctypes.data, b.hap_off.ctypes.data, b.hap_len.ctypes.data, b.n_haps,
+            b.reg_read_start.ctypes.data, b.reg_hap_start.ctypes.data, b.n_regions, C.byref(m), out.ctypes.data,
+            resc.ctypes.data))
+        return out, resc
 
     def resident_load(self, b):
         self._check(self.lib.pairhmm_cuda_resident_load(self.h, *self._flat_args(b)))

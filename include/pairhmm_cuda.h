@@ -209,6 +209,61 @@ int pairhmm_cuda_compute_flat_normalized(pairhmm_cuda_handle *h, const uint8_t *
                                          int64_t n_regions, const pairhmm_cuda_epilogue *ep, double *log10_out,
                                          uint8_t *rescued_out, phmm_read_summary *summary_out);
 
+/* ---- device-side read quality pre-pass ---------------------------------------------------
+ * Takes reads as the BAM record holds them and does on the device what
+ * PairHMMLikelihoodCalculationEngine::modifyReadQualities does on the host before every PairHMM call
+ * (PairHMMLikelihoodCalculationEngine.cpp:123-148): applyPCRErrorModel (:150-158, tandem-repeat scan
+ * findTandemRepeatUnits :177-254), capMinimumReadQualities (:256-267: base quality capped by the mapping quality, below
+ * base_quality_threshold -> 6; insertion / deletion qualities below 6 -> 6), and the constant gap-continuation penalty of
+ * buildGapContinuationPenalties (:284-292). Only bases and base qualities (and BI/BD arrays where a read has them)
+ * cross PCIe: 2 bytes per base instead of 5. */
+typedef struct phmm_raw_read {
+    const uint8_t *bases;
+    const uint8_t *base_q;   /* getBaseQualities()                                                    */
+    const uint8_t *ins_q;    /* existing base insertion qualities, or NULL = default 45 (ReadUtils.h:40) */
+    const uint8_t *del_q;    /* existing base deletion qualities, or NULL = default 45                 */
+    int32_t len;
+    int32_t mapq;            /* getMappingQuality()                                                    */
+} phmm_raw_read;
+
+typedef struct phmm_raw_region {
+    const phmm_raw_read *reads;
+    int32_t n_reads;
+    const phmm_hap *haps;
+    int32_t n_haps;
+    double *log10_out;       /* [n_reads * n_haps], read-major */
+    uint8_t *rescued_out;    /* nullable */
+} phmm_raw_region;
+
+typedef struct pairhmm_cuda_read_model {
+    int32_t pcr_rate_factor;        /* PCRErrorModel: HOSTILE 1, AGGRESSIVE 2, CONSERVATIVE 3 (the default,            */
+                                    /* LikelihoodEngineArgumentCollection.h:30); 0 = no PCR adjustment (GATK's NONE)   */
+    int32_t base_quality_threshold; /* BASE_QUALITY_SCORE_THRESHOLD, 18; must be >= 6 (PHLCE.cpp:39)                   */
+    int32_t constant_gcp;           /* gcpHMM, 10                                                                      */
+    int32_t reserved;
+} pairhmm_cuda_read_model;
+void pairhmm_cuda_default_read_model(pairhmm_cuda_read_model *m);
+
+int pairhmm_cuda_compute_raw(pairhmm_cuda_handle *h, const phmm_raw_read *reads, int n_reads, const phmm_hap *haps,
+                             int n_haps, const pairhmm_cuda_read_model *model, double *log10_out, uint8_t *rescued_out);
+int pairhmm_cuda_compute_batch_raw(pairhmm_cuda_handle *h, const phmm_raw_region *regions, int64_t n_regions,
+                                   const pairhmm_cuda_read_model *model);
+/* Flat form: ins_q / del_q may be NULL (every read takes the default); mapq[n_reads]. */
+int pairhmm_cuda_compute_flat_raw(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                  const uint8_t *ins_q, const uint8_t *del_q, const int32_t *mapq,
+                                  const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                  const uint8_t *hap_bases, const int64_t *hap_off, const int32_t *hap_len,
+                                  int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
+                                  int64_t n_regions, const pairhmm_cuda_read_model *model, double *log10_out,
+                                  uint8_t *rescued_out);
+/* The pre-pass alone (test hook and stand-alone use): processed base / insertion / deletion / gap-continuation
+ * qualities of every read, each array laid out like base_q (read_off, read_len). */
+int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
+                                    const uint8_t *ins_q, const uint8_t *del_q, const int32_t *mapq,
+                                    const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
+                                    const pairhmm_cuda_read_model *model, uint8_t *out_base_q, uint8_t *out_ins_q,
+                                    uint8_t *out_del_q, uint8_t *out_gcp);
+
 int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);
 int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h);
 const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h);

@@ -72,6 +72,9 @@ class Oracle(_Lib):
         self.lib.oracle_epilogue.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_double, C.c_double, C.c_int,
                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         self.lib.oracle_epilogue.restype = None
+        self.lib.oracle_prepare_read.argtypes = [C.c_void_p] * 4 + [C.c_int] * 5 + [C.c_void_p] * 4
+        self.lib.oracle_prepare_read.restype = None
+        self.lib.oracle_tandem_repeat_length.argtypes = [C.c_void_p, C.c_int, C.c_int]
 
     def epilogue(self, m, read_len, likelihood_cap=-4.5, max_error_per_base=0.02, natural_log=False):
         """m[n_reads, n_haps] (copied) -> (normalised m, best, second_best, best_hap, poorly_modeled)"""
@@ -82,6 +85,25 @@ class Oracle(_Lib):
         self.lib.oracle_epilogue(m.ctypes.data, n, nh, rl.ctypes.data, float(likelihood_cap), float(max_error_per_base),
                                  int(natural_log), best.ctypes.data, second.ctypes.data, bh.ctypes.data, pm.ctypes.data)
         return m, best, second, bh, pm
+
+    def prepare_reads(self, read_bases, base_q, mapq, read_off, read_len, ins_q=None, del_q=None, pcr_rate_factor=3,
+                      base_q_threshold=18, constant_gcp=10):
+        """the caller's quality pre-pass (modifyReadQualities) on flat read arrays -> (base_q, ins_q, del_q, gcp)"""
+        bases = np.ascontiguousarray(read_bases, np.uint8); bq = np.ascontiguousarray(base_q, np.uint8)
+        outs = [np.zeros(bq.shape[0], np.uint8) for _ in range(4)]
+        iq = None if ins_q is None else np.ascontiguousarray(ins_q, np.uint8)
+        dq = None if del_q is None else np.ascontiguousarray(del_q, np.uint8)
+        for i in range(len(read_len)):
+            o, n = int(read_off[i]), int(read_len[i])
+            self.lib.oracle_prepare_read(bases.ctypes.data + o, bq.ctypes.data + o,
+                                         None if iq is None else iq.ctypes.data + o,
+                                         None if dq is None else dq.ctypes.data + o, n, int(mapq[i]), pcr_rate_factor,
+                                         base_q_threshold, constant_gcp, *[x.ctypes.data + o for x in outs])
+        return tuple(outs)
+
+    def tandem_repeat_length(self, bases, offset):
+        b = np.frombuffer(bytes(bases), np.uint8)
+        return int(self.lib.oracle_tandem_repeat_length(b.ctypes.data, len(b), int(offset)))
 
     def forward_float(self, b):
         """raw 2^120-scaled FP32 sums (FTZ on, no FMA) for every pair of a FlatPairs"""

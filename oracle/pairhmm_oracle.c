@@ -261,3 +261,90 @@ void oracle_epilogue(double *m, int64_t n_reads, int32_t n_haps, const int32_t *
         if (poorly_modeled) poorly_modeled[r] = poorly;
     }
 }
+
+/* ---- read quality pre-pass (see pairhmm_oracle.h) ---- */
+/* GATKVariantContextUtils::findNumberOfRepetitions, GATKVariantContextUtils.cpp:59-100 */
+static int count_repetitions(const uint8_t *unit_full, int unit_off, int unit_len, const uint8_t *test_full, int test_off,
+                             int test_len, int leading) {
+    if (test_len == 0) return 0;
+    const int diff = test_len - unit_len;
+    int n = 0;
+    if (leading) {
+        for (int start = 0; start <= diff; start += unit_len) {
+            if (memcmp(test_full + test_off + start, unit_full + unit_off, (size_t)unit_len) == 0) n++;   /* Utils::equalRange */
+            else return n;
+        }
+    } else {
+        for (int start = diff; start >= 0; start -= unit_len) {
+            if (memcmp(test_full + test_off + start, unit_full + unit_off, (size_t)unit_len) == 0) n++;
+            else return n;
+        }
+    }
+    return n;
+}
+
+/* PairHMMLikelihoodCalculationEngine::findTandemRepeatUnits, PHLCE.cpp:177-254 (MAX_STR_UNIT_LENGTH 8, MAX_REPEAT_LENGTH 20) */
+int oracle_tandem_repeat_length(const uint8_t *bases, int len, int offset) {
+    int max_bw = 0, bw_off = offset, bw_len = 1;              /* bestBWRepeatUnit = {readBases[offset]} */
+    for (int str = 1; str <= 8; str++) {
+        if (offset + 1 - str < 0) break;
+        max_bw = count_repetitions(bases, offset - str + 1, str, bases, 0, offset + 1, 0);
+        if (max_bw > 1) { bw_off = offset - str + 1; bw_len = str; break; }
+    }
+    int max_rl = max_bw;
+    if (offset < len - 1) {
+        int max_fw = 0, fw_off = offset + 1, fw_len = 1;      /* bestFWRepeatUnit = {readBases[offset+1]} */
+        for (int str = 1; str <= 8; str++) {
+            if (offset + str + 1 > len) break;
+            max_fw = count_repetitions(bases, offset + 1, str, bases, offset + 1, len - offset - 1, 1);
+            if (max_fw > 1) { fw_off = offset + 1; fw_len = str; break; }
+        }
+        if (fw_len == bw_len && memcmp(bases + fw_off, bases + bw_off, (size_t)fw_len) == 0) {
+            max_rl = max_fw + max_bw;                          /* in the middle of a tandem repeat */
+        } else {
+            /* does the FW unit also repeat backwards from here? (:244-247) */
+            max_bw = count_repetitions(bases + fw_off, 0, fw_len, bases, 0, offset + 1, 0);
+            max_rl = max_fw + max_bw;
+        }
+    }
+    return max_rl > 20 ? 20 : max_rl;
+}
+
+/* getErrorModelAdjustedQual / initializePCRErrorModel, PHLCE.cpp:45-61; MathUtils::fastRound MathUtils.cpp:65-68 */
+void oracle_pcr_table(int pcr_rate_factor, uint8_t table[21]) {
+    for (int i = 0; i <= 20; i++) {
+        const double d = 40.0 - exp((double)i / ((double)pcr_rate_factor * 3.14159265358979323846 /* M_PI */));
+        const int r = d > 0.0 ? (int)(d + 0.5) : (int)(d - 0.5);
+        const int q = r + 1 > 10 ? r + 1 : 10;                 /* MIN_ADJUSTED_QSCORE */
+        table[i] = (uint8_t)(char)q;
+    }
+}
+
+void oracle_prepare_read(const uint8_t *bases, const uint8_t *base_q, const uint8_t *ins_q, const uint8_t *del_q,
+                         int len, int mapq, int pcr_rate_factor, int base_q_threshold, int constant_gcp,
+                         uint8_t *out_base_q, uint8_t *out_ins_q, uint8_t *out_del_q, uint8_t *out_gcp) {
+    uint8_t table[21];
+    for (int i = 0; i < len; i++) {
+        out_base_q[i] = base_q[i];
+        out_ins_q[i] = ins_q ? ins_q[i] : 45;                  /* ReadUtils.cpp:254-262 */
+        out_del_q[i] = del_q ? del_q[i] : 45;
+        out_gcp[i] = (uint8_t)constant_gcp;                    /* PHLCE.cpp:284-292 */
+    }
+    if (pcr_rate_factor > 0) {                                 /* applyPCRErrorModel, :150-158: positions 0 .. len-2 */
+        oracle_pcr_table(pcr_rate_factor, table);
+        for (int i = 1; i < len; i++) {
+            const int rl = oracle_tandem_repeat_length(bases, len, i - 1);
+            const int q = 0xff & table[rl];
+            if (q < (0xff & out_ins_q[i - 1])) out_ins_q[i - 1] = (uint8_t)q;
+            if (q < (0xff & out_del_q[i - 1])) out_del_q[i - 1] = (uint8_t)q;
+        }
+    }
+    for (int i = 0; i < len; i++) {                            /* capMinimumReadQualities, :256-267; MIN_USABLE_Q_SCORE 6 */
+        int q = 0xff & out_base_q[i];
+        if (mapq < q) q = mapq;
+        out_base_q[i] = (uint8_t)q;
+        if (out_base_q[i] < (uint8_t)base_q_threshold) out_base_q[i] = 6;
+        if (out_ins_q[i] < 6) out_ins_q[i] = 6;
+        if (out_del_q[i] < 6) out_del_q[i] = 6;
+    }
+}

@@ -41,6 +41,20 @@ double oracle_compute(const uint8_t *read_bases, const uint8_t *base_q, const ui
 void oracle_epilogue(double *m, int64_t n_reads, int32_t n_haps, const int32_t *read_len, double likelihood_cap,
                      double max_error_per_base, int natural_log, double *best, double *second_best,
                      int32_t *best_hap, uint8_t *poorly_modeled);
+/* Quality pre-pass the caller runs on every read before the PairHMM:
+ * PairHMMLikelihoodCalculationEngine::modifyReadQualities (PairHMMLikelihoodCalculationEngine.cpp:123-148) =
+ * applyPCRErrorModel (:150-158, tandem repeats by findTandemRepeatUnits :177-254 over
+ * GATKVariantContextUtils::findNumberOfRepetitions, GATKVariantContextUtils.cpp:59-100, quality table
+ * getErrorModelAdjustedQual :45-61) + capMinimumReadQualities (:256-267), and the constant gap-continuation array of
+ * buildGapContinuationPenalties (:284-292). ins_q / del_q NULL = ReadUtils' default 45 (ReadUtils.cpp:254-262,
+ * ReadUtils.h:40). pcr_rate_factor = the PCRErrorModel enum value (HOSTILE 1, AGGRESSIVE 2, CONSERVATIVE 3); 0 = no PCR
+ * adjustment (GATK's NONE; the reference has no such value). PARITY UNPINNED: these functions sit in translation units
+ * that need the whole Mutect2Cpp build (htslib, boost), so they are restated, not compiled from the reference. */
+int oracle_tandem_repeat_length(const uint8_t *bases, int len, int offset);
+void oracle_pcr_table(int pcr_rate_factor, uint8_t table[21]);
+void oracle_prepare_read(const uint8_t *bases, const uint8_t *base_q, const uint8_t *ins_q, const uint8_t *del_q,
+                         int len, int mapq, int pcr_rate_factor, int base_q_threshold, int constant_gcp,
+                         uint8_t *out_base_q, uint8_t *out_ins_q, uint8_t *out_del_q, uint8_t *out_gcp);
 #ifdef __cplusplus
 }
 #endif

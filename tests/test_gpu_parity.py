@@ -301,3 +301,82 @@ def test_fused_epilogue_region_call_duplicates_and_empty_reads(engine, oracle):
     # the plain entry points are unaffected by an earlier normalised call
     again, _ = engine.compute(reads, haps)
     assert np.array_equal(again, raw)
+
+
+def _raw_quals(b, seed, with_indel):
+    """raw (BAM-like) qualities for the reads of batch b: base qualities 2..41, mapping quality 0..60 per read"""
+    rng = np.random.default_rng(seed)
+    n = b.read_bases.shape[0]
+    bq = rng.integers(2, 42, n).astype(np.uint8)
+    mapq = rng.integers(0, 61, b.n_reads).astype(np.int32)
+    iq = rng.integers(0, 61, n).astype(np.uint8) if with_indel else None
+    dq = rng.integers(0, 61, n).astype(np.uint8) if with_indel else None
+    return bq, mapq, iq, dq
+
+
+def _repeat_rich_batch(seed=5):
+    """reads full of homopolymers and short tandem repeats (what the PCR error model keys on), lengths 1..384"""
+    rng = np.random.default_rng(seed)
+    lens = [1, 2, 3, 8, 9, 31, 32, 33, 150, 151, 250, 384] + [int(x) for x in rng.integers(10, 300, 60)]
+    reads = []
+    for n in lens:
+        s = []
+        while len(s) < n:
+            unit = rng.choice(list(b"ACGT"), int(rng.integers(1, 9)))
+            s.extend(list(unit) * int(rng.integers(1, 12)))
+            if rng.random() < 0.3:
+                s.append(ord("N"))
+        reads.append(np.array(s[:n], np.uint8))
+    b = synth.config1("clean")
+    return synth.RegionBatch(np.concatenate(reads), np.zeros(sum(lens), np.uint8), np.zeros(sum(lens), np.uint8),
+                             np.zeros(sum(lens), np.uint8), np.zeros(sum(lens), np.uint8),
+                             np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64), np.array(lens, np.int32),
+                             b.hap_bases, b.hap_off, b.hap_len, np.array([0, len(lens)], np.int64),
+                             np.array([0, b.n_haps], np.int64), "repeat-rich")
+
+
+@pytest.mark.parametrize("with_indel", [False, True])
+@pytest.mark.parametrize("pcr", [0, 1, 2, 3])
+def test_device_read_prepass_equals_oracle(engine, oracle, with_indel, pcr):
+    """prep_reads_kernel (applyPCRErrorModel + capMinimumReadQualities + constant gcp on the device) against the oracle's
+    restatement of PairHMMLikelihoodCalculationEngine.cpp:123-267: every byte equal"""
+    for b in (_repeat_rich_batch(), synth.config2(2)):
+        bq, mapq, iq, dq = _raw_quals(b, 11 + pcr, with_indel)
+        model = fgdp_b200.pairhmm.ReadModel(pcr, 18, 10)
+        got = engine.prepare_reads(b, bq, mapq, iq, dq, model)
+        want = oracle.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq, pcr, 18, 10)
+        for g, w, name in zip(got, want, ("base_q", "ins_q", "del_q", "gcp")):
+            assert np.array_equal(g, w), (b.name, name, np.nonzero(g != w)[0][:5])
+
+
+@pytest.mark.parametrize("with_indel", [False, True])
+def test_raw_read_entry_point_equals_prepared_reads(engine, oracle, with_indel):
+    """pairhmm_cuda_compute_flat_raw = device pre-pass + PairHMM: identical to feeding the oracle-prepared qualities to the
+    plain entry point, and within the parity bar of the CPU oracle on them"""
+    for b in (_repeat_rich_batch(), synth.config2(3)):
+        bq, mapq, iq, dq = _raw_quals(b, 3, with_indel)
+        got, gresc = engine.compute_batch_raw(b, bq, mapq, iq, dq)
+        pb, pi, pd, pg = oracle.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq)
+        pbatch = synth.RegionBatch(b.read_bases, pb, pi, pd, pg, b.read_off, b.read_len, b.hap_bases, b.hap_off, b.hap_len,
+                                   b.reg_read_start, b.reg_hap_start, b.name + "-prepared")
+        same, sresc = engine.compute_batch(pbatch)
+        assert np.array_equal(got, same) and np.array_equal(gresc, sresc)
+        want, wresc, _ = oracle.compute(pbatch.as_flat(), threads=4)
+        assert_parity(got, gresc, want, wresc, what="raw " + b.name)
+    st = engine.stats()
+    assert st["kernel_launches"] > 0
+    with pytest.raises(fgdp_b200.PairHMMError):
+        engine.compute_batch_raw(b, bq, mapq, iq, dq, fgdp_b200.pairhmm.ReadModel(7, 18, 10))
+
+
+def test_raw_read_entry_point_large_batch_multithreaded_pack(engine):
+    """> 65536 reads: the flat raw entry point builds its views on several host threads and the call spans several chunks"""
+    b = synth.config2(400)
+    assert b.n_reads > 70000
+    bq, mapq, _, _ = _raw_quals(b, 9, False)
+    got, gresc = engine.compute_batch_raw(b, bq, mapq)
+    pb, pi, pd, pg = engine.prepare_reads(b, bq, mapq)
+    pbatch = synth.RegionBatch(b.read_bases, pb, pi, pd, pg, b.read_off, b.read_len, b.hap_bases, b.hap_off, b.hap_len,
+                               b.reg_read_start, b.reg_hap_start, b.name + "-prepared")
+    same, sresc = engine.compute_batch(pbatch)
+    assert np.array_equal(got, same) and np.array_equal(gresc, sresc)

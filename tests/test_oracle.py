@@ -125,3 +125,34 @@ def test_epilogue_oracle_vs_live_reference(oracle):
         mo, best, second, bh, pm = oracle.epilogue(m, rl, cap, rate, bool(nl))
         mr, removed = ref.epilogue(m, rl, cap, rate, bool(nl))
         assert np.array_equal(mo, mr) and np.array_equal(pm, removed), t
+
+
+def test_read_prepass_oracle_known_answers(oracle):
+    """oracle_prepare_read / oracle_tandem_repeat_length (restating PairHMMLikelihoodCalculationEngine.cpp:123-267):
+    hand-derived known answers. PARITY UNPINNED for this row -- the reference functions sit in translation units that do
+    not compile without the whole Mutect2Cpp build (oracle/pairhmm_oracle.h)."""
+    s = b"ACGTTTTTTGCACACACACAGGATTCTTC"
+    # offset 2 ('G' before T x 6): BW unit G x1, FW unit T x6, FW unit does not repeat backwards -> 6;
+    # offset 8 (last T): BW unit T x6 but FW unit G x1 differs and does not repeat backwards -> 1 (GATK's behaviour);
+    # offsets 9..15 (GCACACAC): alternating 5 / 4 repeats of CA / AC
+    want = [1, 1, 6, 6, 6, 6, 6, 6, 1, 5, 4, 5, 4, 5, 4, 5, 1, 1, 1, 2, 2, 1, 2, 2, 1, 2, 2, 1, 2]
+    assert [oracle.tandem_repeat_length(s, i) for i in range(len(s))] == want
+    assert oracle.tandem_repeat_length(b"A" * 50, 10) == 20            # MAX_REPEAT_LENGTH
+    assert oracle.tandem_repeat_length(b"A", 0) == 1
+    # getErrorModelAdjustedQual(i, 3) = max(10, round(40 - exp(i / (3 pi))) + 1)
+    import ctypes as C
+    t = (C.c_uint8 * 21)(); oracle.lib.oracle_pcr_table(3, t)
+    assert list(t) == [max(10, int(40.0 - np.exp(i / (3 * np.pi)) + 0.5) + 1) for i in range(21)]
+    assert t[0] == 40 and t[20] == 33
+    # one read: base quality capped by MAPQ 25 then < 18 -> 6; indel default 45 lowered by the PCR table except at
+    # the last base (applyPCRErrorModel stops at len-2); gcp constant
+    bq = np.full(len(s), 30, np.uint8); bq[3] = 10; bq[5] = 17
+    b, i, d, g = oracle.prepare_reads(np.frombuffer(s, np.uint8), bq, [25], [0], [len(s)])
+    assert list(b) == [25, 25, 25, 6, 25, 6] + [25] * 23
+    assert list(i) == [t[w] for w in want[:-1]] + [45] and list(d) == list(i) and set(g) == {10}
+    # existing indel qualities below 6 are raised to 6, above the table value lowered to it; no PCR model = untouched
+    iq = np.full(len(s), 3, np.uint8); dq = np.full(len(s), 60, np.uint8)
+    b, i, d, g = oracle.prepare_reads(np.frombuffer(s, np.uint8), bq, [60], [0], [len(s)], ins_q=iq, del_q=dq)
+    assert set(i) == {6} and list(d) == [t[w] for w in want[:-1]] + [60] and b[0] == 30
+    b, i, d, g = oracle.prepare_reads(np.frombuffer(s, np.uint8), bq, [60], [0], [len(s)], ins_q=iq, del_q=dq, pcr_rate_factor=0)
+    assert set(d) == {60}
