@@ -41,7 +41,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--regions", type=int, default=10000, help="regions per rank (10000 = BASELINE configs[1])")
+    ap.add_argument("--regions", type=int, default=0, help="c2: regions per rank (default 10000 = BASELINE configs[1]); "
+                                                            "c5: regions of the whole job (default 25000 = configs[4])")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
+                    help="c2 = BASELINE configs[1] per GPU (weak scaling, the metric's config); c5 = configs[4], the "
+                         "whole-box chr20-scale batch LPT-sharded over the ranks (strong scaling)")
     ap.add_argument("--cpu-sample-regions", type=int, default=0, help="regions in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -153,6 +157,8 @@ def run_reference_arm(args, rank, world):
 
 def main():
     args = parse_args()
+    if args.regions <= 0:
+        args.regions = 25000 if args.workload == "c5" else 10000
     rank, world, local = dist_env()
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
@@ -194,13 +200,23 @@ def main():
     # weak scaling: the job is world x BASELINE configs[1]; its regions are split over the ranks by cost
     # (DP cells) with the LPT rule -- every rank derives the same split from the region shapes
     # and generates only its own regions. With one rank this is exactly configs[1].
-    if world > 1:
+    if args.workload == "c5":
+        # strong scaling: the job is fixed (configs[4]), its regions are LPT-split over the ranks
+        _, cost = synth.config5_shapes(args.regions)
+        batch = synth.config5(args.regions, select=synth.lpt_shard(cost, world)[rank] if world > 1 else None)
+        workload = ("BASELINE configs[4]: chr20-scale synthetic batch, %d regions x 200 reads x 10 haps, 150 bp reads, "
+                    "300-500 bp haps, whole job LPT-sharded over %d GPU(s)" % (args.regions, world))
+    elif world > 1:
         _, _, cost = synth.config2_shapes(args.regions * world)
         batch = synth.config2(args.regions * world, select=synth.lpt_shard(cost, world)[rank])
     else:
         batch = synth.config2(args.regions)
+    if args.workload == "c2":
+        workload = ("BASELINE configs[1]: synthetic WES-like batch, %d regions, ~200 reads x 4-16 haps, "
+                    "150 bp reads, 250-500 bp haps, per GPU" % args.regions)
     cells, pairs = batch.cells(), batch.n_pairs
-    eng = fgdp_b200.Engine(device=local)
+    # several ranks share the box's host threads: split them instead of 16 packing threads per rank
+    eng = fgdp_b200.Engine(device=local, pack_threads=0 if world == 1 else max(2, min(16, (os.cpu_count() or 16) // world)))
     eng.initialize(int(batch.read_len.max()), int(batch.hap_len.max()))
 
     # ---- device-resident replay: `value` and the roofline of the FP32 forward kernel
@@ -273,7 +289,7 @@ def main():
                 "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None}
     try:    # DRAM bytes of one launch of that kernel over this workload, from the committed ncu capture (profiles/)
         tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        if tr.get("regions") == args.regions and world == 1:
+        if tr.get("regions") == args.regions and world == 1 and args.workload == "c2":
             roofline["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
             roofline["traffic_source"] = tr["source"]
     except Exception:
@@ -284,11 +300,10 @@ def main():
         cpu = cpu_reference_run(batch.subset(range(n_reg)), os.cpu_count() or 1)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "isa", "sample")}
     line = {"metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.workload == "c5" else "weak",
+            "vs_baseline": None,
             "dtype": "f32+f64-rescue", "data": "synthetic",
-            "config": {"workload": "BASELINE configs[1]: synthetic WES-like batch, %d regions, ~200 reads x 4-16 haps, "
-                                   "150 bp reads, 250-500 bp haps, per GPU" % args.regions,
-                       "pairs_per_gpu": pairs, "cells_per_gpu": cells, "rescued_frac": float(resc.mean()),
+            "config": {"workload": workload, "pairs_per_gpu": pairs, "cells_per_gpu": cells, "rescued_frac": float(resc.mean()),
                        "l2": "inputs (%.2f GB of read planes + haplotype words per GPU) exceed the 126 MB L2" %
                              ((batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4) / 1e9),
                        "parallelism": "%d rank(s), regions LPT-sharded by DP cells, no collective on the data path" % world},

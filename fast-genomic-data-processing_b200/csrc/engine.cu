@@ -116,12 +116,23 @@ inline uint64_t mix64(uint64_t x) {
     x ^= x >> 32; x *= 0xd6e8feb86659fd93ull; x ^= x >> 32; x *= 0xd6e8feb86659fd93ull; x ^= x >> 32;
     return x;
 }
+// De-duplication hash of a byte string: four independent multiply-xor lanes (one multiply per 8 bytes, no serial
+// avalanche per word -- hashing the five arrays of every read was the largest part of the host packing time), one
+// avalanche at the end. Equal hashes are always confirmed by memcmp (same_read), so quality only affects speed.
+inline uint64_t rotl64(uint64_t x, int r) { return (x << r) | (x >> (64 - r)); }
 uint64_t hash_bytes(const uint8_t *p, size_t n, uint64_t h) {
+    constexpr uint64_t M = 0x9e3779b97f4a7c15ull;
+    uint64_t a = h, b = h ^ 0x243f6a8885a308d3ull, c = h ^ 0x13198a2e03707344ull, d = h ^ 0xa4093822299f31d0ull;
     size_t i = 0;
-    for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, p + i, 8); h = mix64(h ^ w) + 0x9e3779b97f4a7c15ull; }
+    for (; i + 32 <= n; i += 32) {
+        uint64_t w[4]; std::memcpy(w, p + i, 32);
+        a = (a ^ w[0]) * M; b = (b ^ w[1]) * M; c = (c ^ w[2]) * M; d = (d ^ w[3]) * M;
+        a ^= a >> 29; b ^= b >> 29; c ^= c >> 29; d ^= d >> 29;
+    }
+    for (; i + 8 <= n; i += 8) { uint64_t w; std::memcpy(&w, p + i, 8); a = (a ^ w) * M; a ^= a >> 29; }
     uint64_t w = 0;
     if (i < n) std::memcpy(&w, p + i, n - i);
-    return mix64(h ^ w ^ (uint64_t)n);
+    return mix64(a ^ rotl64(b, 17) ^ rotl64(c, 31) ^ rotl64(d, 47) ^ w ^ ((uint64_t)n << 56));
 }
 // a read of either kind: processed (five arrays) or raw (bases, base_q, optional ins_q / del_q, mapping quality)
 struct ReadRef { const uint8_t *bases, *base_q, *ins_q, *del_q, *gcp; int32_t len, mapq; };
@@ -201,9 +212,19 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             if (rv.raw) {                           // constant by construction (buildGapContinuationPenalties)
                 pl.gcp_min = pl.gcp_max = (uint8_t)(h->model.constant_gcp & 127);
                 pl.any_indel_q |= r.ins_q != nullptr || r.del_q != nullptr;
-            } else for (int q = 0; q < r.len; ++q) {       // gap-continuation range, as the kernel sees it (&127)
-                const uint8_t c = r.gcp[q] & 127;
-                pl.gcp_min = std::min(pl.gcp_min, c); pl.gcp_max = std::max(pl.gcp_max, c);
+            } else {                                // gap-continuation range, as the kernel sees it (&127)
+                // the usual case is one constant (buildGapContinuationPenalties): compare 8 bytes at a time against the first
+                const uint8_t c0 = r.gcp[0] & 127;
+                const uint64_t bc = 0x0101010101010101ull * c0, m7 = 0x7f7f7f7f7f7f7f7full;
+                uint64_t diff = 0;
+                int q = 0;
+                for (; q + 8 <= r.len; q += 8) { uint64_t w; std::memcpy(&w, r.gcp + q, 8); diff |= (w & m7) ^ bc; }
+                for (; q < r.len; ++q) diff |= (uint64_t)((r.gcp[q] & 127) ^ c0);
+                if (!diff) { pl.gcp_min = std::min(pl.gcp_min, c0); pl.gcp_max = std::max(pl.gcp_max, c0); }
+                else for (q = 0; q < r.len; ++q) {
+                    const uint8_t c = r.gcp[q] & 127;
+                    pl.gcp_min = std::min(pl.gcp_min, c); pl.gcp_max = std::max(pl.gcp_max, c);
+                }
             }
         }
         pl.uniq_of_read[i] = u;
@@ -303,7 +324,9 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
                       : (s.uniform_gcp && !h->cfg.reserved[0]) ? (h->cfg.reserved[2] ? Variant::F32_UG : Variant::F32_PK)
                       : Variant::F32_GEN;
     const int forced_w = h->cfg.reserved[1];
+    const double ms_plan = ms_since(t0);
     parallel_for(n_regs, threads, 8, [&](size_t i) { bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w); });
+    const double ms_bin = ms_since(t0);
 
     // prefix sums
     uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0;
@@ -363,6 +386,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
+    const double ms_reserve = ms_since(t0);
     // pass B: copy bytes, fill descriptors and units
     parallel_for(n_regs, threads, 4, [&](size_t i) {
         const RegionView &rv = s.regions[i];
@@ -415,6 +439,9 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         }
     });
     h->stats.host_ms_pack += ms_since(t0);
+    if (trace_on())
+        std::fprintf(stderr, "[trace] pack %u reads: plan %.1f | bin %.1f | prefix+reserve %.1f | copy %.1f ms (%d threads)\n", s.n_uniq,
+                     ms_plan, ms_bin - ms_plan, ms_reserve - ms_bin, ms_since(t0) - ms_reserve, threads);
     return PAIRHMM_OK;
 }
 

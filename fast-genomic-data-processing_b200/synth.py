@@ -299,13 +299,22 @@ def config4(n_regions=64, n_reads=128, n_haps=8, profile="clean"):
                       foreign_frac=0.02)
 
 
-def config5(n_regions=25000, profile="clean", shard=0):
-    """C5: chr20-scale, regions x 200 reads x 10 haps, R=150, H in [300,500] (configs[4]); `shard`
-    reseeds so every rank / shard gets distinct regions."""
+def config5_shapes(n_regions=25000, shard=0):
+    """region shapes of C5 without generating any bases: (list of haplotype lengths, cost = DP cells per region)"""
     rng = np.random.default_rng(SEED0 + 5 + 7919 * shard)
     hls = [rng.integers(300, 501, size=10) for _ in range(n_regions)]
-    return make_batch(SEED0 + 5 + 104729 * shard, [200] * n_regions, hls, 150, profile,
-                      name="C5-%s-%d-s%d" % (profile, n_regions, shard), foreign_frac=0.02)
+    cost = np.array([200 * 150 * int(h.sum()) for h in hls], np.int64)
+    return hls, cost
+
+
+def config5(n_regions=25000, profile="clean", shard=0, select=None):
+    """C5: chr20-scale, regions x 200 reads x 10 haps, R=150, H in [300,500] (configs[4]); `shard`
+    reseeds so every rank / shard gets distinct regions; `select` = indices of the regions to actually generate
+    (one rank's part of an LPT split of the whole job)."""
+    hls, _ = config5_shapes(n_regions, shard)
+    ids = np.arange(n_regions) if select is None else np.asarray(select, np.int64)
+    return make_batch(SEED0 + 5 + 104729 * shard, [200] * len(ids), [hls[i] for i in ids], 150, profile,
+                      name="C5-%s-%d-s%d" % (profile, len(ids), shard), foreign_frac=0.02, region_ids=ids)
 
 
 def edge_cases(seed=1234):
