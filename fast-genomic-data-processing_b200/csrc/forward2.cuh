@@ -237,7 +237,8 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
 
         int cur = -1;
         uint32_t tix1 = 32 - sl;                       // lane l sees l PAD tiles, then [PAD.., SEP] (tile 31)
-        Tile w = tiles[tix1 - 1], w1 = tiles[tix1];    // current and next tile; tix1 = index of w1
+        const Tile *tp = tiles + tix1;                 // points at w1
+        Tile w = tp[-1], w1 = tp[0];                  // current and next tile; tix1 = index of w1
 
         // one DP column for this lane's K rows (computeMXY, template.h:177-192)
         auto column = [&](uint32_t cw, V Dd, V Uu) {
@@ -280,26 +281,6 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 a.flag[o] = 1;
             }
         };
-        // SEP word = column 0 of the next haplotype: emit the finished one, switch. Runs before the columns of its
-        // tile: they are all flagged (a SEP sits in slot 0 of its own tile, or closes the all-PAD lead-in), add 0 to the
-        // sums and ignore the boundary values, so the order does not matter. PAD words need no handler at all.
-        auto next_haplotype = [&](uint32_t &next_tix) {
-            if ((uint32_t)cur < unit_nh) {
-                const V r = P::add(sumM, sumX);                                    // template.h:339-343
-                if (sl == last_a && valid_a) emit_result(P::lo(r), out_a);
-                if constexpr (P::kReads == 2)
-                    if (sl == last_b && valid_b) emit_result(P::hi(r), out_b);
-            }
-            ++cur;
-            sumM = sumX = P::zero();
-            S initY = (S)0;
-            next_tix = 32;                                                         // drain PAD tiles
-            if ((uint32_t)cur < unit_nh) { const HapRow hi = hap_info[cur]; next_tix = hi.tix; initY = hi.initY; }
-            // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
-            Dbound = P::bc(initY * Num<S>::ugapm(a));
-            if (lane0) Din[C - 1] = Dbound;            // becomes Dprev of the next step's first column
-        };
-
         // one pipeline step = the C columns of this lane's current tile. DIRTY steps are those in which some lane of the
         // warp may hold a SEP tile (the W steps after a haplotype boundary enters lane 0); all others run the branch-free
         // CLEAN instance, whose body is a single basic block.
@@ -309,13 +290,31 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 bool sep = false;
 #pragma unroll
                 for (int j = 0; j < C; ++j) sep |= (tw_get(w, j) & 0xC0000000u) == 0x80000000u;
-                if (sep) {
-                    uint32_t target = tix1;
-                    next_haplotype(target);
-                    // a unit's haplotypes lie back to back in hapw, so the sequential guess is right except after the
-                    // lead-in and before the drain
-                    if (target != tix1) { tix1 = target; w1 = __ldg(tiles + tix1); }
+                // SEP word = column 0 of the next haplotype: emit the finished one, switch. Done before the columns of the
+                // tile: they are all flagged (a SEP sits in slot 0 of its own tile, or closes the all-PAD lead-in), add 0 to
+                // the sums and ignore the boundary values, so the order does not matter; PAD words need nothing at all.
+                // Exactly one lane of the group holds the SEP in each dirty step, so a divergent handler would run every
+                // time with one lane active: the switch is written as selects instead (+1.4 % on the FP32 pass), only the
+                // result store of the lane that owns a read's last row is a branch
+                if (sep && (uint32_t)cur < unit_nh) {
+                    const V r = P::add(sumM, sumX);                                // template.h:339-343
+                    if (sl == last_a && valid_a) emit_result(P::lo(r), out_a);
+                    if constexpr (P::kReads == 2)
+                        if (sl == last_b && valid_b) emit_result(P::hi(r), out_b);
                 }
+                cur += sep ? 1 : 0;
+                sumM = P::sel(sep, P::zero(), sumM);
+                sumX = P::sel(sep, P::zero(), sumX);
+                const bool has = (uint32_t)cur < unit_nh;
+                const HapRow hi = hap_info[has ? cur : 0];
+                const uint32_t target = has ? hi.tix : 32u;                        // 32 = drain PAD tiles
+                const S initY = has ? hi.initY : (S)0;
+                // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
+                Dbound = P::sel(sep, P::bc(initY * Num<S>::ugapm(a)), Dbound);
+                Din[C - 1] = P::sel(sep && lane0, Dbound, Din[C - 1]);   // becomes Dprev of the next step's first column
+                // a unit's haplotypes lie back to back in hapw, so the sequential guess is right except after the
+                // lead-in, before the drain and between the haplotypes of a rescue unit
+                if (sep && target != tix1) { tix1 = target; tp = tiles + tix1; w1 = __ldg(tp); }
             }
             V Dout[C], Uout[C];
 #pragma unroll
@@ -333,8 +332,8 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
             // rotate the tile queue at the END of the step: w is dead by now, so the load can land in a free register and
             // nothing waits for it here; it is consumed two steps later (a full step of latency hiding)
             w = w1;
-            ++tix1;
-            w1 = __ldg(tiles + tix1);
+            ++tix1; ++tp;
+            w1 = __ldg(tp);
         };
         // haplotype boundary h enters lane 0 at the start of segment h and leaves lane W-1 W steps later; segment nh
         // is the drain
