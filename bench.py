@@ -119,10 +119,10 @@ def cpu_reference_run(batch, threads, want_seconds=None):
     else:
         lib, kind, isa = oracle_py.load_oracle(), "port", "scalar C"
     flat = batch.as_flat()
-    _, _, secs = lib.compute(flat, threads=threads, tables_in_timed_region=True, want_rescued=False)
+    out, _, secs = lib.compute(flat, threads=threads, tables_in_timed_region=True, want_rescued=False)
     cells = batch.cells()
     return {"value": cells / secs / 1e9, "unit": "GCUPS", "cores": threads, "kind": kind, "isa": isa,
-            "seconds": secs, "cells": cells,
+            "seconds": secs, "cells": cells, "log10": out, "lib": lib, "flat": flat,
             "sample": "%d regions of the same workload (%d pairs, %.3g cells), per-read tables built inside the timed region"
                       % (batch.n_regions, batch.n_pairs, cells)}
 
@@ -297,8 +297,24 @@ def main():
     cpu = None
     if not args.no_cpu_baseline:
         n_reg = args.cpu_sample_regions or min(args.regions, 160)
-        cpu = cpu_reference_run(batch.subset(range(n_reg)), os.cpu_count() or 1)
-        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "isa", "sample")}
+        threads = os.cpu_count() or 1
+        cpu = cpu_reference_run(batch.subset(range(n_reg)), threads)
+        # the same sample with the per-read tables built before the timed region (the GPU's kernel-only
+        # number has its counterpart), and the correctness gate of this very run: the engine's results on the sample's
+        # pairs (the first regions of the batch) against the CPU reference's
+        _, _, secs_pre = cpu["lib"].compute(cpu["flat"], threads=threads, tables_in_timed_region=False, want_rescued=False)
+        n_s = cpu["log10"].shape[0]
+        gate_regions = min(n_reg, 24)
+        sub = batch.subset(range(gate_regions))
+        _, want_resc, _ = cpu["lib"].compute(sub.as_flat(), threads=threads)
+        n_g = sub.n_pairs
+        fin = np.isfinite(cpu["log10"])
+        parity = {"pairs": int(n_s), "max_abs_dlog10": float(np.abs(out[:n_s][fin] - cpu["log10"][fin]).max()),
+                  "mean_abs_dlog10": float(np.abs(out[:n_s][fin] - cpu["log10"][fin]).mean()),
+                  "tolerance": 1e-4, "rescue_set_identical": bool(np.array_equal(rs[:n_g], want_resc)),
+                  "rescue_set_pairs_checked": int(n_g), "against": cpu["kind"]}
+        cpu["value_tables_prebuilt"] = cpu["cells"] / secs_pre / 1e9
+        cpu = {k: cpu[k] for k in ("value", "value_tables_prebuilt", "unit", "cores", "kind", "isa", "sample")}
     line = {"metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.workload == "c5" else "weak",
             "vs_baseline": None,
@@ -311,6 +327,8 @@ def main():
                     "d2h_bytes_per_step": st["d2h_bytes"] // args.steps, "ms_per_step": e2e_s * 1e3,
                     "host_pack_ms_per_step": st["host_ms_pack"] / args.steps, "identical_to_resident_run": same},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks}
+    if cpu is not None:
+        line["parity"] = parity
     print(json.dumps(line), flush=True)
     del ctypes
 

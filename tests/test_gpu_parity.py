@@ -380,3 +380,30 @@ def test_raw_read_entry_point_large_batch_multithreaded_pack(engine):
                                b.reg_read_start, b.reg_hap_start, b.name + "-prepared")
     same, sresc = engine.compute_batch(pbatch)
     assert np.array_equal(got, same) and np.array_equal(gresc, sresc)
+
+
+def test_handles_on_concurrent_host_threads(oracle):
+    """SURVEY.md 8(b) threading: one handle per host thread (as one PairHMM per Mutect2Cpp worker, M2/main.cpp:199), calls
+    from different threads fully concurrent (ctypes drops the GIL inside the library)."""
+    import threading
+    batches = [synth.config2(6, seed_extra=k) for k in range(4)]
+    wants = [oracle.compute(b.as_flat(), threads=4)[:2] for b in batches]
+    results, errors = [None] * 4, []
+
+    def worker(k):
+        try:
+            e = fgdp_b200.Engine()
+            try:
+                for _ in range(3):
+                    results[k] = e.compute_batch(batches[k])
+            finally:
+                e.close()
+        except Exception as ex:   # noqa: BLE001
+            errors.append(ex)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors
+    for k in range(4):
+        assert_parity(results[k][0], results[k][1], wants[k][0], wants[k][1], what="thread %d" % k)
