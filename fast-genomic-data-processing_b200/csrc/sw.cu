@@ -1,0 +1,316 @@
+// Batched Smith-Waterman with backtrace for sm_100a (include/smithwaterman_cuda.h).
+//
+// One warp per alignment, claimed from an atomic queue by a persistent grid. The affine-gap recurrence of the reference
+// (MAIN_CODE, M2/intel/smithwaterman/PairWiseSW.h:27-62) is swept one anti-diagonal at a time -- the cells of an
+// anti-diagonal are independent, lanes take consecutive columns j -- with the last two anti-diagonals of H and the last
+// one of E, F kept in shared memory indexed by column. Each cell writes one backtrace byte (move | INSERT_EXT |
+// DELETE_EXT, smithwaterman_common.h:44-49) into a per-warp scratch area in anti-diagonal-major order, so the stores
+// of a warp are consecutive bytes. The best cell (last row / last column, visited in anti-diagonal order with the
+// reference's tie rules, :227-251), the backtrace state machine and the CIGAR text (getCIGAR, :265-447) follow the
+// reference step for step; runs of plain matches are walked 32 cells at a time (every lane fetches one cell of the diagonal).
+// Integer work, HBM/L2-bound on the backtrace bytes: no tensor cores.
+#include <algorithm>
+#include <climits>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/smithwaterman_cuda.h"
+
+namespace sw {
+
+constexpr int kWarps = 4;                       // warps per CTA
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int BT_MATCH = 0, BT_INSERT = 1, BT_DELETE = 2, BT_INSERT_EXT = 4, BT_DELETE_EXT = 8;
+constexpr int32_t kMinCutoff = -100000000;      // MATRIX_MIN_CUTOFF
+constexpr int32_t kLowInit = INT_MIN / 2;       // LOW_INIT_VALUE
+
+struct Args {
+    const uint8_t *ref_bases, *alt_bases;
+    const int64_t *ref_off, *alt_off;
+    const int32_t *ref_len, *alt_len;
+    uint32_t n;
+    int32_t match, mismatch, open, extend, strategy;
+    char *cigars;
+    int32_t cigar_stride;
+    int32_t *offsets;
+    uint8_t *scratch;                           // per resident warp: backtrace bytes, then the CIGAR element list
+    uint64_t scratch_per_warp;
+    uint32_t bt_width;                          // max alt length + 1
+    uint32_t max_ref, max_alt;
+    uint32_t *queue;
+};
+
+// ints of shared memory one warp needs
+__host__ __device__ inline size_t warp_smem_ints(uint32_t max_ref, uint32_t max_alt) {
+    const size_t c = max_alt + 2, r = max_ref + 2;
+    return 7 * c + r + (c + 3) / 4 + (r + 3) / 4;          // H x3, E x2, F, lastrow | lastcol | alt bytes | ref bytes
+}
+
+__device__ __forceinline__ int digits_of(int v) { int d = 0; while (v > 0) { v /= 10; ++d; } return d; }
+
+__global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
+    extern __shared__ int32_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t C = a.max_alt + 2, R = a.max_ref + 2;
+    int32_t *base = smem + (size_t)warp * warp_smem_ints(a.max_ref, a.max_alt);
+    int32_t *Hb[3] = {base, base + C, base + 2 * C};
+    int32_t *Eb[2] = {base + 3 * C, base + 4 * C};
+    int32_t *F = base + 5 * C, *lastrow = base + 6 * C, *lastcol = base + 7 * C;
+    uint8_t *alt = reinterpret_cast<uint8_t *>(lastcol + R), *ref = alt + ((C + 3) / 4) * 4;
+    const uint32_t gwarp = blockIdx.x * kWarps + warp;
+    uint8_t *bt = a.scratch + (uint64_t)gwarp * a.scratch_per_warp;
+    const bool indel = a.strategy == SW_CUDA_INDEL || a.strategy == SW_CUDA_LEADING_INDEL;
+
+    for (;;) {
+        uint32_t p = 0;
+        if (lane == 0) p = atomicAdd(a.queue, 1u);
+        p = __shfl_sync(kFull, p, 0);
+        if (p >= a.n) break;
+        const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
+        const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
+        __syncwarp();
+        for (int k = lane; k < nrow; k += 32) ref[k] = rp[k];
+        for (int k = lane; k < ncol; k += 32) alt[k] = ap[k];
+        for (int j = lane; j <= ncol; j += 32) F[j] = kLowInit;         // F[0][j] (PairWiseSW.h:98-101,224)
+        if (lane == 0) Hb[1][0] = 0;                                    // H[0][0]: anti-diagonal 0 = the "ad-1" buffer of the first step
+        __syncwarp();
+
+        // ---- forward sweep over anti-diagonals ad = i + j
+        int h0 = 0, h1 = 1, h2 = 2, e1 = 0, e2 = 1;                     // buffers of ad-2, ad-1, ad
+        for (int ad = 1; ad <= nrow + ncol; ++ad) {
+            int32_t *H0 = Hb[h0], *H1 = Hb[h1], *H2 = Hb[h2], *E1 = Eb[e1], *E2 = Eb[e2];
+            if (lane == 0) {
+                // boundary cells of this anti-diagonal (:214-225): (0, ad) on the top row, (ad, 0) in the left column
+                if (ad <= ncol) H2[ad] = indel ? a.open + (ad - 1) * a.extend : 0;
+                if (ad <= nrow) { H2[0] = indel ? a.open + (ad - 1) * a.extend : 0; E2[0] = kLowInit; }
+            }
+            const int jlo = max(1, ad - nrow), jhi = min(ncol, ad - 1);
+            uint8_t *btd = bt + (uint64_t)ad * a.bt_width;
+            for (int j = jlo + lane; j <= jhi; j += 32) {
+                const int i = ad - j;
+                const int32_t ext_h = E1[j - 1] + a.extend, open_h = H1[j - 1] + a.open;
+                const int32_t e = max(open_h, ext_h);
+                int b = open_h > ext_h ? 0 : BT_INSERT_EXT;
+                const int32_t ext_v = F[j] + a.extend, open_v = H1[j] + a.open;
+                const int32_t f = max(ext_v, open_v);
+                if (!(open_v > ext_v)) b |= BT_DELETE_EXT;
+                const int32_t m = H0[j - 1] + (ref[i - 1] == alt[j - 1] ? a.match : a.mismatch);
+                int32_t h = max(kMinCutoff, m);
+                int mv = e > h ? BT_INSERT : BT_MATCH;
+                h = max(h, e);
+                if (f > h) { mv = BT_DELETE; h = f; }
+                E2[j] = e; F[j] = f; H2[j] = h;
+                btd[j] = (uint8_t)(mv | b);
+                if (i == nrow) lastrow[j] = h;
+                if (j == ncol) lastcol[i] = h;
+            }
+            __syncwarp();
+            const int t = h0; h0 = h1; h1 = h2; h2 = t;
+            e1 ^= 1; e2 ^= 1;
+        }
+
+        // ---- best cell: last row (SOFTCLIP / IGNORE only) and last column in anti-diagonal order (:227-251). Every lane
+        // runs the same scalar code (shared-memory broadcasts), so there is no divergence and all lanes know the result.
+        int32_t max_score = INT_MIN;
+        int max_i = 0, max_j = 0;
+        const bool row_too = a.strategy == SW_CUDA_SOFTCLIP || a.strategy == SW_CUDA_IGNORE;
+        for (int ad = 1; ad <= nrow + ncol; ++ad) {
+            if (ad >= nrow + 1 && row_too) {
+                const int j = ad - nrow;
+                const int32_t s = lastrow[j];
+                if (max_score < s || (max_score == s && abs(nrow - j) < abs(max_i - max_j))) { max_score = s; max_i = nrow; max_j = j; }
+            }
+            if (ad >= ncol + 1) {
+                const int i = ad - ncol;
+                const int32_t s = lastcol[i];
+                if (max_score < s || (max_score == s && (max_j == ncol || abs(i - ncol) <= abs(max_i - max_j)))) { max_score = s; max_i = i; max_j = ncol; }
+            }
+        }
+
+        // ---- backtrace (getCIGAR, :265-402), elements merged as they are produced (the reference merges equal
+        // neighbours afterwards, :404-421 -- same list)
+        int32_t *elems = reinterpret_cast<int32_t *>(bt + ((((uint64_t)a.max_ref + a.max_alt + 1) * a.bt_width + 7) & ~7ull));
+        int n_el = 0, cur_op = -1, cur_len = 0;
+        auto push = [&](int op, int len) {
+            if (n_el > 0 && op == cur_op) { cur_len += len; return; }
+            if (n_el > 0 && lane == 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
+            cur_op = op; cur_len = len; ++n_el;
+        };
+        int i, j;
+        if (a.strategy == SW_CUDA_INDEL) { i = nrow; j = ncol; }
+        else if (a.strategy == SW_CUDA_LEADING_INDEL) { i = max_i; j = ncol; }
+        else { i = max_i; j = max_j; }
+        if (j < ncol) push(SW_CUDA_SOFTCLIP, ncol - j);
+        int state = 0;
+        while (i > 0 && j > 0) {
+            if (state == 0) {
+                // lane l looks at (i - l, j - l): a run of plain matches is consumed in one step
+                const int ii = i - lane, jj = j - lane;
+                int btr = 0xff;
+                if (ii > 0 && jj > 0) btr = bt[(uint64_t)(ii + jj) * a.bt_width + jj];
+                const unsigned plain = __ballot_sync(kFull, ii > 0 && jj > 0 && (btr & 3) == BT_MATCH);
+                const int run = __ffs(~plain) - 1;                      // leading lanes that are plain matches (32 if all)
+                if (run != 0) {
+                    const int r = run < 0 ? 32 : run;
+                    push(BT_MATCH, r); i -= r; j -= r;                  // MATCH leaves state 0
+                    continue;
+                }
+                btr = __shfl_sync(kFull, btr, 0);
+                if ((btr & 3) == BT_INSERT) { --j; push(BT_INSERT, 1); state = btr & BT_INSERT_EXT; }
+                else { --i; push(BT_DELETE, 1); state = btr & BT_DELETE_EXT; }       // (btr & 3) == DELETE
+            } else {
+                const int btr = bt[(uint64_t)(i + j) * a.bt_width + j];
+                if (state == BT_INSERT_EXT) { --j; ++cur_len; state = btr & BT_INSERT_EXT; }
+                else { --i; ++cur_len; state = btr & BT_DELETE_EXT; }
+            }
+        }
+        int offset;
+        if (a.strategy == SW_CUDA_SOFTCLIP) {
+            if (j > 0) push(SW_CUDA_SOFTCLIP, j);
+            offset = i;
+        } else if (a.strategy == SW_CUDA_IGNORE) {
+            if (j > 0) push(n_el > 0 ? cur_op : BT_MATCH, j);
+            offset = (int16_t)(i - j);
+        } else {
+            if (i > 0) push(BT_DELETE, i);
+            else if (j > 0) push(BT_INSERT, j);
+            offset = 0;
+        }
+        // ---- CIGAR text, last element first (:423-445)
+        if (lane == 0) {
+            if (n_el > 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
+            char *out = a.cigars + (uint64_t)p * a.cigar_stride;
+            int cur = 0;
+            for (int k = n_el - 1; k >= 0; --k) {
+                const int op = elems[2 * k], v = elems[2 * k + 1], d = digits_of(v);
+                if (d + 1 > 1 && cur + d + 1 <= a.cigar_stride) {
+                    int x = v;
+                    for (int q = d - 1; q >= 0; --q) { out[cur + q] = (char)('0' + x % 10); x /= 10; }
+                    cur += d;
+                    out[cur++] = op == BT_MATCH ? 'M' : op == BT_INSERT ? 'I' : op == BT_DELETE ? 'D' : op == SW_CUDA_SOFTCLIP ? 'S' : 'R';
+                }
+            }
+            a.offsets[p] = offset;
+        }
+    }
+}
+
+thread_local std::string g_err;
+int fail(int st, const std::string &m) { g_err = m; return st; }
+
+template <class T> struct DevArr {
+    T *p = nullptr;
+    cudaError_t alloc(size_t n) { return cudaMalloc(reinterpret_cast<void **>(&p), std::max<size_t>(1, n) * sizeof(T)); }
+    ~DevArr() { if (p) cudaFree(p); }
+};
+
+}  // namespace sw
+
+extern "C" {
+
+const char *smithwaterman_cuda_last_error(void) { return sw::g_err.c_str(); }
+
+int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const int64_t *ref_off, const int32_t *ref_len,
+                                   const uint8_t *alt_bases, const int64_t *alt_off, const int32_t *alt_len, int64_t n,
+                                   int match, int mismatch, int open, int extend, int strategy, char *cigars,
+                                   int cigar_stride, int32_t *offsets, float *kernel_ms) {
+    using namespace sw;
+    if (kernel_ms) *kernel_ms = 0.f;
+    if (n < 0 || n > 0x7fffffff) return fail(SW_CUDA_ERR_ARG, "bad pair count");
+    if (n == 0) return SW_CUDA_OK;
+    if (!ref_bases || !ref_off || !ref_len || !alt_bases || !alt_off || !alt_len || !cigars || !offsets || cigar_stride < 1)
+        return fail(SW_CUDA_ERR_ARG, "null array or cigar_stride < 1");
+    if (strategy < SW_CUDA_SOFTCLIP || strategy > SW_CUDA_IGNORE) return fail(SW_CUDA_ERR_ARG, "unknown overhang strategy");
+    uint32_t max_ref = 1, max_alt = 1;
+    uint64_t ref_bytes = 0, alt_bytes = 0;
+    for (int64_t p = 0; p < n; ++p) {
+        if (ref_len[p] < 1 || alt_len[p] < 1 || ref_len[p] > SW_CUDA_MAX_LEN || alt_len[p] > SW_CUDA_MAX_LEN || ref_off[p] < 0 || alt_off[p] < 0)
+            return fail(SW_CUDA_ERR_ARG, "sequence length outside [1, SW_CUDA_MAX_LEN] or negative offset");
+        max_ref = std::max<uint32_t>(max_ref, (uint32_t)ref_len[p]); max_alt = std::max<uint32_t>(max_alt, (uint32_t)alt_len[p]);
+        ref_bytes = std::max<uint64_t>(ref_bytes, (uint64_t)ref_off[p] + (uint64_t)ref_len[p]);
+        alt_bytes = std::max<uint64_t>(alt_bytes, (uint64_t)alt_off[p] + (uint64_t)alt_len[p]);
+    }
+#define SWCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(SW_CUDA_ERR_CUDA, std::string(#x ": ") + cudaGetErrorString(e_)); } while (0)
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(SW_CUDA_ERR_NO_DEVICE, "no CUDA device (this aligner has no CPU fallback)"); }
+    if (device < 0) SWCU(cudaGetDevice(&device));
+    if (device >= ndev) return fail(SW_CUDA_ERR_ARG, "device ordinal out of range");
+    cudaDeviceProp prop;
+    SWCU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(SW_CUDA_ERR_NO_DEVICE, "not an sm_100 device (kernels are built for sm_100a only)");
+    SWCU(cudaSetDevice(device));
+
+    const size_t smem = kWarps * warp_smem_ints(max_ref, max_alt) * sizeof(int32_t);
+    if (smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
+    SWCU(cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_kernel, kWarps * 32, smem));
+    per_sm = std::max(1, per_sm);
+    const uint64_t bt_width = (uint64_t)max_alt + 1;
+    uint64_t per_warp = ((uint64_t)max_ref + max_alt + 1) * bt_width + 8ull * ((uint64_t)max_ref + max_alt + 6);
+    per_warp = (per_warp + 255) & ~255ull;
+    uint64_t grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, ((uint64_t)n + kWarps - 1) / kWarps);
+    const uint64_t budget = 8ull << 30;                                   // backtrace scratch of all resident warps
+    grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, budget / (per_warp * kWarps)));
+
+    DevArr<uint8_t> d_ref, d_alt, d_scratch;
+    DevArr<int64_t> d_roff, d_aoff;
+    DevArr<int32_t> d_rlen, d_alen, d_off;
+    DevArr<char> d_cig;
+    DevArr<uint32_t> d_queue;
+    SWCU(d_ref.alloc(ref_bytes)); SWCU(d_alt.alloc(alt_bytes)); SWCU(d_roff.alloc(n)); SWCU(d_aoff.alloc(n));
+    SWCU(d_rlen.alloc(n)); SWCU(d_alen.alloc(n)); SWCU(d_off.alloc(n)); SWCU(d_cig.alloc((size_t)n * cigar_stride));
+    SWCU(d_queue.alloc(1)); SWCU(d_scratch.alloc(per_warp * kWarps * grid));
+    cudaStream_t st;
+    SWCU(cudaStreamCreate(&st));
+    cudaEvent_t ev0, ev1;
+    cudaEventCreate(&ev0); cudaEventCreate(&ev1);
+    auto cleanup = [&]() { cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaStreamDestroy(st); };
+#define SWCU2(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(SW_CUDA_ERR_CUDA, std::string(#x ": ") + cudaGetErrorString(e_)); } } while (0)
+    SWCU2(cudaMemcpyAsync(d_ref.p, ref_bases, ref_bytes, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_alt.p, alt_bases, alt_bytes, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_roff.p, ref_off, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_aoff.p, alt_off, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_rlen.p, ref_len, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_alen.p, alt_len, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemsetAsync(d_cig.p, 0, (size_t)n * cigar_stride, st));
+    SWCU2(cudaMemsetAsync(d_queue.p, 0, sizeof(uint32_t), st));
+    Args a{};
+    a.ref_bases = d_ref.p; a.alt_bases = d_alt.p; a.ref_off = d_roff.p; a.alt_off = d_aoff.p; a.ref_len = d_rlen.p; a.alt_len = d_alen.p;
+    a.n = (uint32_t)n; a.match = match; a.mismatch = mismatch; a.open = open; a.extend = extend; a.strategy = strategy;
+    a.cigars = d_cig.p; a.cigar_stride = cigar_stride; a.offsets = d_off.p; a.scratch = d_scratch.p; a.scratch_per_warp = per_warp;
+    a.bt_width = (uint32_t)bt_width; a.max_ref = max_ref; a.max_alt = max_alt; a.queue = d_queue.p;
+    SWCU2(cudaEventRecord(ev0, st));
+    align_kernel<<<(unsigned)grid, kWarps * 32, smem, st>>>(a);
+    SWCU2(cudaGetLastError());
+    SWCU2(cudaEventRecord(ev1, st));
+    SWCU2(cudaMemcpyAsync(cigars, d_cig.p, (size_t)n * cigar_stride, cudaMemcpyDeviceToHost, st));
+    SWCU2(cudaMemcpyAsync(offsets, d_off.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));
+    SWCU2(cudaStreamSynchronize(st));
+    if (kernel_ms) cudaEventElapsedTime(kernel_ms, ev0, ev1);
+    cleanup();
+    return SW_CUDA_OK;
+#undef SWCU
+#undef SWCU2
+}
+
+int smithwaterman_cuda_align(uint8_t *ref, int ref_length, uint8_t *alt, int alt_length, uint8_t *cigar, int cigar_length,
+                             int match, int mismatch, int open, int extend, uint8_t strategy) {
+    const int64_t off0 = 0;
+    const int32_t rl = ref_length, al = alt_length;
+    int32_t offset = 0;
+    if (cigar_length < 1 || !cigar) { sw::fail(SW_CUDA_ERR_ARG, "no cigar buffer"); return INT_MIN; }
+    std::vector<char> tmp((size_t)cigar_length, 0);
+    const int st = smithwaterman_cuda_align_batch(-1, ref, &off0, &rl, alt, &off0, &al, 1, match, mismatch, open, extend, strategy,
+                                                  tmp.data(), cigar_length, &offset, nullptr);
+    if (st != SW_CUDA_OK) return INT_MIN;
+    std::memcpy(cigar, tmp.data(), (size_t)cigar_length);
+    return offset;
+}
+
+}  // extern "C"

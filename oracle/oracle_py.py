@@ -161,3 +161,54 @@ def reference_available():
 
 def load_reference():
     return Reference()
+
+
+# ---- Smith-Waterman ----
+SW_SOFTCLIP, SW_INDEL, SW_LEADING_INDEL, SW_IGNORE = 9, 10, 11, 12
+
+
+class SWPairs:
+    """flat list of (ref, alt) sequence pairs"""
+
+    def __init__(self, refs, alts):
+        cat = lambda xs: np.ascontiguousarray(np.concatenate(xs) if len(xs) else np.zeros(0, np.uint8), np.uint8)
+        self.n = len(refs)
+        self.ref_len = np.array([len(x) for x in refs], np.int32); self.alt_len = np.array([len(x) for x in alts], np.int32)
+        self.ref_off = np.concatenate([[0], np.cumsum(self.ref_len)[:-1]]).astype(np.int64) if self.n else np.zeros(0, np.int64)
+        self.alt_off = np.concatenate([[0], np.cumsum(self.alt_len)[:-1]]).astype(np.int64) if self.n else np.zeros(0, np.int64)
+        self.ref_bases = cat([np.frombuffer(bytes(x), np.uint8) for x in refs])
+        self.alt_bases = cat([np.frombuffer(bytes(x), np.uint8) for x in alts])
+        self.cigar_stride = int(2 * max([1] + list(self.ref_len) + list(self.alt_len)))   # IntelSmithWaterman.cpp:12
+
+    def cells(self):
+        return int((self.ref_len.astype(np.int64) * self.alt_len.astype(np.int64)).sum())
+
+
+def _sw_call(fn, p, params, strategy, extra=()):
+    cig = np.zeros((p.n, p.cigar_stride), np.uint8); off = np.zeros(p.n, np.int32)
+    r = fn(p.ref_bases.ctypes.data, p.ref_off.ctypes.data, p.ref_len.ctypes.data, p.alt_bases.ctypes.data,
+           p.alt_off.ctypes.data, p.alt_len.ctypes.data, p.n, *[int(x) for x in params], int(strategy), cig.ctypes.data,
+           p.cigar_stride, off.ctypes.data, *extra)
+    cigars = [bytes(row).split(b"\0")[0].decode() for row in cig]
+    return cigars, off, r
+
+
+_SW_ARGS = [C.c_void_p] * 6 + [C.c_int64] + [C.c_int] * 5 + [C.c_void_p, C.c_int, C.c_void_p]
+
+
+def oracle_sw(p, params=(10, -15, -30, -5), strategy=SW_SOFTCLIP):
+    lib = load_oracle().lib
+    lib.oracle_sw_align_batch.argtypes = _SW_ARGS; lib.oracle_sw_align_batch.restype = None
+    c, o, _ = _sw_call(lib.oracle_sw_align_batch, p, params, strategy)
+    return c, o
+
+
+def reference_sw_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_sw.so"))
+
+
+def reference_sw(p, params=(10, -15, -30, -5), strategy=SW_SOFTCLIP, threads=1):
+    """the reference's own SmithWaterman_align on every pair -> (cigars, offsets, seconds)"""
+    lib = C.CDLL(os.path.join(HERE, "_ref", "libref_sw.so"))
+    lib.ref_sw_align_batch.argtypes = _SW_ARGS + [C.c_int]; lib.ref_sw_align_batch.restype = C.c_double
+    return _sw_call(lib.ref_sw_align_batch, p, params, strategy, (int(threads),))

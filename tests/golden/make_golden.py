@@ -23,6 +23,35 @@ FIELDS = ("read_bases", "base_q", "ins_q", "del_q", "gcp", "read_off", "read_len
           "reg_read_start", "reg_hap_start")
 
 
+def sw_pairs(seed, n):
+    """(haplotype-like ref, read-like alt) pairs: reads cut from the ref with substitutions and indels, some unrelated,
+    some longer than the ref, some single bases"""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    refs, alts = [], []
+    for k in range(n):
+        H, R = int(rng.integers(1, 520)), int(rng.integers(1, 260))
+        hap = rng.choice(acgt, H)
+        if k % 6 == 0:
+            read = rng.choice(acgt, R)
+        else:
+            st = int(rng.integers(0, max(1, H - R)))
+            src, out = hap[st:st + R], []
+            for c in src:
+                r = rng.random()
+                if r < 0.03:
+                    out.append(int(rng.choice(acgt)))
+                elif r < 0.04:
+                    continue
+                elif r < 0.05:
+                    out.append(int(c)); out.extend(int(x) for x in rng.choice(acgt, int(rng.integers(1, 6))))
+                else:
+                    out.append(int(c))
+            read = np.array(out if out else [65], np.uint8)
+        refs.append(bytes(hap)); alts.append(bytes(read))
+    return refs, alts
+
+
 def main():
     ref = oracle_py.load_reference()
     gxx = subprocess.run(["g++", "--version"], capture_output=True, text=True).stdout.splitlines()[0]
@@ -76,6 +105,21 @@ def main():
     np.savez_compressed(os.path.join(HERE, "epilogue.npz"), n_cases=np.array(k), meta=np.array(
         "reference AlleleLikelihoods.h via oracle/ref_epilogue_driver.cpp; " + gxx), **ep)
     print("epilogue", k, "cases")
+    # Smith-Waterman: the reference's own SmithWaterman_align (oracle/_ref/libref_sw.so) on
+    # read-vs-haplotype-like pairs, every overhang strategy, the three parameter sets Mutect2Cpp uses
+    refs, alts = sw_pairs(0xB200 + 33, 160)
+    sp = oracle_py.SWPairs(refs, alts)
+    sw = {"ref_bases": sp.ref_bases, "ref_off": sp.ref_off, "ref_len": sp.ref_len, "alt_bases": sp.alt_bases,
+          "alt_off": sp.alt_off, "alt_len": sp.alt_len}
+    k = 0
+    for params in ((10, -15, -30, -5), (200, -150, -260, -11), (25, -50, -110, -6)):
+        for strat in (9, 10, 11, 12):
+            cig, off, _ = oracle_py.reference_sw(sp, params, strat, threads=4)
+            sw["par%d" % k] = np.array(list(params) + [strat]); sw["cig%d" % k] = np.array(cig); sw["off%d" % k] = off
+            k += 1
+    np.savez_compressed(os.path.join(HERE, "sw.npz"), n_cases=np.array(k), meta=np.array(
+        "reference SmithWaterman_align (M2/intel/smithwaterman) via oracle/ref_sw_driver.cpp; " + gxx), **sw)
+    print("sw", k, "cases x", sp.n, "pairs")
     pf, mf, pd, md = ref.tables()
     np.savez_compressed(os.path.join(HERE, "tables.npz"), ph2pr_f=pf, mm_f=mf[:8256], ph2pr_d=pd, mm_d=md[:8256], meta=np.array(meta))
 

@@ -1,0 +1,94 @@
+"""Smith-Waterman with backtrace: the C restatement (oracle/sw_oracle.c) against the reference's own
+aligner (golden vectors + live oracle/_ref/libref_sw.so), and -- marked gpu -- the CUDA aligner against the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_py
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _golden():
+    z = np.load(os.path.join(HERE, "golden", "sw.npz"))
+    refs = [bytes(z["ref_bases"][int(o):int(o) + int(n)]) for o, n in zip(z["ref_off"], z["ref_len"])]
+    alts = [bytes(z["alt_bases"][int(o):int(o) + int(n)]) for o, n in zip(z["alt_off"], z["alt_len"])]
+    cases = [(tuple(int(x) for x in z["par%d" % k][:4]), int(z["par%d" % k][4]), [str(c) for c in z["cig%d" % k]], z["off%d" % k])
+             for k in range(int(z["n_cases"]))]
+    return refs, alts, cases
+
+
+def test_sw_oracle_matches_reference_golden():
+    """every CIGAR string and offset equal to the committed outputs of the reference's SmithWaterman_align"""
+    refs, alts, cases = _golden()
+    p = oracle_py.SWPairs(refs, alts)
+    assert len(cases) == 12
+    for params, strat, cig, off in cases:
+        c, o = oracle_py.oracle_sw(p, params, strat)
+        assert c == cig and np.array_equal(o, off), (params, strat)
+
+
+def test_sw_oracle_vs_live_reference():
+    if not oracle_py.reference_sw_available():
+        pytest.skip("oracle/_ref/libref_sw.so not built (no /root/reference on this machine)")
+    import sys
+    sys.path.insert(0, os.path.join(HERE, "golden"))
+    from make_golden import sw_pairs
+    refs, alts = sw_pairs(99, 300)
+    p = oracle_py.SWPairs(refs, alts)
+    for params in ((10, -15, -30, -5), (200, -150, -260, -11)):
+        for strat in (9, 10, 11, 12):
+            c, o = oracle_py.oracle_sw(p, params, strat)
+            rc, ro, _ = oracle_py.reference_sw(p, params, strat, threads=4)
+            assert c == rc and np.array_equal(o, ro), (params, strat)
+
+
+def test_sw_known_alignments():
+    """hand-checkable cases"""
+    p = oracle_py.SWPairs([b"ACGTACGTAC", b"AAAACCCCGGGG", b"ACGT"], [b"ACGTACGTAC", b"AAAAGGGG", b"TTACGTTT"])
+    c, o = oracle_py.oracle_sw(p, (10, -15, -30, -5), oracle_py.SW_SOFTCLIP)
+    assert c[0] == "10M" and o[0] == 0
+    assert c[1] == "4M4D4M" and o[1] == 0
+    assert c[2] == "2S4M2S" and o[2] == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("strategy", [9, 10, 11, 12])
+def test_cuda_sw_equals_oracle(strategy):
+    """smithwaterman_cuda_align_batch: CIGAR text and offset identical to the oracle (itself identical to the reference)"""
+    from fgdp_b200 import smithwaterman as sw
+    refs, alts, cases = _golden()
+    for params, strat, cig, off in cases:
+        if strat != strategy:
+            continue
+        c, o, ms = sw.align_batch(refs, alts, params, strat)
+        bad = [k for k in range(len(refs)) if c[k] != cig[k] or o[k] != off[k]]
+        assert not bad, (params, strat, bad[:3], [(c[k], cig[k], int(o[k]), int(off[k])) for k in bad[:3]])
+
+
+@pytest.mark.gpu
+def test_cuda_sw_batch_of_read_realignments():
+    """the call Mutect2Cpp makes after the PairHMM (AlignmentUtils.cpp:498): every read against a haplotype, parameters
+    (10, -15, -30, -5), SOFTCLIP -- a few thousand pairs through one launch, plus the single-pair drop-in entry point"""
+    import sys
+    sys.path.insert(0, os.path.join(HERE, "golden"))
+    from make_golden import sw_pairs
+    from fgdp_b200 import smithwaterman as sw
+    refs, alts = sw_pairs(7, 3000)
+    p = oracle_py.SWPairs(refs, alts)
+    want_c, want_o = oracle_py.oracle_sw(p)
+    c, o, ms = sw.align_batch(refs, alts)
+    assert c == want_c and np.array_equal(o, want_o)
+    assert ms > 0
+    import ctypes as C
+    lib = sw._lib()
+    for k in (0, 5, 17):
+        r = np.frombuffer(refs[k], np.uint8).copy(); a = np.frombuffer(alts[k], np.uint8).copy()
+        n = 2 * max(len(r), len(a))
+        buf = np.zeros(n, np.uint8)
+        off = lib.smithwaterman_cuda_align(r.ctypes.data_as(C.c_void_p), len(r), a.ctypes.data_as(C.c_void_p), len(a),
+                                           buf.ctypes.data_as(C.c_void_p), n, 10, -15, -30, -5, 9)
+        assert off == want_o[k] and bytes(buf).split(b"\0")[0].decode() == want_c[k]
+    with pytest.raises(Exception):
+        sw.align_batch([b""], [b"A"])
