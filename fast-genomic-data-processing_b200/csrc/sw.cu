@@ -58,8 +58,9 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t C = a.max_alt + 2, R = a.max_ref + 2;
     int32_t *base = smem + (size_t)warp * warp_smem_ints(a.max_ref, a.max_alt);
-    int32_t *Hb[3] = {base, base + C, base + 2 * C};
-    int32_t *Eb[2] = {base + 3 * C, base + 4 * C};
+    // H (3 anti-diagonals) and E (2) rotate by OFFSET into `base`, not by pointer: the accesses stay LDS/STS with 32-bit
+    // addresses (an array of pointers made them generic 64-bit loads and a third of the inner loop address arithmetic)
+    const int oH = 0, oE = 3 * (int)C;
     int32_t *F = base + 5 * C, *lastrow = base + 6 * C, *lastcol = base + 7 * C;
     uint8_t *alt = reinterpret_cast<uint8_t *>(lastcol + R), *ref = alt + ((C + 3) / 4) * 4;
     const uint32_t gwarp = blockIdx.x * kWarps + warp;
@@ -77,13 +78,13 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
         for (int k = lane; k < nrow; k += 32) ref[k] = rp[k];
         for (int k = lane; k < ncol; k += 32) alt[k] = ap[k];
         for (int j = lane; j <= ncol; j += 32) F[j] = kLowInit;         // F[0][j] (PairWiseSW.h:98-101,224)
-        if (lane == 0) Hb[1][0] = 0;                                    // H[0][0]: anti-diagonal 0 = the "ad-1" buffer of the first step
+        if (lane == 0) base[oH + (int)C] = 0;                           // H[0][0]: anti-diagonal 0 = the "ad-1" buffer of the first step
         __syncwarp();
 
         // ---- forward sweep over anti-diagonals ad = i + j
-        int h0 = 0, h1 = 1, h2 = 2, e1 = 0, e2 = 1;                     // buffers of ad-2, ad-1, ad
+        int h0 = oH, h1 = oH + (int)C, h2 = oH + 2 * (int)C, e1 = oE, e2 = oE + (int)C;   // buffers of ad-2, ad-1, ad
         for (int ad = 1; ad <= nrow + ncol; ++ad) {
-            int32_t *H0 = Hb[h0], *H1 = Hb[h1], *H2 = Hb[h2], *E1 = Eb[e1], *E2 = Eb[e2];
+            int32_t *H0 = base + h0, *H1 = base + h1, *H2 = base + h2, *E1 = base + e1, *E2 = base + e2;
             if (lane == 0) {
                 // boundary cells of this anti-diagonal (:214-225): (0, ad) on the top row, (ad, 0) in the left column
                 if (ad <= ncol) H2[ad] = indel ? a.open + (ad - 1) * a.extend : 0;
@@ -111,7 +112,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
             }
             __syncwarp();
             const int t = h0; h0 = h1; h1 = h2; h2 = t;
-            e1 ^= 1; e2 ^= 1;
+            const int u = e1; e1 = e2; e2 = u;
         }
 
         // ---- best cell: last row (SOFTCLIP / IGNORE only) and last column in anti-diagonal order (:227-251). Every lane

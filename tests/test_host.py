@@ -25,6 +25,13 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), "libpairhmm_cuda.so does not export %s" % name
     assert sorted(fgdp_b200.EXPORTED_SYMBOLS) == declared
     assert lib.pairhmm_cuda_abi_version() == 1
+    # include/smithwaterman_cuda.h (the Smith-Waterman entry points live in the same library)
+    from fgdp_b200 import smithwaterman
+    hdr = open(os.path.join(ROOT, "include", "smithwaterman_cuda.h")).read()
+    declared = sorted(set(re.findall(r"\b(smithwaterman_cuda_[a-z_0-9]+)\s*\(", hdr)))
+    assert declared == sorted(smithwaterman.SW_SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), "libpairhmm_cuda.so does not export %s" % name
 
 
 def test_product_library_does_not_link_the_oracle():
