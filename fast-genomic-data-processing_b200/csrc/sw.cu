@@ -13,6 +13,7 @@
 #include <climits>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -52,6 +53,95 @@ __host__ __device__ inline size_t warp_smem_ints(uint32_t max_ref, uint32_t max_
 }
 
 __device__ __forceinline__ int digits_of(int v) { int d = 0; while (v > 0) { v /= 10; ++d; } return d; }
+
+// Best cell, backtrace and CIGAR text of one alignment (shared by both kernels). btget(i, j) returns the backtrace code
+// of cell (i, j); every lane runs the same scalar code, lane 0 writes the results.
+template <class BtGet>
+__device__ __forceinline__ void finish_alignment(const Args &a, uint32_t p, int lane, int nrow, int ncol, const int32_t *lastrow,
+                                             const int32_t *lastcol, int32_t *elems, BtGet btget) {
+    // ---- best cell: last row (SOFTCLIP / IGNORE only) and last column in anti-diagonal order (:227-251). Every lane
+    // runs the same scalar code (shared-memory broadcasts), so there is no divergence and all lanes know the result.
+    int32_t max_score = INT_MIN;
+    int max_i = 0, max_j = 0;
+    const bool row_too = a.strategy == SW_CUDA_SOFTCLIP || a.strategy == SW_CUDA_IGNORE;
+    for (int ad = 1; ad <= nrow + ncol; ++ad) {
+        if (ad >= nrow + 1 && row_too) {
+            const int j = ad - nrow;
+            const int32_t s = lastrow[j];
+            if (max_score < s || (max_score == s && abs(nrow - j) < abs(max_i - max_j))) { max_score = s; max_i = nrow; max_j = j; }
+        }
+        if (ad >= ncol + 1) {
+            const int i = ad - ncol;
+            const int32_t s = lastcol[i];
+            if (max_score < s || (max_score == s && (max_j == ncol || abs(i - ncol) <= abs(max_i - max_j)))) { max_score = s; max_i = i; max_j = ncol; }
+        }
+    }
+
+    // ---- backtrace (getCIGAR, :265-402), elements merged as they are produced (the reference merges equal
+    // neighbours afterwards, :404-421 -- same list)
+    int n_el = 0, cur_op = -1, cur_len = 0;
+    auto push = [&](int op, int len) {
+        if (n_el > 0 && op == cur_op) { cur_len += len; return; }
+        if (n_el > 0 && lane == 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
+        cur_op = op; cur_len = len; ++n_el;
+    };
+    int i, j;
+    if (a.strategy == SW_CUDA_INDEL) { i = nrow; j = ncol; }
+    else if (a.strategy == SW_CUDA_LEADING_INDEL) { i = max_i; j = ncol; }
+    else { i = max_i; j = max_j; }
+    if (j < ncol) push(SW_CUDA_SOFTCLIP, ncol - j);
+    int state = 0;
+    while (i > 0 && j > 0) {
+        if (state == 0) {
+            // lane l looks at (i - l, j - l): a run of plain matches is consumed in one step
+            const int ii = i - lane, jj = j - lane;
+            int btr = 0xff;
+            if (ii > 0 && jj > 0) btr = btget(ii, jj);
+            const unsigned plain = __ballot_sync(kFull, ii > 0 && jj > 0 && (btr & 3) == BT_MATCH);
+            const int run = __ffs(~plain) - 1;                      // leading lanes that are plain matches (32 if all)
+            if (run != 0) {
+                const int r = run < 0 ? 32 : run;
+                push(BT_MATCH, r); i -= r; j -= r;                  // MATCH leaves state 0
+                continue;
+            }
+            btr = __shfl_sync(kFull, btr, 0);
+            if ((btr & 3) == BT_INSERT) { --j; push(BT_INSERT, 1); state = btr & BT_INSERT_EXT; }
+            else { --i; push(BT_DELETE, 1); state = btr & BT_DELETE_EXT; }       // (btr & 3) == DELETE
+        } else {
+            const int btr = btget(i, j);
+            if (state == BT_INSERT_EXT) { --j; ++cur_len; state = btr & BT_INSERT_EXT; }
+            else { --i; ++cur_len; state = btr & BT_DELETE_EXT; }
+        }
+    }
+    int offset;
+    if (a.strategy == SW_CUDA_SOFTCLIP) {
+        if (j > 0) push(SW_CUDA_SOFTCLIP, j);
+        offset = i;
+    } else if (a.strategy == SW_CUDA_IGNORE) {
+        if (j > 0) push(n_el > 0 ? cur_op : BT_MATCH, j);
+        offset = (int16_t)(i - j);
+    } else {
+        if (i > 0) push(BT_DELETE, i);
+        else if (j > 0) push(BT_INSERT, j);
+        offset = 0;
+    }
+    // ---- CIGAR text, last element first (:423-445)
+    if (lane == 0) {
+        if (n_el > 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
+        char *out = a.cigars + (uint64_t)p * a.cigar_stride;
+        int cur = 0;
+        for (int k = n_el - 1; k >= 0; --k) {
+            const int op = elems[2 * k], v = elems[2 * k + 1], d = digits_of(v);
+            if (d + 1 > 1 && cur + d + 1 <= a.cigar_stride) {
+                int x = v;
+                for (int q = d - 1; q >= 0; --q) { out[cur + q] = (char)('0' + x % 10); x /= 10; }
+                cur += d;
+                out[cur++] = op == BT_MATCH ? 'M' : op == BT_INSERT ? 'I' : op == BT_DELETE ? 'D' : op == SW_CUDA_SOFTCLIP ? 'S' : 'R';
+            }
+        }
+        a.offsets[p] = offset;
+    }
+}
 
 __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
     extern __shared__ int32_t smem[];
@@ -115,89 +205,116 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
             const int u = e1; e1 = e2; e2 = u;
         }
 
-        // ---- best cell: last row (SOFTCLIP / IGNORE only) and last column in anti-diagonal order (:227-251). Every lane
-        // runs the same scalar code (shared-memory broadcasts), so there is no divergence and all lanes know the result.
-        int32_t max_score = INT_MIN;
-        int max_i = 0, max_j = 0;
-        const bool row_too = a.strategy == SW_CUDA_SOFTCLIP || a.strategy == SW_CUDA_IGNORE;
-        for (int ad = 1; ad <= nrow + ncol; ++ad) {
-            if (ad >= nrow + 1 && row_too) {
-                const int j = ad - nrow;
-                const int32_t s = lastrow[j];
-                if (max_score < s || (max_score == s && abs(nrow - j) < abs(max_i - max_j))) { max_score = s; max_i = nrow; max_j = j; }
-            }
-            if (ad >= ncol + 1) {
-                const int i = ad - ncol;
-                const int32_t s = lastcol[i];
-                if (max_score < s || (max_score == s && (max_j == ncol || abs(i - ncol) <= abs(max_i - max_j)))) { max_score = s; max_i = i; max_j = ncol; }
-            }
-        }
-
-        // ---- backtrace (getCIGAR, :265-402), elements merged as they are produced (the reference merges equal
-        // neighbours afterwards, :404-421 -- same list)
         int32_t *elems = reinterpret_cast<int32_t *>(bt + ((((uint64_t)a.max_ref + a.max_alt + 1) * a.bt_width + 7) & ~7ull));
-        int n_el = 0, cur_op = -1, cur_len = 0;
-        auto push = [&](int op, int len) {
-            if (n_el > 0 && op == cur_op) { cur_len += len; return; }
-            if (n_el > 0 && lane == 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
-            cur_op = op; cur_len = len; ++n_el;
-        };
-        int i, j;
-        if (a.strategy == SW_CUDA_INDEL) { i = nrow; j = ncol; }
-        else if (a.strategy == SW_CUDA_LEADING_INDEL) { i = max_i; j = ncol; }
-        else { i = max_i; j = max_j; }
-        if (j < ncol) push(SW_CUDA_SOFTCLIP, ncol - j);
-        int state = 0;
-        while (i > 0 && j > 0) {
-            if (state == 0) {
-                // lane l looks at (i - l, j - l): a run of plain matches is consumed in one step
-                const int ii = i - lane, jj = j - lane;
-                int btr = 0xff;
-                if (ii > 0 && jj > 0) btr = bt[(uint64_t)(ii + jj) * a.bt_width + jj];
-                const unsigned plain = __ballot_sync(kFull, ii > 0 && jj > 0 && (btr & 3) == BT_MATCH);
-                const int run = __ffs(~plain) - 1;                      // leading lanes that are plain matches (32 if all)
-                if (run != 0) {
-                    const int r = run < 0 ? 32 : run;
-                    push(BT_MATCH, r); i -= r; j -= r;                  // MATCH leaves state 0
-                    continue;
+        const uint32_t btw = a.bt_width;
+        finish_alignment(a, p, lane, nrow, ncol, lastrow, lastcol, elems,
+                         [=](int i, int j) { return (int)bt[(uint64_t)(i + j) * btw + j]; });
+    }
+}
+
+// ---- register-blocked variant: lane l owns the K columns l*K+1 .. l*K+K of the alignment matrix (alt positions) and
+// sweeps the rows (ref positions) top to bottom, one row per step, lane l one row behind lane l-1 (the same skewed
+// wavefront as the PairHMM kernels). H of the row above and F live in registers, the row's H/E chain runs through the
+// lane's K cells and leaves for lane l+1 by two shuffles per step; a step's K backtrace codes are one 32-bit word
+// (4 bits per cell), stored at [step][lane] -- 128 consecutive bytes per warp and step. ~4x fewer instructions per cell
+// than the anti-diagonal kernel; used when the longest alt of the batch fits 32 x 8 columns.
+__host__ __device__ inline size_t strip_smem_ints(uint32_t max_ref, uint32_t max_alt) {
+    const size_t c = max_alt + 2, r = max_ref + 2;
+    return c + r + (r + 3) / 4;                            // lastrow | lastcol | ref bytes
+}
+
+template <int K>
+__global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) {
+    extern __shared__ int32_t smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t C = a.max_alt + 2, R = a.max_ref + 2;
+    int32_t *lastrow = smem + (size_t)warp * strip_smem_ints(a.max_ref, a.max_alt), *lastcol = lastrow + C;
+    uint8_t *ref = reinterpret_cast<uint8_t *>(lastcol + R);
+    const uint32_t gwarp = blockIdx.x * kWarps + warp;
+    uint32_t *btw = reinterpret_cast<uint32_t *>(a.scratch + (uint64_t)gwarp * a.scratch_per_warp);
+    int32_t *elems = reinterpret_cast<int32_t *>(btw + (size_t)(a.max_ref + 33) * 32);
+    const bool indel = a.strategy == SW_CUDA_INDEL || a.strategy == SW_CUDA_LEADING_INDEL;
+    const int32_t w_open = a.open, w_ext = a.extend, w_match = a.match, w_mis = a.mismatch;
+
+    for (;;) {
+        uint32_t p = 0;
+        if (lane == 0) p = atomicAdd(a.queue, 1u);
+        p = __shfl_sync(kFull, p, 0);
+        if (p >= a.n) break;
+        const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
+        const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
+        __syncwarp();
+        for (int k = lane; k < nrow; k += 32) ref[k] = rp[k];
+        const int j0 = lane * K;                                        // this lane's columns are j0+1 .. j0+K
+        int32_t Hup[K], F[K];
+        uint32_t altb[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int j = j0 + k + 1;
+            altb[k] = j <= ncol ? ap[j - 1] : 0x100u;                    // a dead column matches nothing
+            Hup[k] = indel ? w_open + (j - 1) * w_ext : 0;               // H[0][j] (:214-223)
+            F[k] = kLowInit;                                             // F[0][j]
+        }
+        // what the lane to the left delivers: H[i][j0] and E[i][j0] of this lane's current row i; h_in_prev = H[i-1][j0]
+        int32_t h_in_prev = j0 == 0 ? 0 : (indel ? w_open + (j0 - 1) * w_ext : 0);   // H[0][j0]
+        int32_t h_out = 0, e_out = kLowInit;
+        const int lc = (ncol - 1) / K, kc = (ncol - 1) % K;             // owner of the last column
+        __syncwarp();
+
+        for (int s = 1; s <= nrow + 31; ++s) {
+            int32_t h_in = __shfl_up_sync(kFull, h_out, 1), e_in = __shfl_up_sync(kFull, e_out, 1);
+            const int i = s - lane;
+            if (lane == 0) { h_in = indel ? w_open + (i - 1) * w_ext : 0; e_in = kLowInit; }   // H[i][0], E[i][0]
+            if (i >= 1 && i <= nrow) {
+                const uint32_t rb = ref[i - 1];
+                int32_t h_left = h_in, e_left = e_in, diag = h_in_prev;
+                uint32_t word = 0;
+#pragma unroll
+                for (int k = 0; k < K; ++k) {                            // MAIN_CODE, PairWiseSW.h:27-62
+                    const int32_t open_h = h_left + w_open, ext_h = e_left + w_ext;
+                    const int32_t e = max(open_h, ext_h);
+                    uint32_t b = open_h > ext_h ? 0u : (uint32_t)BT_INSERT_EXT;
+                    const int32_t open_v = Hup[k] + w_open, ext_v = F[k] + w_ext;
+                    const int32_t f = max(ext_v, open_v);
+                    if (!(open_v > ext_v)) b |= (uint32_t)BT_DELETE_EXT;
+                    const int32_t m = diag + (rb == altb[k] ? w_match : w_mis);
+                    int32_t h = max(kMinCutoff, m);
+                    uint32_t mv = e > h ? (uint32_t)BT_INSERT : (uint32_t)BT_MATCH;
+                    h = max(h, e);
+                    if (f > h) { mv = BT_DELETE; h = f; }
+                    diag = Hup[k];
+                    Hup[k] = h; F[k] = f; h_left = h; e_left = e;
+                    word |= (mv | b) << (4 * k);
                 }
-                btr = __shfl_sync(kFull, btr, 0);
-                if ((btr & 3) == BT_INSERT) { --j; push(BT_INSERT, 1); state = btr & BT_INSERT_EXT; }
-                else { --i; push(BT_DELETE, 1); state = btr & BT_DELETE_EXT; }       // (btr & 3) == DELETE
-            } else {
-                const int btr = bt[(uint64_t)(i + j) * a.bt_width + j];
-                if (state == BT_INSERT_EXT) { --j; ++cur_len; state = btr & BT_INSERT_EXT; }
-                else { --i; ++cur_len; state = btr & BT_DELETE_EXT; }
+                h_out = h_left; e_out = e_left;
+                h_in_prev = h_in;
+                btw[(size_t)s * 32 + lane] = word;
+                if (lane == lc) {
+                    int32_t v = Hup[0];
+#pragma unroll
+                    for (int k = 1; k < K; ++k) v = kc == k ? Hup[k] : v;
+                    lastcol[i] = v;
+                }
+                if (i == nrow) {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) if (j0 + k + 1 <= ncol) lastrow[j0 + k + 1] = Hup[k];
+                }
             }
         }
-        int offset;
-        if (a.strategy == SW_CUDA_SOFTCLIP) {
-            if (j > 0) push(SW_CUDA_SOFTCLIP, j);
-            offset = i;
-        } else if (a.strategy == SW_CUDA_IGNORE) {
-            if (j > 0) push(n_el > 0 ? cur_op : BT_MATCH, j);
-            offset = (int16_t)(i - j);
-        } else {
-            if (i > 0) push(BT_DELETE, i);
-            else if (j > 0) push(BT_INSERT, j);
-            offset = 0;
-        }
-        // ---- CIGAR text, last element first (:423-445)
-        if (lane == 0) {
-            if (n_el > 0) { elems[2 * (n_el - 1)] = cur_op; elems[2 * (n_el - 1) + 1] = cur_len; }
-            char *out = a.cigars + (uint64_t)p * a.cigar_stride;
-            int cur = 0;
-            for (int k = n_el - 1; k >= 0; --k) {
-                const int op = elems[2 * k], v = elems[2 * k + 1], d = digits_of(v);
-                if (d + 1 > 1 && cur + d + 1 <= a.cigar_stride) {
-                    int x = v;
-                    for (int q = d - 1; q >= 0; --q) { out[cur + q] = (char)('0' + x % 10); x /= 10; }
-                    cur += d;
-                    out[cur++] = op == BT_MATCH ? 'M' : op == BT_INSERT ? 'I' : op == BT_DELETE ? 'D' : op == SW_CUDA_SOFTCLIP ? 'S' : 'R';
-                }
-            }
-            a.offsets[p] = offset;
-        }
+        __syncwarp();
+        finish_alignment(a, p, lane, nrow, ncol, lastrow, lastcol, elems, [=](int i, int j) {
+            const int l = (j - 1) / K, k = (j - 1) % K;
+            return (int)((btw[(size_t)(i + l) * 32 + l] >> (4 * k)) & 15u);
+        });
+    }
+}
+
+using KernelFn = void (*)(const Args);
+inline KernelFn strip_kernel_for(int K) {
+    switch (K) {
+        case 1: return align_strip_kernel<1>; case 2: return align_strip_kernel<2>; case 3: return align_strip_kernel<3>;
+        case 4: return align_strip_kernel<4>; case 5: return align_strip_kernel<5>; case 6: return align_strip_kernel<6>;
+        case 7: return align_strip_kernel<7>; case 8: return align_strip_kernel<8>; default: return nullptr;
     }
 }
 
@@ -246,14 +363,21 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     if (prop.major != 10) return fail(SW_CUDA_ERR_NO_DEVICE, "not an sm_100 device (kernels are built for sm_100a only)");
     SWCU(cudaSetDevice(device));
 
-    const size_t smem = kWarps * warp_smem_ints(max_ref, max_alt) * sizeof(int32_t);
+    // the register-blocked kernel when every alt fits 32 lanes x 8 columns (SW_CUDA_KERNEL=diag forces the general one)
+    const int K = (int)((max_alt + 31) / 32);
+    const char *force = std::getenv("SW_CUDA_KERNEL");
+    KernelFn kernel = (force && !std::strcmp(force, "diag")) ? nullptr : strip_kernel_for(K);
+    const bool strip = kernel != nullptr;
+    if (!strip) kernel = align_kernel;
+    const size_t smem = kWarps * (strip ? strip_smem_ints(max_ref, max_alt) : warp_smem_ints(max_ref, max_alt)) * sizeof(int32_t);
     if (smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
-    SWCU(cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SWCU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, align_kernel, kWarps * 32, smem));
+    SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kWarps * 32, smem));
     per_sm = std::max(1, per_sm);
     const uint64_t bt_width = (uint64_t)max_alt + 1;
     uint64_t per_warp = ((uint64_t)max_ref + max_alt + 1) * bt_width + 8ull * ((uint64_t)max_ref + max_alt + 6);
+    if (strip) per_warp = ((uint64_t)max_ref + 33) * 128 + 8ull * ((uint64_t)max_ref + max_alt + 6);
     per_warp = (per_warp + 255) & ~255ull;
     uint64_t grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, ((uint64_t)n + kWarps - 1) / kWarps);
     const uint64_t budget = 8ull << 30;                                   // backtrace scratch of all resident warps
@@ -287,7 +411,7 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     a.cigars = d_cig.p; a.cigar_stride = cigar_stride; a.offsets = d_off.p; a.scratch = d_scratch.p; a.scratch_per_warp = per_warp;
     a.bt_width = (uint32_t)bt_width; a.max_ref = max_ref; a.max_alt = max_alt; a.queue = d_queue.p;
     SWCU2(cudaEventRecord(ev0, st));
-    align_kernel<<<(unsigned)grid, kWarps * 32, smem, st>>>(a);
+    kernel<<<(unsigned)grid, kWarps * 32, smem, st>>>(a);
     SWCU2(cudaGetLastError());
     SWCU2(cudaEventRecord(ev1, st));
     SWCU2(cudaMemcpyAsync(cigars, d_cig.p, (size_t)n * cigar_stride, cudaMemcpyDeviceToHost, st));
