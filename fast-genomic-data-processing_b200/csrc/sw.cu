@@ -44,6 +44,7 @@ struct Args {
     uint32_t bt_width;                          // max alt length + 1
     uint32_t max_ref, max_alt;
     uint32_t *queue;
+    const uint32_t *order;                      // queue position -> pair (the pairs of one launch group)
 };
 
 // ints of shared memory one warp needs
@@ -162,6 +163,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
         if (lane == 0) p = atomicAdd(a.queue, 1u);
         p = __shfl_sync(kFull, p, 0);
         if (p >= a.n) break;
+        p = a.order[p];
         const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
         const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
         __syncwarp();
@@ -241,6 +243,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
         if (lane == 0) p = atomicAdd(a.queue, 1u);
         p = __shfl_sync(kFull, p, 0);
         if (p >= a.n) break;
+        p = a.order[p];
         const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
         const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
         __syncwarp();
@@ -363,34 +366,76 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     if (prop.major != 10) return fail(SW_CUDA_ERR_NO_DEVICE, "not an sm_100 device (kernels are built for sm_100a only)");
     SWCU(cudaSetDevice(device));
 
-    // the register-blocked kernel when every alt fits 32 lanes x 8 columns (SW_CUDA_KERNEL=diag forces the general one)
-    const int K = (int)((max_alt + 31) / 32);
+    // Pairs are grouped by alt length: class c = ceil(alt_len / 32) <= 8 runs the register-blocked kernel with K = c
+    // columns per lane, longer alts the anti-diagonal kernel (SW_CUDA_KERNEL=diag forces it for all). A class too small to
+    // fill the device joins the next wider one. One launch per group, one after the other on the stream: they share
+    // the backtrace scratch.
+    constexpr int kDiagClass = 9;
     const char *force = std::getenv("SW_CUDA_KERNEL");
-    KernelFn kernel = (force && !std::strcmp(force, "diag")) ? nullptr : strip_kernel_for(K);
-    const bool strip = kernel != nullptr;
-    if (!strip) kernel = align_kernel;
-    const size_t smem = kWarps * (strip ? strip_smem_ints(max_ref, max_alt) : warp_smem_ints(max_ref, max_alt)) * sizeof(int32_t);
-    if (smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
-    SWCU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kWarps * 32, smem));
-    per_sm = std::max(1, per_sm);
-    const uint64_t bt_width = (uint64_t)max_alt + 1;
-    uint64_t per_warp = ((uint64_t)max_ref + max_alt + 1) * bt_width + 8ull * ((uint64_t)max_ref + max_alt + 6);
-    if (strip) per_warp = ((uint64_t)max_ref + 33) * 128 + 8ull * ((uint64_t)max_ref + max_alt + 6);
-    per_warp = (per_warp + 255) & ~255ull;
-    uint64_t grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, ((uint64_t)n + kWarps - 1) / kWarps);
-    const uint64_t budget = 8ull << 30;                                   // backtrace scratch of all resident warps
-    grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, budget / (per_warp * kWarps)));
+    const bool force_diag = force && !std::strcmp(force, "diag");
+    std::vector<uint8_t> cls((size_t)n);
+    uint64_t cnt[kDiagClass + 1] = {};
+    for (int64_t p = 0; p < n; ++p) {
+        const int c = force_diag ? kDiagClass : std::min(kDiagClass, (alt_len[p] + 31) / 32);
+        cls[(size_t)p] = (uint8_t)c; ++cnt[c];
+    }
+    int join[kDiagClass + 1];                                 // class -> the class whose launch it rides in
+    uint64_t min_group = (uint64_t)prop.multiProcessorCount * 64;
+    if (const char *mg = std::getenv("SW_CUDA_MIN_GROUP")) min_group = std::strtoull(mg, nullptr, 10);   // tests: one launch per class
+    for (int c = 1; c <= kDiagClass; ++c) join[c] = c;
+    for (int c = 1; c < kDiagClass - 1; ++c) {
+        if (!cnt[c] || cnt[c] >= min_group) continue;
+        int up = c + 1;
+        while (up < kDiagClass - 1 && !cnt[up]) ++up;
+        if (!cnt[up]) continue;                               // nothing wider to join
+        cnt[up] += cnt[c]; cnt[c] = 0; join[c] = up;
+    }
+    for (int c = 1; c < kDiagClass; ++c) { int t = join[c]; while (join[t] != t) t = join[t]; join[c] = t; }
+    struct Group { int K; uint64_t first, count, per_warp, grid; uint32_t max_ref, max_alt; size_t smem; KernelFn kernel; };
+    Group groups[kDiagClass + 1];
+    int group_of[kDiagClass + 1], ngroups = 0;
+    uint64_t first = 0;
+    for (int c = 1; c <= kDiagClass; ++c) {
+        group_of[c] = -1;
+        if (!cnt[c]) continue;
+        group_of[c] = ngroups;
+        groups[ngroups++] = Group{c == kDiagClass ? 0 : c, first, 0, 0, 0, 1, 1, 0, nullptr};
+        first += cnt[c];
+    }
+    std::vector<uint32_t> order((size_t)n);
+    for (int64_t p = 0; p < n; ++p) {
+        Group &g = groups[group_of[join[cls[(size_t)p]]]];
+        order[(size_t)(g.first + g.count++)] = (uint32_t)p;
+        g.max_ref = std::max<uint32_t>(g.max_ref, (uint32_t)ref_len[p]); g.max_alt = std::max<uint32_t>(g.max_alt, (uint32_t)alt_len[p]);
+    }
+    uint64_t scratch_bytes = 0;
+    for (int k = 0; k < ngroups; ++k) {
+        Group &g = groups[k];
+        g.kernel = g.K ? strip_kernel_for(g.K) : align_kernel;
+        g.smem = kWarps * (g.K ? strip_smem_ints(g.max_ref, g.max_alt) : warp_smem_ints(g.max_ref, g.max_alt)) * sizeof(int32_t);
+        if (g.smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
+        SWCU(cudaFuncSetAttribute(g.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+        int per_sm = 0;
+        SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, g.kernel, kWarps * 32, g.smem));
+        per_sm = std::max(1, per_sm);
+        const uint64_t tail = 8ull * ((uint64_t)g.max_ref + g.max_alt + 6);                 // CIGAR element list
+        g.per_warp = g.K ? ((uint64_t)g.max_ref + 33) * 128 + tail
+                         : ((uint64_t)g.max_ref + g.max_alt + 1) * ((uint64_t)g.max_alt + 1) + 8 + tail;
+        g.per_warp = (g.per_warp + 255) & ~255ull;
+        g.grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, (g.count + kWarps - 1) / kWarps);
+        const uint64_t budget = 8ull << 30;                               // backtrace scratch of all resident warps
+        g.grid = std::max<uint64_t>(1, std::min<uint64_t>(g.grid, budget / (g.per_warp * kWarps)));
+        scratch_bytes = std::max(scratch_bytes, g.per_warp * kWarps * g.grid);
+    }
 
     DevArr<uint8_t> d_ref, d_alt, d_scratch;
     DevArr<int64_t> d_roff, d_aoff;
     DevArr<int32_t> d_rlen, d_alen, d_off;
     DevArr<char> d_cig;
-    DevArr<uint32_t> d_queue;
+    DevArr<uint32_t> d_queue, d_order;
     SWCU(d_ref.alloc(ref_bytes)); SWCU(d_alt.alloc(alt_bytes)); SWCU(d_roff.alloc(n)); SWCU(d_aoff.alloc(n));
     SWCU(d_rlen.alloc(n)); SWCU(d_alen.alloc(n)); SWCU(d_off.alloc(n)); SWCU(d_cig.alloc((size_t)n * cigar_stride));
-    SWCU(d_queue.alloc(1)); SWCU(d_scratch.alloc(per_warp * kWarps * grid));
+    SWCU(d_queue.alloc(ngroups)); SWCU(d_order.alloc(n)); SWCU(d_scratch.alloc(scratch_bytes));
     cudaStream_t st;
     SWCU(cudaStreamCreate(&st));
     cudaEvent_t ev0, ev1;
@@ -404,15 +449,20 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     SWCU2(cudaMemcpyAsync(d_rlen.p, ref_len, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemcpyAsync(d_alen.p, alt_len, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemsetAsync(d_cig.p, 0, (size_t)n * cigar_stride, st));
-    SWCU2(cudaMemsetAsync(d_queue.p, 0, sizeof(uint32_t), st));
+    SWCU2(cudaMemcpyAsync(d_order.p, order.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemsetAsync(d_queue.p, 0, sizeof(uint32_t) * ngroups, st));
     Args a{};
     a.ref_bases = d_ref.p; a.alt_bases = d_alt.p; a.ref_off = d_roff.p; a.alt_off = d_aoff.p; a.ref_len = d_rlen.p; a.alt_len = d_alen.p;
-    a.n = (uint32_t)n; a.match = match; a.mismatch = mismatch; a.open = open; a.extend = extend; a.strategy = strategy;
-    a.cigars = d_cig.p; a.cigar_stride = cigar_stride; a.offsets = d_off.p; a.scratch = d_scratch.p; a.scratch_per_warp = per_warp;
-    a.bt_width = (uint32_t)bt_width; a.max_ref = max_ref; a.max_alt = max_alt; a.queue = d_queue.p;
+    a.match = match; a.mismatch = mismatch; a.open = open; a.extend = extend; a.strategy = strategy;
+    a.cigars = d_cig.p; a.cigar_stride = cigar_stride; a.offsets = d_off.p; a.scratch = d_scratch.p;
     SWCU2(cudaEventRecord(ev0, st));
-    kernel<<<(unsigned)grid, kWarps * 32, smem, st>>>(a);
-    SWCU2(cudaGetLastError());
+    for (int k = 0; k < ngroups; ++k) {
+        const Group &g = groups[k];
+        a.n = (uint32_t)g.count; a.order = d_order.p + g.first; a.queue = d_queue.p + k;
+        a.scratch_per_warp = g.per_warp; a.bt_width = g.max_alt + 1; a.max_ref = g.max_ref; a.max_alt = g.max_alt;
+        g.kernel<<<(unsigned)g.grid, kWarps * 32, g.smem, st>>>(a);
+        SWCU2(cudaGetLastError());
+    }
     SWCU2(cudaEventRecord(ev1, st));
     SWCU2(cudaMemcpyAsync(cigars, d_cig.p, (size_t)n * cigar_stride, cudaMemcpyDeviceToHost, st));
     SWCU2(cudaMemcpyAsync(offsets, d_off.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));

@@ -92,3 +92,35 @@ def test_cuda_sw_batch_of_read_realignments():
         assert off == want_o[k] and bytes(buf).split(b"\0")[0].decode() == want_c[k]
     with pytest.raises(Exception):
         sw.align_batch([b""], [b"A"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("min_group", ["1", None])
+def test_cuda_sw_every_kernel_class(min_group, monkeypatch):
+    """alt lengths 1..300 cover the eight register-blocked kernels (K = ceil(alt/32) columns per lane) and the
+    anti-diagonal kernel; SW_CUDA_MIN_GROUP=1 launches every class on its own instead of merging the small ones"""
+    from fgdp_b200 import smithwaterman as sw
+    if min_group:
+        monkeypatch.setenv("SW_CUDA_MIN_GROUP", min_group)
+    rng = np.random.default_rng(41)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    refs, alts = [], []
+    for k in range(2400):
+        H, R = int(rng.integers(1, 420)), 1 + (k * 7) % 300
+        hap = rng.choice(acgt, H)
+        if k % 5 == 0 or H <= R:
+            read = rng.choice(acgt, R)
+        else:
+            st = int(rng.integers(0, H - R))
+            read = hap[st:st + R].copy()
+            m = rng.random(R) < 0.04
+            read[m] = rng.choice(acgt, int(m.sum()))
+            if R > 20 and k % 3 == 0:
+                read = np.concatenate([read[:R // 2], read[R // 2 + 3:], rng.choice(acgt, 3)])
+        refs.append(bytes(hap)); alts.append(bytes(read))
+    p = oracle_py.SWPairs(refs, alts)
+    for params, strat in (((10, -15, -30, -5), 9), ((25, -50, -110, -6), 10), ((3, -1, -4, -3), 11), ((200, -150, -260, -11), 12)):
+        want_c, want_o = oracle_py.oracle_sw(p, params, strat)
+        c, o, ms = sw.align_batch(refs, alts, params, strat)
+        bad = [k for k in range(len(refs)) if c[k] != want_c[k] or o[k] != want_o[k]]
+        assert not bad, (params, strat, len(bad), [(len(refs[k]), len(alts[k]), c[k], want_c[k]) for k in bad[:3]])
