@@ -262,42 +262,46 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
         int32_t h_in_prev = j0 == 0 ? 0 : (indel ? w_open + (j0 - 1) * w_ext : 0);   // H[0][j0]
         int32_t h_out = 0, e_out = kLowInit;
         const int lc = (ncol - 1) / K, kc = (ncol - 1) % K;             // owner of the last column
+        int32_t pick[K];                                                // 1 on the register that holds column ncol
+#pragma unroll
+        for (int k = 0; k < K; ++k) pick[k] = (lane == lc && kc == k) ? 1 : 0;
+        const int32_t bnd_step = indel ? w_ext : 0;
+        int32_t bnd = indel ? w_open - lane * w_ext : 0;                // H[i][0] of row i = s - lane at step s = 1
+        uint32_t *btp = btw + 32 + lane;
         __syncwarp();
 
-        for (int s = 1; s <= nrow + 31; ++s) {
+        for (int s = 1; s <= nrow + 31; ++s, btp += 32, bnd += bnd_step) {
             int32_t h_in = __shfl_up_sync(kFull, h_out, 1), e_in = __shfl_up_sync(kFull, e_out, 1);
             const int i = s - lane;
-            if (lane == 0) { h_in = indel ? w_open + (i - 1) * w_ext : 0; e_in = kLowInit; }   // H[i][0], E[i][0]
+            if (lane == 0) { h_in = bnd; e_in = kLowInit; }            // H[i][0], E[i][0]
             if (i >= 1 && i <= nrow) {
                 const uint32_t rb = ref[i - 1];
-                int32_t h_left = h_in, e_left = e_in, diag = h_in_prev;
+                int32_t h_left = h_in, e_left = e_in, diag = h_in_prev, last = 0;
                 uint32_t word = 0;
 #pragma unroll
                 for (int k = 0; k < K; ++k) {                            // MAIN_CODE, PairWiseSW.h:27-62
+                    // the four comparisons of the cell go into the backtrace word as the SIGN BITS of four differences
+                    // (one funnel shift each; every value is within +-1.1e9, no difference overflows)
                     const int32_t open_h = h_left + w_open, ext_h = e_left + w_ext;
                     const int32_t e = max(open_h, ext_h);
-                    uint32_t b = open_h > ext_h ? 0u : (uint32_t)BT_INSERT_EXT;
+                    word = __funnelshift_l((uint32_t)(ext_h - open_h), word, 1);        // 1: open_h > ext_h
                     const int32_t open_v = Hup[k] + w_open, ext_v = F[k] + w_ext;
                     const int32_t f = max(ext_v, open_v);
-                    if (!(open_v > ext_v)) b |= (uint32_t)BT_DELETE_EXT;
+                    word = __funnelshift_l((uint32_t)(ext_v - open_v), word, 1);        // 1: open_v > ext_v
                     const int32_t m = diag + (rb == altb[k] ? w_match : w_mis);
-                    int32_t h = max(kMinCutoff, m);
-                    uint32_t mv = e > h ? (uint32_t)BT_INSERT : (uint32_t)BT_MATCH;
-                    h = max(h, e);
-                    if (f > h) { mv = BT_DELETE; h = f; }
+                    const int32_t h0 = max(kMinCutoff, m);
+                    word = __funnelshift_l((uint32_t)(h0 - e), word, 1);                // 1: e > h  (INSERT)
+                    const int32_t h1 = max(h0, e);
+                    word = __funnelshift_l((uint32_t)(h1 - f), word, 1);                // 1: f > h  (DELETE)
+                    const int32_t h = max(h1, f);
                     diag = Hup[k];
                     Hup[k] = h; F[k] = f; h_left = h; e_left = e;
-                    word |= (mv | b) << (4 * k);
+                    last += h * pick[k];
                 }
                 h_out = h_left; e_out = e_left;
                 h_in_prev = h_in;
-                btw[(size_t)s * 32 + lane] = word;
-                if (lane == lc) {
-                    int32_t v = Hup[0];
-#pragma unroll
-                    for (int k = 1; k < K; ++k) v = kc == k ? Hup[k] : v;
-                    lastcol[i] = v;
-                }
+                *btp = word;
+                if (lane == lc) lastcol[i] = last;
                 if (i == nrow) {
 #pragma unroll
                     for (int k = 0; k < K; ++k) if (j0 + k + 1 <= ncol) lastrow[j0 + k + 1] = Hup[k];
@@ -307,7 +311,9 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
         __syncwarp();
         finish_alignment(a, p, lane, nrow, ncol, lastrow, lastcol, elems, [=](int i, int j) {
             const int l = (j - 1) / K, k = (j - 1) % K;
-            return (int)((btw[(size_t)(i + l) * 32 + l] >> (4 * k)) & 15u);
+            const uint32_t nib = btw[(size_t)(i + l) * 32 + l] >> (4 * (K - 1 - k));    // open_h> | open_v> | e> | f>
+            const int mv = (nib & 1u) ? BT_DELETE : ((nib & 2u) ? BT_INSERT : BT_MATCH);
+            return mv | ((nib & 8u) ? 0 : BT_INSERT_EXT) | ((nib & 4u) ? 0 : BT_DELETE_EXT);
         });
     }
 }
