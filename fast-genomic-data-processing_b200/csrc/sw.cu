@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 #include <string>
 #include <vector>
 
@@ -262,32 +263,40 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
         int32_t h_in_prev = j0 == 0 ? 0 : (indel ? w_open + (j0 - 1) * w_ext : 0);   // H[0][j0]
         int32_t h_out = 0, e_out = kLowInit;
         const int lc = (ncol - 1) / K, kc = (ncol - 1) % K;             // owner of the last column
-        int32_t pick[K];                                                // 1 on the register that holds column ncol
-#pragma unroll
-        for (int k = 0; k < K; ++k) pick[k] = (lane == lc && kc == k) ? 1 : 0;
         const int32_t bnd_step = indel ? w_ext : 0;
         int32_t bnd = indel ? w_open - lane * w_ext : 0;                // H[i][0] of row i = s - lane at step s = 1
         uint32_t *btp = btw + 32 + lane;
+        // column ncol's H goes to lastcol[i] every step: picked out of the lane's K registers by multiply-add with 0/1
+        // factors the compiler cannot see through (it would turn them into K compares and selects per step), stored by
+        // every lane -- the others to slot 0 (H[0][ncol]), which nobody reads
+        int32_t pick[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) asm("mov.s32 %0, %1;" : "=r"(pick[k]) : "r"(kc == k ? 1 : 0));
+        const int lc_step = lane == lc ? 1 : 0;
+        int lc_idx = lane == lc ? 1 - lane : 0;                         // i of lane lc at step s = 1
         __syncwarp();
 
-        for (int s = 1; s <= nrow + 31; ++s, btp += 32, bnd += bnd_step) {
+        // one row per lane; `guarded` = some lanes are outside their rows (the ramps at both ends of the sweep)
+        auto step = [&](const int s, auto guard) {
+            constexpr bool guarded = decltype(guard)::value;
             int32_t h_in = __shfl_up_sync(kFull, h_out, 1), e_in = __shfl_up_sync(kFull, e_out, 1);
             const int i = s - lane;
             if (lane == 0) { h_in = bnd; e_in = kLowInit; }            // H[i][0], E[i][0]
-            if (i >= 1 && i <= nrow) {
+            if (!guarded || (i >= 1 && i <= nrow)) {
                 const uint32_t rb = ref[i - 1];
-                int32_t h_left = h_in, e_left = e_in, diag = h_in_prev, last = 0;
+                int32_t h_left = h_in, e_left = e_in, diag = h_in_prev;
                 uint32_t word = 0;
 #pragma unroll
                 for (int k = 0; k < K; ++k) {                            // MAIN_CODE, PairWiseSW.h:27-62
                     // the four comparisons of the cell go into the backtrace word as the SIGN BITS of four differences
-                    // (one funnel shift each; every value is within +-1.1e9, no difference overflows)
-                    const int32_t open_h = h_left + w_open, ext_h = e_left + w_ext;
-                    const int32_t e = max(open_h, ext_h);
-                    word = __funnelshift_l((uint32_t)(ext_h - open_h), word, 1);        // 1: open_h > ext_h
-                    const int32_t open_v = Hup[k] + w_open, ext_v = F[k] + w_ext;
-                    const int32_t f = max(ext_v, open_v);
-                    word = __funnelshift_l((uint32_t)(ext_v - open_v), word, 1);        // 1: open_v > ext_v
+                    // (one funnel shift each; every value is within +-1.1e9, no difference overflows). The kernel is
+                    // bound by instruction issue: each max is taken once and the flag read off its result
+                    const int32_t ext_h = e_left + w_ext;
+                    const int32_t e = max(h_left + w_open, ext_h);
+                    word = __funnelshift_l((uint32_t)(ext_h - e), word, 1);             // 1: open_h > ext_h
+                    const int32_t ext_v = F[k] + w_ext;
+                    const int32_t f = max(Hup[k] + w_open, ext_v);
+                    word = __funnelshift_l((uint32_t)(ext_v - f), word, 1);             // 1: open_v > ext_v
                     const int32_t m = diag + (rb == altb[k] ? w_match : w_mis);
                     const int32_t h0 = max(kMinCutoff, m);
                     word = __funnelshift_l((uint32_t)(h0 - e), word, 1);                // 1: e > h  (INSERT)
@@ -296,18 +305,28 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
                     const int32_t h = max(h1, f);
                     diag = Hup[k];
                     Hup[k] = h; F[k] = f; h_left = h; e_left = e;
-                    last += h * pick[k];
                 }
                 h_out = h_left; e_out = e_left;
                 h_in_prev = h_in;
                 *btp = word;
-                if (lane == lc) lastcol[i] = last;
-                if (i == nrow) {
+                int32_t last = 0;
+#pragma unroll
+                for (int k = 0; k < K; ++k) last += Hup[k] * pick[k];
+                lastcol[lc_idx] = last;
+                if (guarded && i == nrow) {
 #pragma unroll
                     for (int k = 0; k < K; ++k) if (j0 + k + 1 <= ncol) lastrow[j0 + k + 1] = Hup[k];
                 }
             }
-        }
+            btp += 32; bnd += bnd_step; lc_idx += lc_step;
+        };
+        // steps 32 .. nrow - 1 have every lane inside its rows and none on the last row: no range checks there, and two
+        // steps per trip so that no register is shuffled between trips
+        const int last_step = nrow + 31;
+        int s = 1;
+        for (; s <= min(31, last_step); ++s) step(s, std::true_type{});
+        for (; s + 1 <= nrow - 1; s += 2) { step(s, std::false_type{}); step(s + 1, std::false_type{}); }
+        for (; s <= last_step; ++s) step(s, std::true_type{});
         __syncwarp();
         finish_alignment(a, p, lane, nrow, ncol, lastrow, lastcol, elems, [=](int i, int j) {
             const int l = (j - 1) / K, k = (j - 1) % K;
