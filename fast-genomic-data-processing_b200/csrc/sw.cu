@@ -25,7 +25,7 @@
 
 namespace sw {
 
-constexpr int kWarps = 4;                       // warps per CTA
+constexpr int kWarps = 4;                       // warps per CTA (fewer when long sequences need the shared memory)
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int BT_MATCH = 0, BT_INSERT = 1, BT_DELETE = 2, BT_INSERT_EXT = 4, BT_DELETE_EXT = 8;
 constexpr int32_t kMinCutoff = -100000000;      // MATRIX_MIN_CUTOFF
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
     const int oH = 0, oE = 3 * (int)C;
     int32_t *F = base + 5 * C, *lastrow = base + 6 * C, *lastcol = base + 7 * C;
     uint8_t *alt = reinterpret_cast<uint8_t *>(lastcol + R), *ref = alt + ((C + 3) / 4) * 4;
-    const uint32_t gwarp = blockIdx.x * kWarps + warp;
+    const uint32_t gwarp = blockIdx.x * (blockDim.x >> 5) + warp;
     uint8_t *bt = a.scratch + (uint64_t)gwarp * a.scratch_per_warp;
     const bool indel = a.strategy == SW_CUDA_INDEL || a.strategy == SW_CUDA_LEADING_INDEL;
 
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
     const size_t C = a.max_alt + 2, R = a.max_ref + 2;
     int32_t *lastrow = smem + (size_t)warp * strip_smem_ints(a.max_ref, a.max_alt), *lastcol = lastrow + C;
     uint8_t *ref = reinterpret_cast<uint8_t *>(lastcol + R);
-    const uint32_t gwarp = blockIdx.x * kWarps + warp;
+    const uint32_t gwarp = blockIdx.x * (blockDim.x >> 5) + warp;
     uint32_t *btw = reinterpret_cast<uint32_t *>(a.scratch + (uint64_t)gwarp * a.scratch_per_warp);
     int32_t *elems = reinterpret_cast<int32_t *>(btw + (size_t)(a.max_ref + 33) * 32);
     const bool indel = a.strategy == SW_CUDA_INDEL || a.strategy == SW_CUDA_LEADING_INDEL;
@@ -416,7 +416,7 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
         cnt[up] += cnt[c]; cnt[c] = 0; join[c] = up;
     }
     for (int c = 1; c < kDiagClass; ++c) { int t = join[c]; while (join[t] != t) t = join[t]; join[c] = t; }
-    struct Group { int K; uint64_t first, count, per_warp, grid; uint32_t max_ref, max_alt; size_t smem; KernelFn kernel; };
+    struct Group { int K, warps; uint64_t first, count, per_warp, grid; uint32_t max_ref, max_alt; size_t smem; KernelFn kernel; };
     Group groups[kDiagClass + 1];
     int group_of[kDiagClass + 1], ngroups = 0;
     uint64_t first = 0;
@@ -424,7 +424,7 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
         group_of[c] = -1;
         if (!cnt[c]) continue;
         group_of[c] = ngroups;
-        groups[ngroups++] = Group{c == kDiagClass ? 0 : c, first, 0, 0, 0, 1, 1, 0, nullptr};
+        groups[ngroups++] = Group{c == kDiagClass ? 0 : c, kWarps, first, 0, 0, 0, 1, 1, 0, nullptr};
         first += cnt[c];
     }
     std::vector<uint32_t> order((size_t)n);
@@ -437,20 +437,22 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     for (int k = 0; k < ngroups; ++k) {
         Group &g = groups[k];
         g.kernel = g.K ? strip_kernel_for(g.K) : align_kernel;
-        g.smem = kWarps * (g.K ? strip_smem_ints(g.max_ref, g.max_alt) : warp_smem_ints(g.max_ref, g.max_alt)) * sizeof(int32_t);
+        const size_t warp_smem = (g.K ? strip_smem_ints(g.max_ref, g.max_alt) : warp_smem_ints(g.max_ref, g.max_alt)) * sizeof(int32_t);
+        while (g.warps > 1 && g.warps * warp_smem > (size_t)prop.sharedMemPerBlockOptin) --g.warps;
+        g.smem = g.warps * warp_smem;
         if (g.smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
         SWCU(cudaFuncSetAttribute(g.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
         int per_sm = 0;
-        SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, g.kernel, kWarps * 32, g.smem));
+        SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, g.kernel, g.warps * 32, g.smem));
         per_sm = std::max(1, per_sm);
         const uint64_t tail = 8ull * ((uint64_t)g.max_ref + g.max_alt + 6);                 // CIGAR element list
         g.per_warp = g.K ? ((uint64_t)g.max_ref + 33) * 128 + tail
                          : ((uint64_t)g.max_ref + g.max_alt + 1) * ((uint64_t)g.max_alt + 1) + 8 + tail;
         g.per_warp = (g.per_warp + 255) & ~255ull;
-        g.grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, (g.count + kWarps - 1) / kWarps);
+        g.grid = std::min<uint64_t>((uint64_t)prop.multiProcessorCount * per_sm, (g.count + g.warps - 1) / g.warps);
         const uint64_t budget = 8ull << 30;                               // backtrace scratch of all resident warps
-        g.grid = std::max<uint64_t>(1, std::min<uint64_t>(g.grid, budget / (g.per_warp * kWarps)));
-        scratch_bytes = std::max(scratch_bytes, g.per_warp * kWarps * g.grid);
+        g.grid = std::max<uint64_t>(1, std::min<uint64_t>(g.grid, budget / (g.per_warp * g.warps)));
+        scratch_bytes = std::max(scratch_bytes, g.per_warp * g.warps * g.grid);
     }
 
     DevArr<uint8_t> d_ref, d_alt, d_scratch;
@@ -485,7 +487,7 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
         const Group &g = groups[k];
         a.n = (uint32_t)g.count; a.order = d_order.p + g.first; a.queue = d_queue.p + k;
         a.scratch_per_warp = g.per_warp; a.bt_width = g.max_alt + 1; a.max_ref = g.max_ref; a.max_alt = g.max_alt;
-        g.kernel<<<(unsigned)g.grid, kWarps * 32, g.smem, st>>>(a);
+        g.kernel<<<(unsigned)g.grid, g.warps * 32, g.smem, st>>>(a);
         SWCU2(cudaGetLastError());
     }
     SWCU2(cudaEventRecord(ev1, st));

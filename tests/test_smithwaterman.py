@@ -124,3 +124,30 @@ def test_cuda_sw_every_kernel_class(min_group, monkeypatch):
         c, o, ms = sw.align_batch(refs, alts, params, strat)
         bad = [k for k in range(len(refs)) if c[k] != want_c[k] or o[k] != want_o[k]]
         assert not bad, (params, strat, len(bad), [(len(refs[k]), len(alts[k]), c[k], want_c[k]) for k in bad[:3]])
+
+
+@pytest.mark.gpu
+def test_cuda_sw_longest_sequences():
+    """haplotype-against-reference sized pairs up to SW_CUDA_MAX_LEN = 4096 on both sides (the anti-diagonal kernel with
+    one warp per CTA: its shared memory holds eight rows of max_alt ints), next to short ones in the same call; one base
+    more is refused"""
+    from fgdp_b200 import smithwaterman as sw
+    rng = np.random.default_rng(77)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    refs, alts = [], []
+    for H, R in ((4096, 4096), (3000, 1200), (700, 4096), (4096, 33), (520, 500), (64, 40)):
+        hap = rng.choice(acgt, H)
+        src = hap[:R] if R <= H else np.concatenate([hap, rng.choice(acgt, R - H)])
+        read = src.copy()
+        m = rng.random(R) < 0.02
+        read[m] = rng.choice(acgt, int(m.sum()))
+        if R > 300:
+            read = np.concatenate([read[:100], read[110:R // 2], rng.choice(acgt, 10), read[R // 2:]])
+        refs.append(bytes(hap)); alts.append(bytes(read[:4096]))
+    p = oracle_py.SWPairs(refs, alts)
+    for params, strat in (((10, -15, -30, -5), 9), ((200, -150, -260, -11), 10), ((25, -50, -110, -6), 12)):
+        want_c, want_o = oracle_py.oracle_sw(p, params, strat)
+        c, o, ms = sw.align_batch(refs, alts, params, strat)
+        assert c == want_c and np.array_equal(o, want_o), (params, strat)
+    with pytest.raises(Exception):
+        sw.align_batch([b"A" * 4097], [b"A" * 10])
