@@ -42,7 +42,7 @@ template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; 
 
 void Slot::release() {
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
-    h_hapoff.release(); h_haplist.release(); h_units.release(); h_out.release(); h_rescue_base.release();
+    h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); h_units.release(); h_out.release(); h_rescue_base.release();
     h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
@@ -165,6 +165,14 @@ uint8_t pcr_adjusted_qual(int repeat_length, int rate_factor) {
     return (uint8_t)(char)std::max(10, r + 1);
 }
 
+// haplotypes per work unit of a region when the batch is large enough to fill the GPU
+uint32_t default_unit_haps(int n_haps, int32_t hmax) {
+    uint32_t g = (uint32_t)std::max(1, n_haps);
+    const uint32_t cap_cols = 16384u / (uint32_t)(hmax + 1);
+    g = std::min(g, std::max(1u, cap_cols));
+    return std::min(g, (uint32_t)kMaxUnitHaps);
+}
+
 // Pass A for one region: read de-duplication (VectorLoglessPairHMM.cpp:83-103) and sizes.
 int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, uint32_t group_hint) {
     pl = RegionPlan();
@@ -232,11 +240,9 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     pl.n_uniq = (uint32_t)pl.uniq_src.size();
     // haplotypes per work unit: all of them unless the chunk is too small to fill the GPU
     // (group_hint) or the unit would get very long (tail balance)
-    uint32_t g = (uint32_t)std::max(1, rv.n_haps);
-    const uint32_t cap_cols = 16384u / (uint32_t)(hmax + 1);
-    g = std::min(g, std::max(1u, cap_cols));
-    g = std::min(g, (uint32_t)kMaxUnitHaps);
+    uint32_t g = default_unit_haps(rv.n_haps, hmax);
     if (group_hint) g = std::min(g, group_hint);
+    if (h->cfg.reserved[5] > 0) g = (uint32_t)std::min<int>(std::min(h->cfg.reserved[5], (int)kMaxUnitHaps), std::max(1, rv.n_haps));
     pl.group = g;
     pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;
     return PAIRHMM_OK;
@@ -245,7 +251,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
 // Lane-group width for a read of length R under the given FP32 variant. Narrow groups (more rows per
 // lane) exist for the uniform-gcp kernels only; forced_w (config.reserved[1]) overrides the choice.
 int choose_width(int R, Variant v, int forced_w) {
-    if (v != Variant::F32_PK) return 32;
+    if (!is_packed_f32(v)) return 32;
     if (forced_w && bin_of_read(R, forced_w) >= 0) return forced_w;
     // the narrowest group that fits wins: more rows per lane amortise the per-column overhead (shuffles,
     // table address, loop) over more cells
@@ -282,6 +288,56 @@ void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w) {
         while (e < n && bin[order[e]] == b) ++e;
         pl.runs.push_back(RegionPlan::BinRun{b, j, e - j, 0});
         j = e;
+    }
+}
+
+constexpr double kPfxMinSharedFrac = 0.12;   // config.reserved[4] == 1: share only if the plan skips more than this part of the cells
+
+// Pass A3 (Variant::F32_PFX only): order the region's haplotypes by (length, bytes) and plan, per work unit, which
+// sweeps start from a checkpoint. The GPU analogue of the reference's trie (M2/trie/buildTreeUtils.cpp:155-258:
+// buildTreeWithHaplotype_same_height shares 32-column prefix blocks between haplotypes of one length; here the unit is
+// a tile of kTile columns). In sorted order the prefix two neighbours share is the longest either shares with anything
+// before it, so a stack of checkpoints (ascending tile counts, all on the current haplotype's path) is enough:
+// haplotype j drops the checkpoints beyond what it shares with j-1, resumes from the deepest one left, and leaves one at
+// the boundary it shares with j+1 if that lies inside its own sweep and a slot is free.
+void plan_prefix(const RegionView &rv, RegionPlan &pl) {
+    const uint32_t n = (uint32_t)rv.n_haps;
+    pl.hap_order.resize(n);
+    for (uint32_t j = 0; j < n; ++j) pl.hap_order[j] = j;
+    std::stable_sort(pl.hap_order.begin(), pl.hap_order.end(), [&](uint32_t a, uint32_t b) {
+        const phmm_hap &x = rv.haps[a], &y = rv.haps[b];
+        if (x.len != y.len) return x.len < y.len;
+        return x.len > 0 && std::memcmp(x.bases, y.bases, (size_t)x.len) < 0;
+    });
+    pl.hap_plan.assign(n, pfx_plan(0, 0, 0, 0));
+    pl.shared_cols = 0;
+    const uint32_t group = std::max(1u, pl.group);
+    std::vector<uint32_t> shared(n + 1, 0);        // tiles position j shares with position j-1 of the same unit
+    for (uint32_t j = 1; j < n; ++j) {
+        if (j % group == 0) continue;
+        const phmm_hap &x = rv.haps[pl.hap_order[j - 1]], &y = rv.haps[pl.hap_order[j]];
+        if (x.len != y.len || x.len <= 0 || hap_tiles(x.len) > kPfxMaxTiles) continue;
+        int32_t lcp = 0;
+        while (lcp < x.len && x.bases[lcp] == y.bases[lcp]) ++lcp;
+        shared[j] = lcp == x.len ? ((uint32_t)lcp + kTile - 1u) / kTile : (uint32_t)lcp / kTile;
+    }
+    struct Ck { uint32_t tiles, slot; } stack[kPfxSlots];
+    int depth = 0;
+    for (uint32_t j = 0; j < n; ++j) {
+        if (j % group == 0) depth = 0;
+        while (depth && stack[depth - 1].tiles > shared[j]) --depth;
+        uint32_t ts = 0, rs = 0, tv = 0, ss = 0;
+        if (depth) { ts = stack[depth - 1].tiles; rs = stack[depth - 1].slot + 1; }
+        const uint32_t next = (j + 1 < n && (j + 1) % group != 0) ? shared[j + 1] : 0;
+        if (next > ts && depth < kPfxSlots) {
+            uint32_t used = 0;
+            for (int d = 0; d < depth; ++d) used |= 1u << stack[d].slot;
+            while (used & (1u << ss)) ++ss;
+            tv = next;
+            stack[depth++] = Ck{next, ss};
+        }
+        pl.hap_plan[j] = pfx_plan(ts, rs, tv, ss);
+        pl.shared_cols += std::min<uint64_t>((uint64_t)rv.haps[pl.hap_order[j]].len, (uint64_t)ts * kTile);
     }
 }
 
@@ -323,13 +379,27 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     s.float_variant = (h->cfg.use_double || h->cfg.exact_fp32) ? (h->cfg.exact_fp32 ? Variant::F32_EXACT : Variant::F32_GEN)
                       : (s.uniform_gcp && !h->cfg.reserved[0]) ? (h->cfg.reserved[2] ? Variant::F32_UG : Variant::F32_PK)
                       : Variant::F32_GEN;
+    // prefix sharing (config.reserved[4]) reorders a region's haplotypes inside the chunk; the fused epilogue reports
+    // haplotype indices and breaks ties by position, so it keeps the caller's order
+    const bool pfx_candidate = s.float_variant == Variant::F32_PK && h->cfg.reserved[4] && !h->ep_on;
     const int forced_w = h->cfg.reserved[1];
     const double ms_plan = ms_since(t0);
-    parallel_for(n_regs, threads, 8, [&](size_t i) { bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w); });
+    parallel_for(n_regs, threads, 8, [&](size_t i) {
+        bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w);
+        if (pfx_candidate) plan_prefix(s.regions[i], s.plans[i]);
+    });
+    if (pfx_candidate) {
+        // the sharing kernel's dirty and checkpoint steps cost ~10 % of its rate (tools/prefix_perf.py): reserved[4] == 1
+        // takes it only when the plan saves more than that, reserved[4] >= 2 always (testing)
+        uint64_t all = 0, shared = 0;
+        for (size_t i = 0; i < n_regs; ++i) { all += s.plans[i].read_bytes * s.plans[i].hap_bytes; shared += s.plans[i].read_bytes * s.plans[i].shared_cols; }
+        if (h->cfg.reserved[4] >= 2 || (double)shared > kPfxMinSharedFrac * (double)all) s.float_variant = Variant::F32_PFX;
+        else for (size_t i = 0; i < n_regs; ++i) { s.plans[i].hap_order.clear(); s.plans[i].hap_plan.clear(); s.plans[i].shared_cols = 0; }
+    }
     const double ms_bin = ms_since(t0);
 
     // prefix sums
-    uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0;
+    uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0, swept = 0;
     uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
     std::vector<uint32_t> bin_count(kNumBins, 0);
     uint32_t bin_pairs[kNumBinsW32] = {0};
@@ -354,6 +424,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         uint64_t rl = 0;
         for (int r = 0; r < s.regions[i].n_reads; ++r) rl += (uint64_t)read_ref(s.regions[i], (size_t)r).len;
         cells += rl * p.hap_bytes;
+        swept += p.read_bytes * (p.hap_bytes - p.shared_cols);
         pairs += (uint64_t)s.regions[i].n_reads * (uint64_t)s.regions[i].n_haps;
         reads_in += (uint64_t)s.regions[i].n_reads;
     }
@@ -364,7 +435,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     const uint32_t n_units = s.bin_start[kNumBins];
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
-    s.cells = cells; s.pairs = pairs; s.reads_in = reads_in;
+    s.cells = cells; s.pairs = pairs; s.reads_in = reads_in; s.cells_swept = swept;
 
     cudaError_t e;
 #define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
@@ -383,6 +454,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         s.raw_indel_q |= s.plans[i].any_indel_q;
     }
     if (s.raw_on) { RES(h_mapq, nu + 1); RES(d_mapq, nu + 1); }
+    if (s.float_variant == Variant::F32_PFX) { RES(h_happlan, hl + 1); RES(d_happlan, hl + 1); }
     if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
@@ -429,8 +501,10 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         }
         uint64_t ho = p.hap_byte_off;
         uint32_t wo = p.hap_word_off;
+        const bool pfx = s.float_variant == Variant::F32_PFX;
         for (int q = 0; q < rv.n_haps; ++q) {
-            const phmm_hap &hp = rv.haps[q];
+            const phmm_hap &hp = rv.haps[pfx ? p.hap_order[q] : (uint32_t)q];
+            if (pfx) s.h_happlan.p[p.hap_list_off + q] = p.hap_plan[q];
             if (hp.len) std::memcpy(s.h_hapbytes.p + ho, hp.bases, hp.len);
             s.h_hapoff.p[p.first_hap + q] = ho;
             s.h_haps.p[p.first_hap + q] = DevHap{wo, hp.len};
@@ -476,6 +550,10 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, cudaMemcpyAsync(s.d_hapoff.p, s.h_hapoff.p, sizeof(uint64_t) * s.n_haps, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_haps.p, s.h_haps.p, sizeof(DevHap) * s.n_haps, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_haplist.p, s.h_haplist.p, sizeof(uint32_t) * s.n_haplist, cudaMemcpyHostToDevice, st));
+        if (s.float_variant == Variant::F32_PFX) {
+            CU(h, cudaMemcpyAsync(s.d_happlan.p, s.h_happlan.p, sizeof(uint2) * s.n_haplist, cudaMemcpyHostToDevice, st));
+            h->stats.h2d_bytes += sizeof(uint2) * (uint64_t)s.n_haplist;
+        }
     }
     if (n_units) CU(h, cudaMemcpyAsync(s.d_units.p, s.h_units.p, sizeof(DevUnit) * n_units, cudaMemcpyHostToDevice, st));
     if (s.ep_on && s.n_uniq) {
@@ -511,7 +589,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
     const HostTables &t = host_tables();
     KernelArgs a{};
     a.rd = s.d_rd.p; a.plane = s.plane; a.reads = s.d_reads.p; a.hapw = s.d_hapw.p; a.haps = s.d_haps.p;
-    a.hap_list = s.d_haplist.p; a.fres = s.d_fres.p; a.out = s.d_out.p; a.flag = s.d_flag.p;
+    a.hap_list = s.d_haplist.p; a.hap_plan = s.d_happlan.p; a.fres = s.d_fres.p; a.out = s.d_out.p; a.flag = s.d_flag.p;
     a.log10_init_d = h->log10_init_d;
     // uniform gap-continuation constants, computed exactly as the per-row path does (ph2pr[c], 1 - ph2pr[c])
     const int gc = s.gcp_value & 127;
@@ -636,8 +714,13 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
             }
             if (s.ep_on && rv.summ) rv.summ[r] = s.h_summ.p[p.first_uniq + u];
             const size_t src = (size_t)p.upair_off + (size_t)u * nh;
-            std::memcpy(o, s.h_out.p + src, nh * sizeof(double));
-            if (f) std::memcpy(f, s.h_flag.p + src, nh);
+            if (p.hap_order.empty()) {
+                std::memcpy(o, s.h_out.p + src, nh * sizeof(double));
+                if (f) std::memcpy(f, s.h_flag.p + src, nh);
+            } else {                   // prefix sharing: the chunk holds the haplotypes in sorted order
+                for (size_t q = 0; q < nh; ++q) o[p.hap_order[q]] = s.h_out.p[src + q];
+                if (f) for (size_t q = 0; q < nh; ++q) f[p.hap_order[q]] = s.h_flag.p[src + q];
+            }
         }
         for (size_t q = 0; q < (size_t)p.n_uniq * nh; ++q) resc += s.h_flag.p[p.upair_off + q];
         rescued += resc; uniq_pairs += (uint64_t)p.n_uniq * nh;
@@ -645,6 +728,7 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     h->stats.host_ms_scatter += ms_since(t0);
     h->stats.regions += s.regions.size(); h->stats.reads += s.reads_in; h->stats.unique_reads += s.n_uniq;
     h->stats.pairs += s.pairs; h->stats.unique_pairs += uniq_pairs.load(); h->stats.cells += s.cells;
+    h->stats.cells_swept += s.cells_swept;
     h->stats.rescued_pairs += rescued.load();
     s.busy = false;
     return PAIRHMM_OK;
@@ -698,6 +782,29 @@ int pairhmm_cuda_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm
     if (mm_f) std::memcpy(mm_f, t.mm_f, sizeof t.mm_f);
     if (ph2pr_d) std::memcpy(ph2pr_d, t.ph2pr_d, sizeof t.ph2pr_d);
     if (mm_d) std::memcpy(mm_d, t.mm_d, sizeof t.mm_d);
+    return PAIRHMM_OK;
+}
+
+int pairhmm_cuda_prefix_plan(const phmm_hap *haps, int n_haps, int unit_haps, uint32_t *order, uint32_t *t_start,
+                             int32_t *restore_slot, uint32_t *t_save, uint32_t *save_slot, uint64_t *shared_cols) {
+    if (n_haps < 0 || (n_haps > 0 && (!haps || !order || !t_start || !restore_slot || !t_save || !save_slot))) return PAIRHMM_ERR_ARG;
+    int32_t hmax = 0;
+    for (int i = 0; i < n_haps; ++i) {
+        if (haps[i].len < 0 || (haps[i].len > 0 && !haps[i].bases)) return PAIRHMM_ERR_ARG;
+        hmax = std::max(hmax, haps[i].len);
+    }
+    RegionView rv{};
+    rv.haps = haps; rv.n_haps = n_haps;
+    RegionPlan pl;
+    pl.group = unit_haps > 0 ? (uint32_t)std::min(unit_haps, (int)kMaxUnitHaps) : default_unit_haps(n_haps, hmax);
+    plan_prefix(rv, pl);
+    for (int q = 0; q < n_haps; ++q) {
+        const uint2 w = pl.hap_plan[q];
+        order[q] = pl.hap_order[q];
+        t_start[q] = w.x & 0xffffu; t_save[q] = w.x >> 16;
+        restore_slot[q] = (int32_t)(w.y & 0xffu) - 1; save_slot[q] = (w.y >> 8) & 0xffu;
+    }
+    if (shared_cols) *shared_cols = pl.shared_cols;
     return PAIRHMM_OK;
 }
 
@@ -1211,7 +1318,7 @@ int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *f
     if (kernel_ms) *kernel_ms = a;
     if (float_kernel_ms) *float_kernel_ms = b;
     h->stats.gpu_ms_total += a; h->stats.gpu_ms_float += b; h->stats.gpu_ms_double += a - b;
-    h->stats.cells += s.cells; h->stats.pairs += s.pairs;
+    h->stats.cells += s.cells; h->stats.pairs += s.pairs; h->stats.cells_swept += s.cells_swept;
     return PAIRHMM_OK;
 }
 
@@ -1227,10 +1334,10 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
     }
     int st = download_chunk(h, s);
     if (st != PAIRHMM_OK) return st;
-    const uint64_t c = h->stats.cells, p = h->stats.pairs;   // finish_chunk would count the batch again
+    const uint64_t c = h->stats.cells, p = h->stats.pairs, cs = h->stats.cells_swept;   // finish_chunk would count the batch again
     const double g0 = h->stats.gpu_ms_total, g1 = h->stats.gpu_ms_float, g2 = h->stats.gpu_ms_double;
     st = finish_chunk(h, s, pack_threads(h));
-    h->stats.cells = c; h->stats.pairs = p;
+    h->stats.cells = c; h->stats.pairs = p; h->stats.cells_swept = cs;
     h->stats.gpu_ms_total = g0; h->stats.gpu_ms_float = g1; h->stats.gpu_ms_double = g2;
     return st;
 }
@@ -1253,7 +1360,9 @@ int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int
         const size_t nh = (size_t)rv.n_haps;
         for (int r = 0; r < rv.n_reads; ++r, off += nh) {
             const uint32_t u = p.uniq_of_read[r];
-            for (size_t q = 0; q < nh; ++q) fres_out[off + q] = (u == kNoRead) ? 0.f : tmp[(size_t)p.upair_off + (size_t)u * nh + q];
+            for (size_t q = 0; q < nh; ++q)
+                fres_out[off + (p.hap_order.empty() ? q : (size_t)p.hap_order[q])] =
+                    (u == kNoRead) ? 0.f : tmp[(size_t)p.upair_off + (size_t)u * nh + q];
         }
     }
     return PAIRHMM_OK;

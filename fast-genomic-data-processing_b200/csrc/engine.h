@@ -53,6 +53,10 @@ struct RegionPlan {
     std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
     std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
     bool any_indel_q = false;            // raw reads: some read has its own insertion / deletion qualities
+    // prefix sharing (Variant::F32_PFX): the region's haplotypes are laid out ordered by (length, bytes)
+    std::vector<uint32_t> hap_order;     // position in the chunk -> index in the caller's list (empty = identity)
+    std::vector<uint2> hap_plan;         // sweep plan per position (kernels.cuh: pfx_plan)
+    uint64_t shared_cols = 0;            // haplotype columns not swept again thanks to a checkpoint
 };
 
 // Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
@@ -65,6 +69,7 @@ struct Slot {
     PinnedBuf<DevHap> h_haps;
     PinnedBuf<uint64_t> h_hapoff;
     PinnedBuf<uint32_t> h_haplist;
+    PinnedBuf<uint2> h_happlan;       // F32_PFX: sweep plan per hap_list entry
     PinnedBuf<DevUnit> h_units;
     PinnedBuf<double> h_out;
     PinnedBuf<int32_t> h_mapq;        // raw reads: mapping quality per unique read
@@ -76,6 +81,7 @@ struct Slot {
     DevBuf<DevHap> d_haps;
     DevBuf<uint64_t> d_hapoff;
     DevBuf<uint32_t> d_haplist, d_hapw, d_counters;
+    DevBuf<uint2> d_happlan;
     DevBuf<DevUnit> d_units, d_rescue;
     DevBuf<float> d_fres;
     DevBuf<double> d_out;
@@ -95,6 +101,7 @@ struct Slot {
     bool uniform_gcp = false;                 // every gcp byte of the chunk equals gcp_value -> UG kernels
     uint8_t gcp_value = 0;
     uint64_t cells = 0, pairs = 0, reads_in = 0;
+    uint64_t cells_swept = 0;         // DP cells the FP32 pass sweeps: unique reads x haplotype columns not shared
     bool busy = false;
     bool ep_on = false;               // this chunk runs the fused epilogue (pairhmm_cuda_compute_*_normalized)
     pairhmm_cuda_epilogue ep{};

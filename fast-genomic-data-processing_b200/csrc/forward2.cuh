@@ -95,8 +95,14 @@ __host__ __device__ constexpr size_t pk_etab_bytes(int K) { return (size_t)6 * p
 template <typename S> struct PkHapInfo;
 template <> struct PkHapInfo<float>  { uint32_t tix; float initY; int32_t tiles; };
 template <> struct PkHapInfo<double> { uint32_t tix; int32_t tiles; double initY; uint32_t idx, pad_; };
+// prefix-sharing kernel: tix / tiles describe the sweep (first tile after the shared prefix, tiles left); save_tix1 = index
+// of the tile AFTER the last one the checkpoint covers (~0: none); slots = restore slot + 1 | save slot << 8 (kernels.cuh)
+struct PkHapInfoPfx { uint32_t tix; float initY; int32_t tiles; uint32_t save_tix1, slots; };
 template <typename P> __host__ __device__ constexpr size_t pk_smem_bytes_t(int K) {
     return (size_t)(kThreads / 32) * (pk_etab_bytes(K) + sizeof(PkHapInfo<typename P::S>) * kMaxUnitHaps);
+}
+__host__ __device__ constexpr size_t pk_smem_bytes_pfx(int K) {
+    return (size_t)(kThreads / 32) * (pk_etab_bytes(K) + sizeof(PkHapInfoPfx) * kMaxUnitHaps);
 }
 __host__ __device__ constexpr size_t pk_smem_bytes(int K) { return pk_smem_bytes_t<PkF32>(K); }
 __host__ __device__ constexpr size_t pk_smem_bytes_f64(int K) { return pk_smem_bytes_t<PkF64>(K); }
@@ -132,14 +138,15 @@ template <typename S> __device__ __forceinline__ S e_of(const RowConstT<S> &c, u
 #define PHMM_MINB_PK 2
 #endif
 
-template <typename P, int W, int K, int KL>
+template <typename P, int W, int K, int KL, bool PFX = false>
 __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
+    static_assert(!PFX || sizeof(typename P::S) == 4, "prefix sharing is an FP32-pass feature (the rescue is per pair, IntelPairHmm.cc:700-703)");
     static_assert(W == 32 || W == 16 || W == 8, "lane-group width");
     static_assert(KL >= 0 && KL < K, "last-row slot out of range");
     using V = typename P::V;
     using S = typename P::S;
     using Quad = QuadT<V>;
-    using HapRow = PkHapInfo<S>;
+    using HapRow = std::conditional_t<PFX, PkHapInfoPfx, PkHapInfo<S>>;
     constexpr bool F64 = sizeof(S) == 8;
     constexpr int C = kTile;
     using Tile = typename TileWord<C>::type;
@@ -205,7 +212,15 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
         if (sl == W - 1) { nMM = P::zero(); nMX = P::zero(); }
 
         // haplotype table of the unit for the SEP handler and the step schedule
-        if constexpr (!F64) {
+        if constexpr (PFX) {
+            if ((uint32_t)lane < unit_nh) {
+                const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
+                const uint2 pl = a.hap_plan[unit.hap_list + lane];
+                const uint32_t ts = pl.x & 0xffffu, tv = pl.x >> 16;
+                hap_info[lane] = HapRow{hp.off / C + ts, hp.len ? __fdiv_rn(Num<float>::init_const(), (float)hp.len) : 0.f,
+                                        (int32_t)(hap_tiles(hp.len) - ts), tv ? hp.off / C + tv : 0xffffffffu, pl.y};
+            }
+        } else if constexpr (!F64) {
             if ((uint32_t)lane < unit_nh) {                // nh <= kMaxUnitHaps == 32 (host guarantees)
                 const DevHap hp = a.haps[a.hap_list[unit.hap_list + lane]];
                 hap_info[lane] = HapRow{hp.off / C, hp.len ? __fdiv_rn(Num<float>::init_const(), (float)hp.len) : 0.f,   // template.h:115
@@ -235,6 +250,10 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
 #pragma unroll
         for (int j = 0; j < C; ++j) { Din[j] = Uin[j] = P::zero(); }
 
+        // prefix sharing: checkpoints of this lane (local memory: the slot index is dynamic), the tile index at which the
+        // current sweep writes one, and the slots of the current sweep
+        V ck[PFX ? kPfxSlots : 1][3 * K + 3];
+        uint32_t save_at = 0xffffffffu, pfx_slots = 0u;
         int cur = -1;
         uint32_t tix1 = 32 - sl;                       // lane l sees l PAD tiles, then [PAD.., SEP] (tile 31)
         const Tile *tp = tiles + tix1;                 // points at w1
@@ -284,10 +303,11 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
         // one pipeline step = the C columns of this lane's current tile. DIRTY steps are those in which some lane of the
         // warp may hold a SEP tile (the W steps after a haplotype boundary enters lane 0); all others run the branch-free
         // CLEAN instance, whose body is a single basic block.
-        auto step = [&](auto dirty_tag) {
+        auto step = [&](auto dirty_tag, auto save_tag) {
             constexpr bool DIRTY = decltype(dirty_tag)::value;
+            constexpr bool SAVE = PFX && (DIRTY || decltype(save_tag)::value);   // may some lane write a checkpoint in this step?
+            bool sep = false;
             if (DIRTY) {
-                bool sep = false;
 #pragma unroll
                 for (int j = 0; j < C; ++j) sep |= (tw_get(w, j) & 0xC0000000u) == 0x80000000u;
                 // SEP word = column 0 of the next haplotype: emit the finished one, switch. Done before the columns of the
@@ -309,6 +329,10 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 const HapRow hi = hap_info[has ? cur : 0];
                 const uint32_t target = has ? hi.tix : 32u;                        // 32 = drain PAD tiles
                 const S initY = has ? hi.initY : (S)0;
+                if constexpr (PFX) {
+                    save_at = sep ? (has ? hi.save_tix1 : 0xffffffffu) : save_at;
+                    pfx_slots = sep ? (has ? hi.slots : 0u) : pfx_slots;
+                }
                 // row 0 of the matrix seen from row 1: ((0*pMM + 0*pGAPM) + Y0*pGAPM) = Y0*pGAPM[row 1]
                 Dbound = P::sel(sep, P::bc(initY * Num<S>::ugapm(a)), Dbound);
                 Din[C - 1] = P::sel(sep && lane0, Dbound, Din[C - 1]);   // becomes Dprev of the next step's first column
@@ -329,6 +353,26 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 Din[j] = P::sel(lane0, Dbound, dn);
                 Uin[j] = P::sel(lane0, P::zero(), un);
             }
+            if constexpr (PFX) {
+                // The SEP tile's flagged columns have wiped the lane's state: a sweep that starts behind a shared prefix takes
+                // it from the checkpoint instead. M/X/Y = the lane's rows at the prefix' last column, the sums cover the
+                // prefix' columns (same order of additions as a full sweep: the result is bit-identical), Dprev = the
+                // lane above's bottom row at that column; the inputs of the first own tile (Din/Uin) arrived in the exchange
+                // just above -- the lane above restored one step earlier and has swept that tile in this step
+                if (DIRTY && sep && (pfx_slots & 0xffu)) {
+                    const V *c = ck[(pfx_slots & 0xffu) - 1u];
+#pragma unroll
+                    for (int k = 0; k < K; ++k) { M[k] = c[k]; X[k] = c[K + k]; Y[k] = c[2 * K + k]; }
+                    sumM = c[3 * K]; sumX = c[3 * K + 1]; Dprev = c[3 * K + 2];
+                }
+                // the lane has just finished the last tile another haplotype of the unit shares with this one
+                if (SAVE && tix1 == save_at) {
+                    V *c = ck[(pfx_slots >> 8) & 0xffu];
+#pragma unroll
+                    for (int k = 0; k < K; ++k) { c[k] = M[k]; c[K + k] = X[k]; c[2 * K + k] = Y[k]; }
+                    c[3 * K] = sumM; c[3 * K + 1] = sumX; c[3 * K + 2] = Dprev;
+                }
+            }
             // rotate the tile queue at the END of the step: w is dead by now, so the load can land in a free register and
             // nothing waits for it here; it is consumed two steps later (a full step of latency hiding)
             w = w1;
@@ -339,11 +383,29 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
         // is the drain
         for (uint32_t h = 0; h <= unit_nh; ++h) {
             const int T = h < unit_nh ? hap_info[h].tiles : W;
-            const int nd = min(W, T), nc = T - nd;
+            const int nd = min(W, T);
 PHMM_UNROLL(1)
-            for (int i = 0; i < nd; ++i) step(std::true_type{});
+            for (int i = 0; i < nd; ++i) step(std::true_type{}, std::false_type{});
+            if constexpr (PFX) {
+                // lane l finishes the checkpoint's last tile in step d + l of the segment (d = tiles between the sweep's
+                // start and the checkpoint): only the steps [d, d + W) carry the save test, the rest run the plain clean
+                // instance. What sticks out beyond the segment falls into the dirty steps of the next ones (d < T),
+                // which always test
+                int a_ = T, b_ = T;
+                if (h < unit_nh && hap_info[h].save_tix1 != 0xffffffffu) {
+                    const int d = (int)(hap_info[h].save_tix1 - hap_info[h].tix);
+                    a_ = min(max(d, nd), T); b_ = min(max(d + W, nd), T);
+                }
 PHMM_UNROLL(1)
-            for (int i = 0; i < nc; ++i) step(std::false_type{});
+                for (int i = nd; i < a_; ++i) step(std::false_type{}, std::false_type{});
+PHMM_UNROLL(1)
+                for (int i = a_; i < b_; ++i) step(std::false_type{}, std::true_type{});
+PHMM_UNROLL(1)
+                for (int i = b_; i < T; ++i) step(std::false_type{}, std::false_type{});
+            } else {
+PHMM_UNROLL(1)
+                for (int i = nd; i < T; ++i) step(std::false_type{}, std::false_type{});
+            }
         }
     }
 }
@@ -352,6 +414,11 @@ PHMM_UNROLL(1)
 template <int W, int K, int KL>
 __global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2_kernel(const KernelArgs a) {
     wide_forward<PkF32, W, K, KL>(a);
+}
+// FP32 pass with prefix sharing between the same-length haplotypes of a unit (kernels.cuh, Variant::F32_PFX)
+template <int W, int K, int KL>
+__global__ void __launch_bounds__(kThreads, PHMM_MINB_PK) forward2p_kernel(const KernelArgs a) {
+    wide_forward<PkF32, W, K, KL, true>(a);
 }
 // FP64 rescue pass: one read per lane, same structure
 template <int W, int K, int KL>

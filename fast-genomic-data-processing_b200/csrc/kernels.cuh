@@ -88,7 +88,23 @@ struct KernelArgs {
     double log10_init_d;          // log10(2^1020), host libm (Context.h:143)
     uint32_t rescue_filter;       // FP64 launches over rescue units: a unit names a read and its whole haplotype run, only
                                   // the pairs with fres < 1e-28f are swept
+    const uint2 *hap_plan;        // F32_PFX: sweep plan per hap_list entry (pfx_plan() below)
 };
+
+// Prefix sharing (the reference's trie, M2/trie/buildTreeUtils.cpp:155-258 + avx-pairhmm-template.h:475-721,
+// shares the DP columns of a common prefix between SAME-LENGTH haplotypes -- the initial Y row is 2^s/H, template.h:115, so
+// only equal H gives equal columns). Here: the host orders a region's haplotypes by (length, bytes), and for every
+// haplotype of a work unit names the tile its sweep starts at (t_start tiles are shared with an earlier haplotype of the
+// unit), the checkpoint slot that holds the lane state after those tiles, and at most one tile boundary t_save at which this
+// sweep leaves a checkpoint for a later one. A checkpoint = a lane's M/X/Y rows, its last-row sums and the diagonal input
+// of the next column, kept per thread in local memory; lanes save / restore at their own (skewed) step.
+constexpr int kPfxSlots = 4;                 // checkpoints alive at once per lane (depth of the shared-prefix stack)
+// x = t_start | t_save << 16 (tiles from the haplotype's first tile; t_save == 0: no checkpoint is written)
+// y = restore slot + 1 (0 = fresh start, t_start == 0) | save slot << 8
+inline __host__ __device__ uint2 pfx_plan(uint32_t t_start, uint32_t restore_slot_plus1, uint32_t t_save, uint32_t save_slot) {
+    return make_uint2(t_start | (t_save << 16), restore_slot_plus1 | (save_slot << 8));
+}
+constexpr uint32_t kPfxMaxTiles = 0xffffu;   // haplotypes with more tiles are swept without sharing
 
 // Between the passes: every read with at least one pair below the reference's threshold (fres < 1e-28f,
 // IntelPairHmm.cc:342) becomes ONE unit of the FP64 pass -- the read against its unit's whole haplotype run, the FP64
@@ -173,11 +189,13 @@ inline void bin_shape(int bin, int &W, int &K, int &KL) {
 // F32_PK: packed (two reads per lane, FFMA2) uniform-gcp kernel of forward2.cuh -- the production FP32 path;
 // F32_UG: scalar uniform-gcp kernel (W = 32 only; kept as the cross-check of the packed one);
 // F32_GEN / F32_EXACT / F64_GEN: per-row gap-continuation registers, W = 32 only;
-// F64_PK: the wide kernel of forward2.cuh on doubles (uniform gcp, W = 32) -- the production FP64 rescue path.
-enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3, F32_PK = 4, F64_PK = 5 };
-constexpr int kNumVariants = 6;
+// F64_PK: the wide kernel of forward2.cuh on doubles (uniform gcp, W = 32) -- the production FP64 rescue path;
+// F32_PFX: F32_PK with prefix sharing between the same-length haplotypes of a work unit (config.reserved[4]).
+enum class Variant { F32_UG = 0, F32_GEN = 1, F32_EXACT = 2, F64_GEN = 3, F32_PK = 4, F64_PK = 5, F32_PFX = 6 };
+constexpr int kNumVariants = 7;
+inline bool is_packed_f32(Variant v) { return v == Variant::F32_PK || v == Variant::F32_PFX; }
 // reads swept by one warp
-inline int reads_per_warp(Variant v, int W) { return (v == Variant::F32_PK ? 2 : 1) * (32 / W); }
+inline int reads_per_warp(Variant v, int W) { return (is_packed_f32(v) ? 2 : 1) * (32 / W); }
 
 // Launchers. All asynchronous on `st`; return the cudaError of the launch.
 cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off, const DevHap *haps,

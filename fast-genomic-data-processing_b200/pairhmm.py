@@ -22,6 +22,7 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_default_read_model", "pairhmm_cuda_compute_raw", "pairhmm_cuda_compute_batch_raw",
     "pairhmm_cuda_compute_flat_raw", "pairhmm_cuda_prepare_reads_flat",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
+    "pairhmm_cuda_prefix_plan",
 ]
 MM_COUNT = 8256
 
@@ -45,7 +46,7 @@ class Stats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("calls", "regions", "reads", "unique_reads", "pairs", "unique_pairs",
                                           "cells", "rescued_pairs", "h2d_bytes", "d2h_bytes", "kernel_launches")] + \
                [(n, C.c_double) for n in ("gpu_ms_float", "gpu_ms_double", "gpu_ms_total", "host_ms_pack",
-                                          "host_ms_scatter", "host_ms_total")]
+                                          "host_ms_scatter", "host_ms_total")] + [("cells_swept", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -147,6 +148,27 @@ def device_count():
     return int(load_library().pairhmm_cuda_device_count())
 
 
+def prefix_plan(haps, unit_haps=0):
+    """the engine's prefix-sharing plan for one region's haplotypes (pairhmm_cuda_prefix_plan; host logic, no device):
+    dict of order, t_start, restore_slot, t_save, save_slot (arrays in sweep order) and shared_cols"""
+    lib = load_library()
+    haps = [np.ascontiguousarray(h, np.uint8) for h in haps]
+    n = len(haps)
+    arr = (PhmmHap * max(1, n))()
+    for i, hp in enumerate(haps):
+        arr[i].bases = hp.ctypes.data if hp.size else None
+        arr[i].len = int(hp.size)
+    order, ts, tv, ss = (np.zeros(n, np.uint32) for _ in range(4))
+    rs = np.zeros(n, np.int32)
+    shared = C.c_uint64(0)
+    lib.pairhmm_cuda_prefix_plan.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.POINTER(C.c_uint64)]
+    st = lib.pairhmm_cuda_prefix_plan(C.cast(arr, C.c_void_p), n, int(unit_haps), order.ctypes.data, ts.ctypes.data,
+                                      rs.ctypes.data, tv.ctypes.data, ss.ctypes.data, C.byref(shared))
+    if st != 0:
+        raise PairHMMError(st, "pairhmm_cuda_prefix_plan")
+    return {"order": order, "t_start": ts, "restore_slot": rs, "t_save": tv, "save_slot": ss, "shared_cols": int(shared.value)}
+
+
 def host_tables():
     """the lookup tables the engine uploads: (ph2pr_f32[128], mm_f32[8256], ph2pr_f64[128], mm_f64[8256])"""
     lib = load_library()
@@ -165,7 +187,8 @@ class Engine:
     """One libpairhmm_cuda handle (one per host thread, like one PairHMM per Mutect2Cpp worker)."""
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
-                 chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0):
+                 chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0,
+                 prefix_sharing=False, unit_haps=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
@@ -175,6 +198,10 @@ class Engine:
         cfg.reserved[1] = int(lane_group)      # 8 | 16 | 32: force that lane-group width where it fits
         cfg.reserved[3] = int(max_ctas_per_sm) # tuning: cap on resident CTAs per SM
         cfg.reserved[2] = int(scalar_uniform)  # scalar instead of packed (FFMA2) uniform-gcp kernels (testing)
+        # same-length haplotypes sharing a prefix are swept from a checkpoint (the trie analogue): True / 1 = when it pays,
+        # 2 = always (testing)
+        cfg.reserved[4] = int(prefix_sharing)
+        cfg.reserved[5] = int(unit_haps)       # haplotypes per work unit (tuning / testing)
         self.h = C.c_void_p()
         st = self.lib.pairhmm_cuda_create(C.byref(cfg), C.byref(self.h))
         if st != 0:

@@ -317,6 +317,40 @@ def config5(n_regions=25000, profile="clean", shard=0, select=None):
                       name="C5-%s-%d-s%d" % (profile, len(ids), shard), foreign_frac=0.02, region_ids=ids)
 
 
+def snv_family(n_regions=64, n_reads=64, n_haps=12, R=150, H=300, profile="clean", seed_extra=0, max_snvs=3,
+               dup_frac=0.15, indel_frac=0.0):
+    """The workload the reference's trie path is built for (VectorLoglessPairHMM.cpp:35: nHaps / nDistinctLens > 3):
+    a region's haplotypes are the reference haplotype plus variants that differ from it (or from another variant)
+    by a few SNVs only, so most have the same length and share long prefixes. `dup_frac` of the haplotypes repeat an
+    earlier one exactly, `indel_frac` carry a 1-5 bp indel on top (another length: never shared). H may be an int or
+    a per-region list. Reads as in the other configs."""
+    Hs = [int(H)] * n_regions if np.isscalar(H) else [int(x) for x in H]
+    b = make_batch(SEED0 + 7 + seed_extra, [n_reads] * n_regions, [np.full(n_haps, h) for h in Hs], R, profile,
+                   name="snv-family-" + profile, foreign_frac=0.1)
+    hb, hl = [], []
+    for g in range(n_regions):
+        rng = np.random.default_rng([SEED0 + 77 + seed_extra, g])
+        h0 = int(b.reg_hap_start[g])
+        fam = [b.hap_bases[int(b.hap_off[h0]):int(b.hap_off[h0]) + int(b.hap_len[h0])].copy()]
+        for _ in range(1, n_haps):
+            par = fam[int(rng.integers(0, len(fam)))].copy()
+            if rng.random() >= dup_frac and len(par):
+                for _ in range(int(rng.integers(1, max_snvs + 1))):
+                    p = int(rng.integers(0, len(par)))
+                    par[p] = ACGT[(int(np.searchsorted(ACGT, par[p]) if par[p] in ACGT else 0) + int(rng.integers(1, 4))) % 4]
+            if rng.random() < indel_frac and len(par) > 8:
+                p, n = int(rng.integers(1, len(par) - 6)), int(rng.integers(1, 6))
+                par = np.concatenate([par[:p], _rand_bases(rng, n, 0.0), par[p:]]) if rng.random() < 0.5 else np.concatenate([par[:p], par[p + n:]])
+            fam.append(np.ascontiguousarray(par))
+        perm = rng.permutation(n_haps)                      # the caller's order is arbitrary
+        for k in perm:
+            hb.append(fam[int(k)]); hl.append(len(fam[int(k)]))
+    b.hap_len = np.asarray(hl, np.int32)
+    b.hap_bases = np.concatenate(hb) if hb else np.zeros(0, np.uint8)
+    b.hap_off = _offsets(b.hap_len)
+    return b
+
+
 def edge_cases(seed=1234):
     """ragged edge-case batch: R in {1,2,15,...,255}, H in {1..700} incl. R>H, N bases, lower-case and
     junk bytes (behave as 'A'), quals with the high bit set, per-base gcp != 10, quals 0/6/93/127."""

@@ -93,6 +93,15 @@ typedef struct pairhmm_cuda_config {
                              /* [1] = 8|16|32: force that lane-group width where it fits (tuning)    */
                              /* [2] != 0: scalar instead of packed (FFMA2) uniform-gcp kernels (testing) */
                              /* [3] > 0: at most that many resident CTAs per SM (tuning)              */
+                             /* [5] > 0: haplotypes per work unit (tuning; default: all of a region's, fewer */
+                             /*     when the batch is too small to fill the GPU otherwise)                  */
+                             /* [4] != 0: prefix sharing -- same-length haplotypes of a region that share  */
+                             /*     a prefix are swept from a checkpoint (the reference's trie,            */
+                             /*     VectorLoglessPairHMM.cpp:35,150-286; M2/trie/buildTreeUtils.cpp:155);  */
+                             /*     results are bit-identical to the per-pair sweep. Applies to the packed */
+                             /*     FP32 pass; calls with the fused epilogue ignore it. 1 = per launch     */
+                             /*     group, only when the plan skips enough cells to pay for the checkpoint  */
+                             /*     steps (> 12 %); 2 = always (testing)                                    */
 } pairhmm_cuda_config;
 
 typedef struct pairhmm_cuda_stats {
@@ -102,6 +111,8 @@ typedef struct pairhmm_cuda_stats {
     uint64_t kernel_launches;    /* launches of this library's own kernels                */
     double gpu_ms_float, gpu_ms_double, gpu_ms_total; /* CUDA-event times, summed over calls   */
     double host_ms_pack, host_ms_scatter, host_ms_total;
+    uint64_t cells_swept;        /* DP cells the FP32 pass swept: `cells` less duplicate reads and,      */
+                                 /* with prefix sharing, less the shared haplotype prefixes              */
 } pairhmm_cuda_stats;
 
 typedef struct pairhmm_cuda_handle pairhmm_cuda_handle;
@@ -166,6 +177,25 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
  * order; n must equal the pair count. Test hook for bit-exactness of the FP32 kernel against
  * compute_full_prob_avxs (avx-pairhmm-template.h:204-345). */
 int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n);
+
+/* ---- prefix sharing -------------------------------------------------------------------
+ * The reference's trie (VectorLoglessPairHMM::initialize picks it when nHaps / nDistinctLens > 3,
+ * VectorLoglessPairHMM.cpp:35; buildTreeUtils::buildTreeWithHaplotype_same_height, M2/trie/buildTreeUtils.cpp:155-258;
+ * compute_full_prob_with_trie_, avx-pairhmm-template.h:475-721) computes the DP columns of a prefix shared by several
+ * SAME-LENGTH haplotypes once per read. With config.reserved[4] != 0 the engine does the same inside its packed FP32
+ * pass, at the granularity of its 4-column tiles: a region's haplotypes are swept in (length, bytes) order, a sweep
+ * may leave one checkpoint of the lane state at a tile boundary and may start from an earlier one. Values are
+ * bit-identical to the per-pair sweep (same operations in the same order), as the reference's trie path is to its
+ * per-pair path; the FP64 rescue stays per pair (IntelPairHmm.cc:700-703).
+ *
+ * pairhmm_cuda_prefix_plan exposes the host-side plan for one region (no device needed; what the packer computes):
+ * order[q] = index in haps[] of the haplotype swept q-th; for the q-th sweep t_start[q] = tiles (of 4 columns) taken
+ * from a checkpoint, restore_slot[q] = the slot it is read from (-1: fresh sweep, t_start == 0), t_save[q] / save_slot[q]
+ * = the tile boundary at which it writes a checkpoint and where (t_save == 0: none). unit_haps = haplotypes per work
+ * unit (sharing never crosses a unit; 0 = as the packer would choose for a large batch). shared_cols (nullable) = sum of
+ * the columns not swept again. */
+int pairhmm_cuda_prefix_plan(const phmm_hap *haps, int n_haps, int unit_haps, uint32_t *order, uint32_t *t_start,
+                             int32_t *restore_slot, uint32_t *t_save, uint32_t *save_slot, uint64_t *shared_cols);
 
 /* ---- fused per-read epilogue ---------------------------------------------------------
  * What PairHMMLikelihoodCalculationEngine::computeReadLikelihoods does to the matrix right after the PairHMM
