@@ -43,9 +43,12 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--regions", type=int, default=0, help="c2: regions per rank (default 10000 = BASELINE configs[1]); "
                                                             "c5: regions of the whole job (default 25000 = configs[4])")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5", "snv"],
                     help="c2 = BASELINE configs[1] per GPU (weak scaling, the metric's config); c5 = configs[4], the "
-                         "whole-box chr20-scale batch LPT-sharded over the ranks (strong scaling)")
+                         "whole-box chr20-scale batch LPT-sharded over the ranks (strong scaling); snv = the workload of "
+                         "the reference's trie path (same-length haplotypes that differ by SNVs), engine with prefix "
+                         "sharing on: value / e2e are EFFECTIVE GCUPS (R x H of every pair), the roofline counts only "
+                         "the cells actually swept (SURVEY.md 8f N4)")
     ap.add_argument("--cpu-sample-regions", type=int, default=0, help="regions in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -158,7 +161,7 @@ def run_reference_arm(args, rank, world):
 def main():
     args = parse_args()
     if args.regions <= 0:
-        args.regions = 25000 if args.workload == "c5" else 10000
+        args.regions = 25000 if args.workload == "c5" else 3000 if args.workload == "snv" else 10000
     rank, world, local = dist_env()
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
@@ -206,6 +209,10 @@ def main():
         batch = synth.config5(args.regions, select=synth.lpt_shard(cost, world)[rank] if world > 1 else None)
         workload = ("BASELINE configs[4]: chr20-scale synthetic batch, %d regions x 200 reads x 10 haps, 150 bp reads, "
                     "300-500 bp haps, whole job LPT-sharded over %d GPU(s)" % (args.regions, world))
+    elif args.workload == "snv":
+        batch = synth.snv_family(args.regions, 200, 12, 150, 300, dup_frac=0.0, seed_extra=rank)
+        workload = ("SNV family (the reference's trie workload, VectorLoglessPairHMM.cpp:35): %d regions x 200 reads x 12 "
+                    "haplotypes of 300 bases that differ by 1-3 SNVs, 150 bp reads, per GPU; prefix sharing on" % args.regions)
     elif world > 1:
         _, _, cost = synth.config2_shapes(args.regions * world)
         batch = synth.config2(args.regions * world, select=synth.lpt_shard(cost, world)[rank])
@@ -216,7 +223,8 @@ def main():
                     "150 bp reads, 250-500 bp haps, per GPU" % args.regions)
     cells, pairs = batch.cells(), batch.n_pairs
     # several ranks share the box's host threads: split them instead of 16 packing threads per rank
-    eng = fgdp_b200.Engine(device=local, pack_threads=0 if world == 1 else max(2, min(16, (os.cpu_count() or 16) // world)))
+    eng = fgdp_b200.Engine(device=local, pack_threads=0 if world == 1 else max(2, min(16, (os.cpu_count() or 16) // world)),
+                           prefix_sharing=args.workload == "snv")
     eng.initialize(int(batch.read_len.max()), int(batch.hap_len.max()))
 
     # ---- device-resident replay: `value` and the roofline of the FP32 forward kernel
@@ -232,6 +240,7 @@ def main():
         ms_total += a; ms_float += f
     barrier()
     launches = eng.stats()["kernel_launches"]
+    swept_cells = eng.stats()["cells_swept"] // max(1, args.steps)      # unique reads x haplotype columns not shared
     got, resc = eng.resident_fetch()
     ms_step = reduce_max(ms_total / args.steps)
     total_cells = reduce_sum(float(cells))
@@ -273,7 +282,9 @@ def main():
     clocks = sampler.summary()
     peak_ops = n_sm * FP32_LANES_PER_SM * sm_max_mhz * 1e6                    # FMA-pipe lane-ops / s
     float_ms_step = ms_float / args.steps
-    achieved_ops = cells * PIPE_OPS_PER_CELL / (float_ms_step * 1e-3)
+    # the pipe works on the cells the kernel sweeps: with read de-duplication and prefix sharing fewer than R x H per pair
+    pipe_cells = swept_cells if args.workload == "snv" else cells
+    achieved_ops = pipe_cells * PIPE_OPS_PER_CELL / (float_ms_step * 1e-3)
     # 4 read planes (the uniform-gcp kernel never touches the gcp plane), one 4-byte column word per haplotype base,
     # one float per pair
     algo_bytes = int(batch.read_len.astype(np.int64).sum()) * 4 + int(batch.hap_len.astype(np.int64).sum()) * 4 + pairs * 4
@@ -287,6 +298,10 @@ def main():
                 "float_kernel_gcups": cells / (float_ms_step * 1e-3) / 1e9, "float_kernel_ms": float_ms_step,
                 "algorithmic_bytes": algo_bytes, "algorithmic_hbm_GBps": algo_bytes / (float_ms_step * 1e-3) / 1e9,
                 "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None}
+    if args.workload == "snv":
+        roofline["kernel"] = "forward2p_kernel<W, K, KL> (packed FP32 with prefix sharing between same-length haplotypes)"
+        roofline["swept_frac"] = swept_cells / cells
+        roofline["note"] = "achieved counts swept cells only; value / e2e / float_kernel_gcups are effective (R x H of every pair)"
     try:    # DRAM bytes of one launch of that kernel over this workload, from the committed ncu capture (profiles/)
         tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         if tr.get("regions") == args.regions and world == 1 and args.workload == "c2":

@@ -14,6 +14,10 @@ CudaPairHMM::CudaPairHMM(PairHMMNativeArgumentCollection &args, int device) {
     pairhmm_cuda_default_config(&cfg);
     cfg.device = device;
     cfg.use_double = args.useDoublePrecision ? 1 : 0;   // pairHmmNativeThreads has no meaning on the GPU
+    // the reference switches to its trie kernels when nHaps / nDistinctLens > 3 (VectorLoglessPairHMM.cpp:35); the engine makes
+    // the equivalent choice itself, per launch group, from the prefixes the same-length haplotypes really share (bit-identical
+    // results either way)
+    cfg.reserved[4] = 1;
     int st = pairhmm_cuda_create(&cfg, &handle);
     if (st != PAIRHMM_OK)
         throw std::runtime_error("CudaPairHMM: pairhmm_cuda_create failed with status " + std::to_string(st) +
