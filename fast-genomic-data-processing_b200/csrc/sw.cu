@@ -34,6 +34,7 @@ constexpr int32_t kLowInit = INT_MIN / 2;       // LOW_INIT_VALUE
 struct Args {
     const uint8_t *ref_bases, *alt_bases;
     const int64_t *ref_off, *alt_off;
+    int64_t ref_first, alt_first;               // the device copies start at these offsets of the caller's arrays
     const int32_t *ref_len, *alt_len;
     uint32_t n;
     int32_t match, mismatch, open, extend, strategy;
@@ -166,7 +167,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_kernel(const Args a) {
         if (p >= a.n) break;
         p = a.order[p];
         const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
-        const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
+        const uint8_t *rp = a.ref_bases + (a.ref_off[p] - a.ref_first), *ap = a.alt_bases + (a.alt_off[p] - a.alt_first);
         __syncwarp();
         for (int k = lane; k < nrow; k += 32) ref[k] = rp[k];
         for (int k = lane; k < ncol; k += 32) alt[k] = ap[k];
@@ -246,7 +247,7 @@ __global__ void __launch_bounds__(kWarps * 32) align_strip_kernel(const Args a) 
         if (p >= a.n) break;
         p = a.order[p];
         const int nrow = a.ref_len[p], ncol = a.alt_len[p];             // rows i = ref, columns j = alt
-        const uint8_t *rp = a.ref_bases + a.ref_off[p], *ap = a.alt_bases + a.alt_off[p];
+        const uint8_t *rp = a.ref_bases + (a.ref_off[p] - a.ref_first), *ap = a.alt_bases + (a.alt_off[p] - a.alt_first);
         __syncwarp();
         for (int k = lane; k < nrow; k += 32) ref[k] = rp[k];
         const int j0 = lane * K;                                        // this lane's columns are j0+1 .. j0+K
@@ -349,17 +350,62 @@ inline KernelFn strip_kernel_for(int K) {
 thread_local std::string g_err;
 int fail(int st, const std::string &m) { g_err = m; return st; }
 
+// Grow-only device array: a call reuses what the previous calls of this host thread allocated.
 template <class T> struct DevArr {
     T *p = nullptr;
-    cudaError_t alloc(size_t n) { return cudaMalloc(reinterpret_cast<void **>(&p), std::max<size_t>(1, n) * sizeof(T)); }
-    ~DevArr() { if (p) cudaFree(p); }
+    size_t cap = 0;
+    cudaError_t alloc(size_t n) {
+        n = std::max<size_t>(1, n);
+        if (n <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        const size_t want = n + n / 4;
+        cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&p), want * sizeof(T));
+        if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(reinterpret_cast<void **>(&p), n * sizeof(T)); if (e == cudaSuccess) cap = n; return e; }
+        cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
+
+// Per host thread (Mutect2Cpp keeps one engine per worker thread, M2/main.cpp:199) and device: stream, events, device
+// properties and the device buffers survive between calls, so a per-region call (a few hundred alignments) does not pay
+// a dozen cudaMalloc / cudaFree, a stream and two events each time. smithwaterman_cuda_release() frees them.
+struct Context {
+    int device = -1;
+    cudaDeviceProp prop{};
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    DevArr<uint8_t> d_ref, d_alt, d_scratch;
+    DevArr<int64_t> d_roff, d_aoff;
+    DevArr<int32_t> d_rlen, d_alen, d_off;
+    DevArr<char> d_cig;
+    DevArr<uint32_t> d_queue, d_order;
+    struct Occ { size_t smem = 0; int warps = 0, per_sm = 0; } occ[10];   // per kernel (index K; 0 = anti-diagonal kernel)
+    void release() {
+        if (device < 0) return;
+        int cur = -1;
+        if (cudaGetDevice(&cur) == cudaSuccess && cudaSetDevice(device) == cudaSuccess) {
+            d_ref.release(); d_alt.release(); d_scratch.release(); d_roff.release(); d_aoff.release(); d_rlen.release();
+            d_alen.release(); d_off.release(); d_cig.release(); d_queue.release(); d_order.release();
+            if (ev0) cudaEventDestroy(ev0);
+            if (ev1) cudaEventDestroy(ev1);
+            if (st) cudaStreamDestroy(st);
+            cudaSetDevice(cur);
+        }
+        cudaGetLastError();
+        *this = Context();
+    }
+    ~Context() { release(); }
+};
+thread_local Context g_ctx;
 
 }  // namespace sw
 
 extern "C" {
 
 const char *smithwaterman_cuda_last_error(void) { return sw::g_err.c_str(); }
+
+void smithwaterman_cuda_release(void) { sw::g_ctx.release(); }
 
 int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const int64_t *ref_off, const int32_t *ref_len,
                                    const uint8_t *alt_bases, const int64_t *alt_off, const int32_t *alt_len, int64_t n,
@@ -374,22 +420,33 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     if (strategy < SW_CUDA_SOFTCLIP || strategy > SW_CUDA_IGNORE) return fail(SW_CUDA_ERR_ARG, "unknown overhang strategy");
     uint32_t max_ref = 1, max_alt = 1;
     uint64_t ref_bytes = 0, alt_bytes = 0;
+    int64_t ref_first = INT64_MAX, alt_first = INT64_MAX;      // only the span the pairs touch is copied to the device
     for (int64_t p = 0; p < n; ++p) {
         if (ref_len[p] < 1 || alt_len[p] < 1 || ref_len[p] > SW_CUDA_MAX_LEN || alt_len[p] > SW_CUDA_MAX_LEN || ref_off[p] < 0 || alt_off[p] < 0)
             return fail(SW_CUDA_ERR_ARG, "sequence length outside [1, SW_CUDA_MAX_LEN] or negative offset");
         max_ref = std::max<uint32_t>(max_ref, (uint32_t)ref_len[p]); max_alt = std::max<uint32_t>(max_alt, (uint32_t)alt_len[p]);
         ref_bytes = std::max<uint64_t>(ref_bytes, (uint64_t)ref_off[p] + (uint64_t)ref_len[p]);
         alt_bytes = std::max<uint64_t>(alt_bytes, (uint64_t)alt_off[p] + (uint64_t)alt_len[p]);
+        ref_first = std::min(ref_first, ref_off[p]); alt_first = std::min(alt_first, alt_off[p]);
     }
+    ref_bytes -= (uint64_t)ref_first; alt_bytes -= (uint64_t)alt_first;
 #define SWCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(SW_CUDA_ERR_CUDA, std::string(#x ": ") + cudaGetErrorString(e_)); } while (0)
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(SW_CUDA_ERR_NO_DEVICE, "no CUDA device (this aligner has no CPU fallback)"); }
     if (device < 0) SWCU(cudaGetDevice(&device));
     if (device >= ndev) return fail(SW_CUDA_ERR_ARG, "device ordinal out of range");
-    cudaDeviceProp prop;
-    SWCU(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10) return fail(SW_CUDA_ERR_NO_DEVICE, "not an sm_100 device (kernels are built for sm_100a only)");
+    sw::Context &cx = sw::g_ctx;
+    if (cx.device != device) {
+        cx.release();
+        SWCU(cudaGetDeviceProperties(&cx.prop, device));
+        if (cx.prop.major != 10) return fail(SW_CUDA_ERR_NO_DEVICE, "not an sm_100 device (kernels are built for sm_100a only)");
+        SWCU(cudaSetDevice(device));
+        SWCU(cudaStreamCreate(&cx.st));
+        SWCU(cudaEventCreate(&cx.ev0)); SWCU(cudaEventCreate(&cx.ev1));
+        cx.device = device;
+    }
     SWCU(cudaSetDevice(device));
+    const cudaDeviceProp &prop = cx.prop;
 
     // Pairs are grouped by alt length: class c = ceil(alt_len / 32) <= 8 runs the register-blocked kernel with K = c
     // columns per lane, longer alts the anti-diagonal kernel (SW_CUDA_KERNEL=diag forces it for all). A class too small to
@@ -441,10 +498,17 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
         while (g.warps > 1 && g.warps * warp_smem > (size_t)prop.sharedMemPerBlockOptin) --g.warps;
         g.smem = g.warps * warp_smem;
         if (g.smem > (size_t)prop.sharedMemPerBlockOptin) return fail(SW_CUDA_ERR_ARG, "sequences too long for the shared-memory anti-diagonals");
-        SWCU(cudaFuncSetAttribute(g.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-        int per_sm = 0;
-        SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, g.kernel, g.warps * 32, g.smem));
-        per_sm = std::max(1, per_sm);
+        // the attribute and the occupancy query cost ~20 us each: remembered per kernel for the last shared-memory size, which
+        // is rounded up to 4 KB so that per-region calls (whose longest sequences differ a little) hit the entry
+        g.smem = std::min<size_t>((g.smem + 4095) & ~(size_t)4095, (size_t)prop.sharedMemPerBlockOptin);
+        sw::Context::Occ &oc = cx.occ[g.K];
+        if (oc.smem != g.smem || oc.warps != g.warps) {
+            SWCU(cudaFuncSetAttribute(g.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+            int q = 0;
+            SWCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, g.kernel, g.warps * 32, g.smem));
+            oc.smem = g.smem; oc.warps = g.warps; oc.per_sm = std::max(1, q);
+        }
+        const int per_sm = oc.per_sm;
         const uint64_t tail = 8ull * ((uint64_t)g.max_ref + g.max_alt + 6);                 // CIGAR element list
         g.per_warp = g.K ? ((uint64_t)g.max_ref + 33) * 128 + tail
                          : ((uint64_t)g.max_ref + g.max_alt + 1) * ((uint64_t)g.max_alt + 1) + 8 + tail;
@@ -455,22 +519,19 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
         scratch_bytes = std::max(scratch_bytes, g.per_warp * g.warps * g.grid);
     }
 
-    DevArr<uint8_t> d_ref, d_alt, d_scratch;
-    DevArr<int64_t> d_roff, d_aoff;
-    DevArr<int32_t> d_rlen, d_alen, d_off;
-    DevArr<char> d_cig;
-    DevArr<uint32_t> d_queue, d_order;
+    auto &d_ref = cx.d_ref; auto &d_alt = cx.d_alt; auto &d_scratch = cx.d_scratch; auto &d_roff = cx.d_roff; auto &d_aoff = cx.d_aoff;
+    auto &d_rlen = cx.d_rlen; auto &d_alen = cx.d_alen; auto &d_off = cx.d_off; auto &d_cig = cx.d_cig; auto &d_queue = cx.d_queue;
+    auto &d_order = cx.d_order;
     SWCU(d_ref.alloc(ref_bytes)); SWCU(d_alt.alloc(alt_bytes)); SWCU(d_roff.alloc(n)); SWCU(d_aoff.alloc(n));
     SWCU(d_rlen.alloc(n)); SWCU(d_alen.alloc(n)); SWCU(d_off.alloc(n)); SWCU(d_cig.alloc((size_t)n * cigar_stride));
     SWCU(d_queue.alloc(ngroups)); SWCU(d_order.alloc(n)); SWCU(d_scratch.alloc(scratch_bytes));
-    cudaStream_t st;
-    SWCU(cudaStreamCreate(&st));
-    cudaEvent_t ev0, ev1;
-    cudaEventCreate(&ev0); cudaEventCreate(&ev1);
-    auto cleanup = [&]() { cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaStreamDestroy(st); };
+    cudaStream_t st = cx.st;
+    cudaEvent_t ev0 = cx.ev0, ev1 = cx.ev1;
+    // a failed call drops the thread's context: the next one starts from a clean stream
+    auto cleanup = [&]() { cudaStreamSynchronize(st); cudaGetLastError(); cx.release(); };
 #define SWCU2(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(SW_CUDA_ERR_CUDA, std::string(#x ": ") + cudaGetErrorString(e_)); } } while (0)
-    SWCU2(cudaMemcpyAsync(d_ref.p, ref_bases, ref_bytes, cudaMemcpyHostToDevice, st));
-    SWCU2(cudaMemcpyAsync(d_alt.p, alt_bases, alt_bytes, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_ref.p, ref_bases + ref_first, ref_bytes, cudaMemcpyHostToDevice, st));
+    SWCU2(cudaMemcpyAsync(d_alt.p, alt_bases + alt_first, alt_bytes, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemcpyAsync(d_roff.p, ref_off, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemcpyAsync(d_aoff.p, alt_off, sizeof(int64_t) * n, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemcpyAsync(d_rlen.p, ref_len, sizeof(int32_t) * n, cudaMemcpyHostToDevice, st));
@@ -479,6 +540,7 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     SWCU2(cudaMemcpyAsync(d_order.p, order.data(), sizeof(uint32_t) * n, cudaMemcpyHostToDevice, st));
     SWCU2(cudaMemsetAsync(d_queue.p, 0, sizeof(uint32_t) * ngroups, st));
     Args a{};
+    a.ref_first = ref_first; a.alt_first = alt_first;
     a.ref_bases = d_ref.p; a.alt_bases = d_alt.p; a.ref_off = d_roff.p; a.alt_off = d_aoff.p; a.ref_len = d_rlen.p; a.alt_len = d_alen.p;
     a.match = match; a.mismatch = mismatch; a.open = open; a.extend = extend; a.strategy = strategy;
     a.cigars = d_cig.p; a.cigar_stride = cigar_stride; a.offsets = d_off.p; a.scratch = d_scratch.p;
@@ -495,7 +557,6 @@ int smithwaterman_cuda_align_batch(int device, const uint8_t *ref_bases, const i
     SWCU2(cudaMemcpyAsync(offsets, d_off.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));
     SWCU2(cudaStreamSynchronize(st));
     if (kernel_ms) cudaEventElapsedTime(kernel_ms, ev0, ev1);
-    cleanup();
     return SW_CUDA_OK;
 #undef SWCU
 #undef SWCU2

@@ -12,7 +12,8 @@ SOFTCLIP, INDEL, LEADING_INDEL, IGNORE = 9, 10, 11, 12
 ALIGNMENT_TO_BEST_HAPLOTYPE = (10, -15, -30, -5)
 NEW_SW_PARAMETERS = (200, -150, -260, -11)
 STANDARD_NGS = (25, -50, -110, -6)
-SW_SYMBOLS = ["smithwaterman_cuda_align_batch", "smithwaterman_cuda_align", "smithwaterman_cuda_last_error"]
+SW_SYMBOLS = ["smithwaterman_cuda_align_batch", "smithwaterman_cuda_align", "smithwaterman_cuda_last_error",
+              "smithwaterman_cuda_release"]
 
 
 def _lib():
@@ -23,6 +24,31 @@ def _lib():
     lib.smithwaterman_cuda_align.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_int] + [C.c_int] * 4 + [C.c_uint8]
     lib.smithwaterman_cuda_last_error.restype = C.c_char_p
     return lib
+
+
+def align_flat(ref_bases, ref_off, ref_len, alt_bases, alt_off, alt_len, params=ALIGNMENT_TO_BEST_HAPLOTYPE, strategy=SOFTCLIP,
+               device=-1, cigar_stride=None):
+    """the C call on flat numpy arrays (no Python list packing): -> (cigar bytes uint8[n, stride], offsets int32[n],
+    kernel milliseconds)"""
+    lib = _lib()
+    rb = np.ascontiguousarray(ref_bases, np.uint8); ab = np.ascontiguousarray(alt_bases, np.uint8)
+    ro = np.ascontiguousarray(ref_off, np.int64); ao = np.ascontiguousarray(alt_off, np.int64)
+    rl = np.ascontiguousarray(ref_len, np.int32); al = np.ascontiguousarray(alt_len, np.int32)
+    n = int(rl.shape[0])
+    stride = int(cigar_stride or 2 * max(1, int(rl.max(initial=1)), int(al.max(initial=1))))
+    cig = np.zeros((n, stride), np.uint8); off = np.zeros(n, np.int32)
+    ms = C.c_float(0)
+    st = lib.smithwaterman_cuda_align_batch(device, rb.ctypes.data, ro.ctypes.data, rl.ctypes.data, ab.ctypes.data,
+                                            ao.ctypes.data, al.ctypes.data, n, *[int(x) for x in params], int(strategy),
+                                            cig.ctypes.data, stride, off.ctypes.data, C.byref(ms))
+    if st != 0:
+        raise PairHMMError(st, (lib.smithwaterman_cuda_last_error() or b"").decode())
+    return cig, off, float(ms.value)
+
+
+def release():
+    """frees the calling thread's cached stream and device buffers (smithwaterman_cuda_release)"""
+    _lib().smithwaterman_cuda_release()
 
 
 def align_batch(refs, alts, params=ALIGNMENT_TO_BEST_HAPLOTYPE, strategy=SOFTCLIP, device=-1, cigar_stride=None):

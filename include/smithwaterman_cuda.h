@@ -47,6 +47,11 @@ int smithwaterman_cuda_align(uint8_t *ref, int ref_length, uint8_t *alt, int alt
 
 const char *smithwaterman_cuda_last_error(void);
 
+/* The aligner keeps, per host thread, its stream and device buffers between calls (grow-only), so that a per-region call
+ * does not pay for allocations; this frees the calling thread's (they are also freed when the thread ends). The
+ * reference has no counterpart (its scratch is per call, PairWiseSW.h:108-125). */
+void smithwaterman_cuda_release(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -151,3 +151,35 @@ def test_cuda_sw_longest_sequences():
         assert c == want_c and np.array_equal(o, want_o), (params, strat)
     with pytest.raises(Exception):
         sw.align_batch([b"A" * 4097], [b"A" * 10])
+
+
+@pytest.mark.gpu
+def test_repeated_calls_reuse_the_thread_context():
+    """per-region use: many small calls of changing size on one host thread (the stream and the device buffers are kept
+    between calls and grow), a release in the middle, and a second host thread with its own context"""
+    import threading
+    from fgdp_b200 import smithwaterman as sw
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+
+    def one_round(seed, results):
+        r = np.random.default_rng(seed)
+        out = []
+        for n, hl, rl in ((3, 60, 30), (200, 400, 150), (1, 17, 9), (64, 900, 300), (5, 40, 40)):
+            refs = [bytes(r.choice(acgt, hl + int(r.integers(0, 9)))) for _ in range(n)]
+            alts = [bytes(r.choice(acgt, rl + int(r.integers(0, 5)))) for _ in range(n)]
+            out.append((refs, alts, sw.align_batch(refs, alts)[:2]))
+        results.append(out)
+
+    res = []
+    one_round(1, res)
+    sw.release()
+    one_round(1, res)
+    th = threading.Thread(target=one_round, args=(1, res)); th.start(); th.join()
+    assert len(res) == 3
+    for k in (1, 2):
+        for (_, _, (c0, o0)), (_, _, (c1, o1)) in zip(res[0], res[k]):
+            assert c0 == c1 and np.array_equal(o0, o1)
+    import oracle_py
+    for refs, alts, (c, o) in res[0]:
+        wc, wo = oracle_py.oracle_sw(oracle_py.SWPairs(refs, alts))
+        assert c == wc and np.array_equal(o, wo)

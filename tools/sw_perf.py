@@ -25,6 +25,28 @@ for i in range(3):
     t = time.perf_counter(); c, o, ms = sw.align_batch(refs, alts); dt = time.perf_counter() - t
     print("GPU: %d pairs, %.3g cells: kernel %.2f ms (%.1f GCUPS), call %.1f ms (incl. python list packing)" % (
         n, cells, ms, cells / ms / 1e6, dt * 1e3), flush=True)
+# the C call on flat arrays (what a C++ caller pays): host arrays in, CIGAR text + offsets out, H2D / D2H inside
+rl = np.array([len(x) for x in refs], np.int32); al = np.array([len(x) for x in alts], np.int32)
+ro = np.concatenate([[0], np.cumsum(rl)[:-1]]).astype(np.int64); ao = np.concatenate([[0], np.cumsum(al)[:-1]]).astype(np.int64)
+rb = np.frombuffer(b"".join(refs), np.uint8); ab = np.frombuffer(b"".join(alts), np.uint8)
+for i in range(3):
+    t = time.perf_counter(); cig, off, ms = sw.align_flat(rb, ro, rl, ab, ao, al); dt = time.perf_counter() - t
+    print("C call, flat host arrays: %d pairs end to end %.1f ms = %.1f GCUPS (kernel %.2f ms)" % (n, dt * 1e3, cells / dt / 1e9, ms), flush=True)
+assert np.array_equal(off, o)
+for i in range(2):    # a caller that knows its reads are short passes a short CIGAR buffer: 64 B instead of 2 * max(len)
+    t = time.perf_counter(); cig, off, ms = sw.align_flat(rb, ro, rl, ab, ao, al, cigar_stride=64); dt = time.perf_counter() - t
+    print("C call, flat host arrays, cigar_stride 64: end to end %.1f ms = %.1f GCUPS (kernel %.2f ms)" % (dt * 1e3, cells / dt / 1e9, ms), flush=True)
+assert np.array_equal(off, o) and [bytes(r).split(b"\0")[0].decode() for r in cig[:2000]] == c[:2000]
+# per-region use: 200 alignments per call (one call per active region, after the PairHMM)
+m = 200
+calls = min(500, n // m)
+sw.align_flat(rb, ro[:m], rl[:m], ab, ao[:m], al[:m], cigar_stride=64)
+t = time.perf_counter()
+for k in range(calls):
+    q = slice(k * m, (k + 1) * m)
+    sw.align_flat(rb, ro[q], rl[q], ab, ao[q], al[q], cigar_stride=64)
+dt = time.perf_counter() - t
+print("per-region calls: %d calls x %d pairs: %.3f ms per call (%.1f GCUPS)" % (calls, m, dt / calls * 1e3, float((rl[:calls * m].astype(np.int64) * al[:calls * m]).sum()) / dt / 1e9), flush=True)
 ns = min(n, 20000)
 p = oracle_py.SWPairs(refs[:ns], alts[:ns])
 th = os.cpu_count() or 1
