@@ -622,7 +622,10 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, launch_finalize(f, st));
         if (s.n_upairs) h->stats.kernel_launches += 1;
         RescueScanArgs r{s.d_units.p, s.bin_start[kNumBins], s.d_reads.p, s.d_fres.p, s.d_rescue.p,
-                         s.d_counters.p + kRescueBaseDev, s.d_counters.p + kRescueCount};
+                         s.d_counters.p + kRescueBaseDev, s.d_counters.p + kRescueCount,
+                         // few reads (a region per call): one FP64 unit per underflowed pair, the pass is as short as one
+                         // sweep; many reads: the read's whole row in one unit (one pipeline fill per read)
+                         s.n_uniq <= 4096u ? 1u : s.n_uniq <= 16384u ? 2u : (uint32_t)kMaxUnitHaps};
         CU(h, launch_rescue_scan(r, st));
         if (r.n_units) h->stats.kernel_launches += 1;
     }

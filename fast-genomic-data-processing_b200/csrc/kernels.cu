@@ -50,15 +50,22 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     const uint32_t nh = unit.shape & 0xffu, nreads = (unit.shape >> 8) & 0xffu, stride = unit.shape >> 16;
     if (j >= nreads) return;
     const uint32_t out = unit.out + j * stride;
-    bool any = false;
-    for (uint32_t i = 0; i < nh; ++i) any |= a.fres[out + i] < 1e-28f;
-    if (!any) return;
     const int len = a.reads[unit.read + j].len;
     if (len < 1) return;
     const int k32 = (len + 31) >> 5;                   // the FP64 kernels run at W = 32
     const int bin = k32 * (k32 - 1) / 2 + (len - 1) % k32;
-    const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
-    a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list, unit_shape(nh, 1u, 0u), out};
+    // a run of the read's haplotypes with at most max_pairs underflowed ones becomes one FP64 unit: the whole row in a big
+    // chunk (one pipeline fill per read), single pairs in a small one (one region per call: the FP64 pass is as long as
+    // its longest unit, and a sweep of one 150 x 400 pair alone takes ~25 us)
+    uint32_t first = 0, cnt = 0;
+    for (uint32_t i = 0; i < nh; ++i) {
+        cnt += a.fres[out + i] < 1e-28f ? 1u : 0u;
+        if (cnt && (cnt == a.max_pairs || i + 1 == nh)) {
+            const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
+            a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list + first, unit_shape(i + 1 - first, 1u, 0u), out + first};
+            first = i + 1; cnt = 0;
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

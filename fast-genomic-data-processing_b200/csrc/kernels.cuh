@@ -118,6 +118,7 @@ struct RescueScanArgs {
     DevUnit *rescue_units;
     const uint32_t *rescue_base;
     uint32_t *rescue_count;
+    uint32_t max_pairs;           // underflowed pairs per FP64 unit (>= 1; kMaxUnitHaps = the read's whole row)
 };
 constexpr int kMaxUnitReads = 8;  // reads of one work unit: 2 * 32 / 8 (packed kernel, 8-lane groups)
 
