@@ -42,7 +42,7 @@ template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; 
 
 void Slot::release() {
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
-    h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); h_units.release(); h_out.release(); h_rescue_base.release();
+    h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); d_long_scratch.release(); h_units.release(); h_out.release(); h_rescue_base.release();
     h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
@@ -87,8 +87,8 @@ int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
 // counters layout in d_counters, one word per (K,KL) bin each: work queues of the FP32 launches,
 // rescue counts, work queues of the FP64 launches
 // (zeroed per run), then the device copy of Slot::rescue_base
-constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32;
-constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32;
+constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32, kQueueLong = kNumBins + 2 * kNumBinsW32;
+constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32 + 1;
 constexpr int kRescueBaseDev = kZeroedWords;
 constexpr int kCounterWords = kZeroedWords + kNumBinsW32 + 4;
 
@@ -200,8 +200,6 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || (!rv.raw && (!r.ins_q || !r.del_q || !r.gcp)))))
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
-        if (bin_of_read(r.len, 32) < 0)
-            return fail(h, PAIRHMM_ERR_ARG, "read longer than 384 bases: not supported by this build");
         uint32_t u = kNoRead;
         if (!table.empty()) {
             const uint64_t hv = hash_read(r);
@@ -238,6 +236,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         pl.uniq_of_read[i] = u;
     }
     pl.n_uniq = (uint32_t)pl.uniq_src.size();
+    pl.hmax = hmax;
     // haplotypes per work unit: all of them unless the chunk is too small to fill the GPU
     // (group_hint) or the unit would get very long (tail balance)
     uint32_t g = default_unit_haps(rv.n_haps, hmax);
@@ -267,6 +266,7 @@ void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w) {
     std::vector<uint16_t> bin(n);
     for (uint32_t j = 0; j < n; ++j) {
         const int R = read_ref(rv, pl.uniq_src[j]).len;
+        if (R > kMaxReadLen) { bin[j] = (uint16_t)kLongBin; continue; }      // swept in row stripes by long.cu, one unit per pair
         bin[j] = (uint16_t)bin_of_read(R, choose_width(R, v, forced_w));
         pl.pairs32[bin_of_read(R, 32)] += (uint32_t)rv.n_haps;
     }
@@ -401,16 +401,19 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // prefix sums
     uint64_t rbytes = 0, hbytes = 0, cells = 0, pairs = 0, reads_in = 0, swept = 0;
     uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
-    std::vector<uint32_t> bin_count(kNumBins, 0);
+    std::vector<uint32_t> bin_count(kNumBins + 1, 0);
     uint32_t bin_pairs[kNumBinsW32] = {0};
+    int32_t hap_max = 0;
     for (size_t i = 0; i < n_regs; ++i) {
         RegionPlan &p = s.plans[i];
         p.first_uniq = nu; p.read_byte_off = rbytes; p.first_hap = nh; p.hap_byte_off = hbytes;
         p.hap_word_off = hw; p.hap_list_off = hl; p.upair_off = up;
+        hap_max = std::max(hap_max, p.hmax);
         for (auto &run : p.runs) {
+            run.unit_off = bin_count[run.bin];
+            if (run.bin == kLongBin) { bin_count[kLongBin] += run.n_reads * (uint32_t)s.regions[i].n_haps; continue; }   // one unit per pair
             int W, K, KL; bin_shape(run.bin, W, K, KL);
             const uint32_t per_warp = (uint32_t)reads_per_warp(s.float_variant, W);
-            run.unit_off = bin_count[run.bin];
             bin_count[run.bin] += (run.n_reads + per_warp - 1) / per_warp * p.n_groups;
         }
         for (int k = 0; k < kNumBinsW32; ++k) bin_pairs[k] += p.pairs32[k];
@@ -430,9 +433,10 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     }
     s.bin_start[0] = 0;
     s.rescue_base[0] = 0;
-    for (int k = 0; k < kNumBins; ++k) s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
+    for (int k = 0; k <= kNumBins; ++k) s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
     for (int k = 0; k < kNumBinsW32; ++k) s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
-    const uint32_t n_units = s.bin_start[kNumBins];
+    const uint32_t n_units = s.bin_start[kNumBins + 1];
+    s.hap_max = hap_max;
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
     s.cells = cells; s.pairs = pairs; s.reads_in = reads_in; s.cells_swept = swept;
@@ -486,9 +490,16 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         // work units: per bin run, 32/W consecutive reads per warp, one unit per haplotype group
         const uint32_t nhap = (uint32_t)rv.n_haps;
         for (const auto &run : p.runs) {
+            DevUnit *ud = s.h_units.p + s.bin_start[run.bin] + run.unit_off;
+            if (run.bin == kLongBin) {           // long reads: one unit per (read, haplotype) pair
+                for (uint32_t j = 0; j < run.n_reads; ++j)
+                    for (uint32_t q = 0; q < nhap; ++q)
+                        *ud++ = DevUnit{p.first_uniq + run.first + j, p.hap_list_off + q, unit_shape(1u, 1u, nhap),
+                                        p.upair_off + (run.first + j) * nhap + q};
+                continue;
+            }
             int W, K, KL; bin_shape(run.bin, W, K, KL);
             const uint32_t per_warp = (uint32_t)reads_per_warp(s.float_variant, W);
-            DevUnit *ud = s.h_units.p + s.bin_start[run.bin] + run.unit_off;
             for (uint32_t j = 0; j < run.n_reads; j += per_warp) {
                 const uint32_t nr = std::min(per_warp, run.n_reads - j), first = run.first + j;
                 for (uint32_t g = 0; g < p.n_groups; ++g) {
@@ -522,7 +533,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 // H2D of a packed chunk + haplotype word expansion. Asynchronous on the slot's stream.
 int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
-    const uint32_t n_units = s.bin_start[kNumBins];
+    const uint32_t n_units = s.bin_start[kNumBins + 1];
     uint64_t plane_bytes = s.plane * 5;
     if (s.n_uniq && !s.raw_on) {
         CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * 5, cudaMemcpyHostToDevice, st));
@@ -650,6 +661,24 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
             grid = grid_for(vd, b, cap);
         }
         CU(h, launch_forward(vd, W, K, KL, a, grid, st));
+        h->stats.kernel_launches += 1;
+    }
+    if (const uint32_t n_long = s.bin_start[kNumBins + 1] - s.bin_start[kNumBins]) {
+        // reads longer than 384 bases: row stripes, one warp per pair, float + threshold + double + log10 in one kernel;
+        // it runs after finalize, whose output for these entries (computed from unwritten FP32 sums) it replaces
+        LongArgs l{};
+        l.rd = s.d_rd.p; l.plane = s.plane; l.reads = s.d_reads.p; l.hap_bytes = s.d_hapbytes.p; l.hap_byte_off = s.d_hapoff.p;
+        l.haps = s.d_haps.p; l.hap_list = s.d_haplist.p; l.units = s.d_units.p + s.bin_start[kNumBins]; l.n_units = n_long;
+        l.queue = s.d_counters.p + kQueueLong;
+        l.ph2pr_f = h->d_ph2pr_f; l.mm_f = h->d_mm_f; l.ph2pr_d = h->d_ph2pr_d; l.mm_d = h->d_mm_d;
+        l.log10_init_f = h->log10_init_f; l.log10_init_d = h->log10_init_d;
+        l.out = s.d_out.p; l.flag = s.d_flag.p; l.use_double = all_double ? 1 : 0;
+        const int grid = (int)std::min<uint64_t>((uint64_t)h->sm_count * 4u, ((uint64_t)n_long + 3) / 4);
+        l.scratch_per_warp = ((uint64_t)(s.hap_max + 1) * 3 * sizeof(double) + 255) & ~255ull;
+        cudaError_t e = s.d_long_scratch.reserve((size_t)l.scratch_per_warp * 4u * (size_t)grid);
+        if (e != cudaSuccess) return fail_cuda(h, e, "reserve d_long_scratch");
+        l.scratch = s.d_long_scratch.p;
+        CU(h, launch_forward_long(l, grid, st));
         h->stats.kernel_launches += 1;
     }
     if (s.ep_on && s.n_uniq) {       // fused per-read epilogue on the finished matrix

@@ -57,6 +57,7 @@ struct RegionPlan {
     std::vector<uint32_t> hap_order;     // position in the chunk -> index in the caller's list (empty = identity)
     std::vector<uint2> hap_plan;         // sweep plan per position (kernels.cuh: pfx_plan)
     uint64_t shared_cols = 0;            // haplotype columns not swept again thanks to a checkpoint
+    int32_t hmax = 0;                    // longest haplotype of the region
 };
 
 // Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
@@ -82,6 +83,8 @@ struct Slot {
     DevBuf<uint64_t> d_hapoff;
     DevBuf<uint32_t> d_haplist, d_hapw, d_counters;
     DevBuf<uint2> d_happlan;
+    DevBuf<uint8_t> d_long_scratch;   // stripe hand-over lines of the long-read kernel
+    int32_t hap_max = 0;              // longest haplotype of the chunk
     DevBuf<DevUnit> d_units, d_rescue;
     DevBuf<float> d_fres;
     DevBuf<double> d_out;
@@ -94,7 +97,7 @@ struct Slot {
     uint64_t plane = 0;               // bytes per read plane
     uint32_t n_uniq = 0, n_haps = 0, n_hap_words = 0, n_haplist = 0, n_upairs = 0;
     uint64_t hap_bytes = 0;
-    uint32_t bin_start[kNumBins + 1] = {0};   // units of bin b are [bin_start[b], bin_start[b+1])
+    uint32_t bin_start[kNumBins + 2] = {0};   // units of bin b are [bin_start[b], bin_start[b+1]); bin kLongBin = long reads (long.cu)
     uint32_t rescue_base[kNumBinsW32 + 1] = {0}; // W=32 bin b appends its rescue units at d_rescue + rescue_base[b]
     PinnedBuf<uint32_t> h_rescue_base;        // the same, staged for the device
     Variant float_variant = Variant::F32_GEN; // kernels this chunk was binned for

@@ -119,12 +119,14 @@ __global__ void prep_reads_kernel(const PrepReadsArgs a) {
         const int mapq = a.mapq[r];
         uint8_t *p = a.rd + rr.off;
         __syncthreads();
-        for (int i = threadIdx.x; i < rr.len; i += blockDim.x) sb[i] = p[i];
+        const bool staged = rr.len <= kMaxReadLen;            // longer reads (long.cu) are scanned in place: this kernel never writes the bases
+        if (staged) for (int i = threadIdx.x; i < rr.len; i += blockDim.x) sb[i] = p[i];
         __syncthreads();
+        const uint8_t *bases = staged ? sb : p;
         for (int i = threadIdx.x; i < rr.len; i += blockDim.x) {
             int iq = p[2 * a.plane + i], dq = p[3 * a.plane + i];
             if (a.pcr_on && i < rr.len - 1) {
-                const int q = a.pcr_table[tandem_repeat_length(sb, rr.len, i)];
+                const int q = a.pcr_table[tandem_repeat_length(bases, rr.len, i)];
                 iq = min(iq, q); dq = min(dq, q);
             }
             int bq = min((int)p[a.plane + i], mapq);

@@ -149,6 +149,20 @@ struct PrepReadsArgs {
     uint8_t pcr_table[24];        // getErrorModelAdjustedQual(repeat length 0..20), host libm
 };
 
+// Reads longer than kMaxReadLen (long.cu): one work unit = one (read, haplotype) pair, swept in row stripes by one warp;
+// float pass, threshold, double pass and log10 in one kernel. unit.hap_list = index of the pair's entry in hap_list,
+// unit.out = index of its result.
+struct LongArgs {
+    const uint8_t *rd; uint64_t plane; const DevRead *reads;
+    const uint8_t *hap_bytes; const uint64_t *hap_byte_off; const DevHap *haps; const uint32_t *hap_list;
+    const DevUnit *units; uint32_t n_units; uint32_t *queue;
+    const float *ph2pr_f, *mm_f; const double *ph2pr_d, *mm_d;
+    float log10_init_f; double log10_init_d;
+    uint8_t *scratch; uint64_t scratch_per_warp;   // 3 lines of (longest haplotype) doubles per resident warp
+    double *out; uint8_t *flag;
+    int32_t use_double;
+};
+
 struct FinalizeArgs {
     const float *fres;
     double *out;
@@ -168,6 +182,7 @@ constexpr int tri(int k) { return k * (k + 1) / 2; }
 constexpr int kBinBase[kNumWidths + 1] = {0, tri(12), tri(12) + tri(12), tri(12) + tri(12) + tri(12)};
 constexpr int kNumBins = kBinBase[kNumWidths];           // 78 + 78 + 78 = 234
 constexpr int kNumBinsW32 = kBinBase[1];
+constexpr int kLongBin = kNumBins;                       // pseudo-bin of the reads longer than kMaxReadLen (long.cu)
 
 inline int width_index(int W) { return W == 32 ? 0 : W == 16 ? 1 : W == 8 ? 2 : -1; }
 inline int bin_of(int W, int K, int KL) { return kBinBase[width_index(W)] + K * (K - 1) / 2 + KL; }
@@ -203,6 +218,7 @@ cudaError_t launch_prep_haps(const uint8_t *hap_bytes, const uint64_t *byte_off,
                              uint32_t n_haps, uint32_t *hapw, cudaStream_t st);
 cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
+cudaError_t launch_forward_long(const LongArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
 cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st);
 cudaError_t launch_prep_reads(const PrepReadsArgs &a, int sm_count, cudaStream_t st);

@@ -351,6 +351,40 @@ def snv_family(n_regions=64, n_reads=64, n_haps=12, R=150, H=300, profile="clean
     return b
 
 
+def long_reads(seed=4321, uniform_gcp=True, profile="clean"):
+    """reads longer than one warp's register block (384 rows), mixed with ordinary ones in the same regions: lengths
+    around the stripe boundaries of the long-read kernel (256-row stripes) and well beyond, haplotypes shorter and
+    longer than the reads, N bases. uniform_gcp=False perturbs the gap-continuation bytes (general kernels)."""
+    rng = np.random.default_rng(seed)
+    regions = [([385, 150, 400, 7], [300, 600, 601]), ([512, 513, 384, 511], [700, 90]), ([768, 769, 1025, 33], [1200, 1, 40]),
+               ([2049, 151, 640], [2500, 2100]), ([1000] * 3 + [150] * 6, [1500] * 5)]
+    rb, bq, iq, dq, gc, rl, hb, hl, rrs, rhs = [], [], [], [], [], [], [], [], [0], [0]
+    for Rs, Hs in regions:
+        base = _rand_bases(rng, max(Hs) + max(Rs), 0.002)
+        haps = []
+        for k, h in enumerate(Hs):
+            hh = base[:h].copy()
+            if k and h > 8:
+                hh[int(rng.integers(0, h))] = ACGT[int(rng.integers(0, 4))]
+            haps.append(hh); hb.append(hh); hl.append(h)
+        for r, R in enumerate(Rs):
+            st = int(rng.integers(0, max(1, max(Hs) - R + 1)))
+            b = base[st:st + R].copy()
+            if r % 4 == 3:
+                b = _rand_bases(rng, R)                    # unrelated read: underflows in float -> double pass
+            mut = rng.random(R) < 0.01
+            b[mut] = ACGT[rng.integers(0, 4, size=int(mut.sum()))]
+            q, i_, d_, c_ = _quals(rng, (R,), profile)
+            if not uniform_gcp:
+                c_ = c_.copy(); c_[rng.random(R) < 0.3] = 7
+            rb.append(b); bq.append(q); iq.append(i_); dq.append(d_); gc.append(c_); rl.append(R)
+        rrs.append(rrs[-1] + len(Rs)); rhs.append(rhs[-1] + len(Hs))
+    rl = np.asarray(rl, np.int32); hl = np.asarray(hl, np.int32)
+    return RegionBatch(np.concatenate(rb), np.concatenate(bq), np.concatenate(iq), np.concatenate(dq),
+                       np.concatenate(gc), _offsets(rl), rl, np.concatenate(hb), _offsets(hl), hl,
+                       np.asarray(rrs, np.int64), np.asarray(rhs, np.int64), "long-reads-" + profile + ("" if uniform_gcp else "-gcp"))
+
+
 def edge_cases(seed=1234):
     """ragged edge-case batch: R in {1,2,15,...,255}, H in {1..700} incl. R>H, N bases, lower-case and
     junk bytes (behave as 'A'), quals with the high bit set, per-base gcp != 10, quals 0/6/93/127."""

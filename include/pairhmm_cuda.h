@@ -47,7 +47,7 @@ extern "C" {
 
 typedef enum pairhmm_cuda_status {
     PAIRHMM_OK = 0,
-    PAIRHMM_ERR_ARG = -1,      /* null pointer, negative size, length above the initialised maximum */
+    PAIRHMM_ERR_ARG = -1,      /* null pointer, negative size or count (reads and haplotypes may have any length) */
     PAIRHMM_ERR_CUDA = -2,     /* a CUDA runtime call failed (text in last_error)                    */
     PAIRHMM_ERR_NO_DEVICE = -3,/* no usable sm_100 device: the engine has NO CPU fallback            */
     PAIRHMM_ERR_OOM = -4,      /* host or device allocation failed                                   */

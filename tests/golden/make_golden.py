@@ -63,7 +63,19 @@ def main():
         "c3_small": synth.config3(48, 6),
         "c4_small": synth.config4(2, 6, 3),
         "c2_small": synth.config2(3),
+        "long_reads": synth.long_reads(),                    # reads of 385..2049 bases (row stripes in the reference too)
+        "long_reads_gcp": synth.long_reads(uniform_gcp=False, profile="lowq"),
     }
+    only = [a for a in sys.argv[1:] if a in cases]
+    if only:                                                 # python make_golden.py long_reads ...: just these fixtures
+        for name in only:
+            b = cases[name]
+            out, resc, _ = ref.compute(b.as_flat(), threads=8)
+            out_d, _, _ = ref.compute(b.as_flat(), use_double=True, threads=8)
+            np.savez_compressed(os.path.join(HERE, name + ".npz"), log10=out, rescued=resc, log10_use_double=out_d,
+                                meta=np.array(meta), **{f: getattr(b, f) for f in FIELDS})
+            print(name, b.n_pairs, "pairs, rescued", int(resc.sum()))
+        return
     for name, b in cases.items():
         out, resc, _ = ref.compute(b.as_flat(), threads=8)
         out_d, _, _ = ref.compute(b.as_flat(), use_double=True, threads=8)

@@ -209,8 +209,10 @@ def test_empty_and_errors(engine):
     with pytest.raises(fgdp_b200.PairHMMError):
         engine.initialize(10, 0)
     r = tuple(np.full(385, v, np.uint8) for v in (65, 30, 45, 45, 10))
+    out, resc = engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 384 rows: the row-striped kernel
+    assert np.isfinite(out).all()
     with pytest.raises(fgdp_b200.PairHMMError):
-        engine.compute([r], [np.frombuffer(b"ACGT", np.uint8)])   # > 384 rows: refused loudly, not faked
+        engine.initialize(0, 10)
     z = tuple(np.zeros(0, np.uint8) for _ in range(5))
     out, resc = engine.compute([z], [np.frombuffer(b"ACGT", np.uint8)])
     assert np.isneginf(out).all() and resc.all()
@@ -340,7 +342,7 @@ def _repeat_rich_batch(seed=5):
 def test_device_read_prepass_equals_oracle(engine, oracle, with_indel, pcr):
     """prep_reads_kernel (applyPCRErrorModel + capMinimumReadQualities + constant gcp on the device) against the oracle's
     restatement of PairHMMLikelihoodCalculationEngine.cpp:123-267: every byte equal"""
-    for b in (_repeat_rich_batch(), synth.config2(2)):
+    for b in (_repeat_rich_batch(), synth.config2(2), synth.long_reads()):
         bq, mapq, iq, dq = _raw_quals(b, 11 + pcr, with_indel)
         model = fgdp_b200.pairhmm.ReadModel(pcr, 18, 10)
         got = engine.prepare_reads(b, bq, mapq, iq, dq, model)
@@ -353,7 +355,7 @@ def test_device_read_prepass_equals_oracle(engine, oracle, with_indel, pcr):
 def test_raw_read_entry_point_equals_prepared_reads(engine, oracle, with_indel):
     """pairhmm_cuda_compute_flat_raw = device pre-pass + PairHMM: identical to feeding the oracle-prepared qualities to the
     plain entry point, and within the parity bar of the CPU oracle on them"""
-    for b in (_repeat_rich_batch(), synth.config2(3)):
+    for b in (_repeat_rich_batch(), synth.config2(3), synth.long_reads()):
         bq, mapq, iq, dq = _raw_quals(b, 3, with_indel)
         got, gresc = engine.compute_batch_raw(b, bq, mapq, iq, dq)
         pb, pi, pd, pg = oracle.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq)
@@ -407,3 +409,41 @@ def test_handles_on_concurrent_host_threads(oracle):
     assert not errors, errors
     for k in range(4):
         assert_parity(results[k][0], results[k][1], wants[k][0], wants[k][1], what="thread %d" % k)
+
+
+def test_long_reads_row_stripes(oracle):
+    """reads above 384 bases go through the row-striped kernel (long.cu), alone and mixed with ordinary reads, under every
+    engine mode; the per-region call and the batch call agree"""
+    for b in (synth.long_reads(), synth.long_reads(uniform_gcp=False, profile="lowq"), synth.long_reads(seed=99, profile="lowq")):
+        want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+        assert 0 < wresc.sum() < wresc.size
+        for kw in ({}, {"prefix_sharing": 2, "unit_haps": 32}, {"force_general": True}, {"exact_fp32": True}, {"dedup_reads": False}):
+            e = fgdp_b200.Engine(**kw)
+            try:
+                got, gresc = e.compute_batch(b)
+                assert_parity(got, gresc, want, wresc, what="%s %s" % (b.name, kw))
+                e.resident_load(b); e.resident_run()
+                got2, gresc2 = e.resident_fetch()
+                assert np.array_equal(got, got2) and np.array_equal(gresc, gresc2)
+            finally:
+                e.close()
+        e = fgdp_b200.Engine(use_double=True)
+        try:
+            got_d, resc_d = e.compute_batch(b)
+        finally:
+            e.close()
+        want_d = oracle.compute(b.as_flat(), threads=4, use_double=True)[0]
+        fin = np.isfinite(want_d)
+        assert resc_d.all() and np.array_equal(np.isfinite(got_d), fin) and np.abs(got_d[fin] - want_d[fin]).max() < 1e-9
+    # one region through pairhmm_cuda_compute
+    b = synth.long_reads()
+    e = fgdp_b200.Engine()
+    try:
+        off = b.region_out_offsets()
+        want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+        for g in range(b.n_regions):
+            reads, haps = _region_lists(b, g)
+            got, gresc = e.compute(reads, haps)
+            assert_parity(got, gresc, want[off[g]:off[g + 1]], wresc[off[g]:off[g + 1]], what="long region %d" % g)
+    finally:
+        e.close()

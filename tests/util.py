@@ -27,4 +27,4 @@ def load_golden(name):
     return b, z["log10"], z["rescued"], z["log10_use_double"]
 
 
-GOLDEN = ["c1_clean", "c1_lowq", "edge", "c3_small", "c4_small", "c2_small"]
+GOLDEN = ["c1_clean", "c1_lowq", "edge", "c3_small", "c4_small", "c2_small", "long_reads", "long_reads_gcp"]
