@@ -143,10 +143,10 @@ inline ReadRef read_ref(const RegionView &rv, size_t i) {
 }
 uint64_t hash_read(const ReadRef &r) {
     uint64_t h = 0x243f6a8885a308d3ull ^ (uint64_t)r.len ^ ((uint64_t)(uint32_t)r.mapq << 32);
+    // bases and base qualities only: two reads that agree in both and differ in their indel / gap-continuation qualities
+    // are rare (Mutect2Cpp derives those from the bases, PHLCE.cpp:123-157,284-292), and same_read() compares all five
+    // arrays anyway -- hashing 2 arrays instead of 5 halves the plan phase of the packer
     h = hash_bytes(r.bases, r.len, h); h = hash_bytes(r.base_q, r.len, h);
-    if (r.ins_q) h = hash_bytes(r.ins_q, r.len, h);
-    if (r.del_q) h = hash_bytes(r.del_q, r.len, h);
-    if (r.gcp) h = hash_bytes(r.gcp, r.len, h);
     return h;
 }
 inline bool same_plane(const uint8_t *a, const uint8_t *b, int32_t n) { return (!a || !b) ? a == b || (!a && !b) : !std::memcmp(a, b, n); }
@@ -199,6 +199,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         const ReadRef r = read_ref(rv, (size_t)i);
         if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || (!rv.raw && (!r.ins_q || !r.del_q || !r.gcp)))))
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
+        pl.read_len_sum += (uint64_t)r.len;
         if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
         uint32_t u = kNoRead;
         if (!table.empty()) {
@@ -424,9 +425,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             return fail(h, PAIRHMM_ERR_ARG, "chunk too large for 32-bit device indices (lower chunk_cells)");
         nu += p.n_uniq; rbytes += p.read_bytes; nh += (uint32_t)s.regions[i].n_haps; hbytes += p.hap_bytes;
         hw += p.hap_words; hl += (uint32_t)s.regions[i].n_haps; up = (uint32_t)up_next;
-        uint64_t rl = 0;
-        for (int r = 0; r < s.regions[i].n_reads; ++r) rl += (uint64_t)read_ref(s.regions[i], (size_t)r).len;
-        cells += rl * p.hap_bytes;
+        cells += p.read_len_sum * p.hap_bytes;
         swept += p.read_bytes * (p.hap_bytes - p.shared_cols);
         pairs += (uint64_t)s.regions[i].n_reads * (uint64_t)s.regions[i].n_haps;
         reads_in += (uint64_t)s.regions[i].n_reads;
@@ -437,6 +436,10 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     for (int k = 0; k < kNumBinsW32; ++k) s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
     const uint32_t n_units = s.bin_start[kNumBins + 1];
     s.hap_max = hap_max;
+    // the packed FP32 kernels and the wide FP64 kernel take the (uniform) gap-continuation penalty as a launch constant and
+    // never read the gcp plane: it is neither staged nor sent (a fifth of the read bytes). The long-read kernel reads it.
+    s.skip_gcp = is_packed_f32(s.float_variant) && s.bin_start[kNumBins + 1] == s.bin_start[kNumBins] &&
+                 !(n_regs > 0 && s.regions[0].raw != nullptr);
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
     s.cells = cells; s.pairs = pairs; s.reads_in = reads_in; s.cells_swept = swept;
@@ -474,7 +477,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             std::memcpy(d, r.bases, r.len); std::memcpy(d + s.plane, r.base_q, r.len);
             if (!s.raw_on) {
                 std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
-                std::memcpy(d + 4 * s.plane, r.gcp, r.len);
+                if (!s.skip_gcp) std::memcpy(d + 4 * s.plane, r.gcp, r.len);
             } else {
                 // planes 2-4 are filled on the device unless some read of the chunk has its own indel qualities
                 if (s.raw_indel_q) {
@@ -534,9 +537,9 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
     const uint32_t n_units = s.bin_start[kNumBins + 1];
-    uint64_t plane_bytes = s.plane * 5;
+    uint64_t plane_bytes = s.plane * (s.skip_gcp ? 4 : 5);
     if (s.n_uniq && !s.raw_on) {
-        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * 5, cudaMemcpyHostToDevice, st));
+        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, plane_bytes, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
     }
     if (s.n_uniq && s.raw_on) {

@@ -39,6 +39,7 @@ struct RegionPlan {
     uint32_t n_uniq = 0;            // unique reads with len > 0
     uint32_t first_uniq = 0;        // global unique-read id of this region's first unique read
     uint64_t read_bytes = 0, read_byte_off = 0;
+    uint64_t read_len_sum = 0;      // bases of every input read (duplicates included): the region's DP cells = this x hap_bytes
     uint32_t first_hap = 0;         // global hap id
     uint64_t hap_bytes = 0, hap_byte_off = 0;
     uint32_t hap_words = 0, hap_word_off = 0;
@@ -103,6 +104,7 @@ struct Slot {
     Variant float_variant = Variant::F32_GEN; // kernels this chunk was binned for
     bool uniform_gcp = false;                 // every gcp byte of the chunk equals gcp_value -> UG kernels
     uint8_t gcp_value = 0;
+    bool skip_gcp = false;                    // the chunk's kernels never read the gcp plane: not staged, not sent
     uint64_t cells = 0, pairs = 0, reads_in = 0;
     uint64_t cells_swept = 0;         // DP cells the FP32 pass sweeps: unique reads x haplotype columns not shared
     bool busy = false;
