@@ -43,12 +43,13 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--regions", type=int, default=0, help="c2: regions per rank (default 10000 = BASELINE configs[1]); "
                                                             "c5: regions of the whole job (default 25000 = configs[4])")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c5", "snv"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5", "snv", "c1", "c3", "c4"],
                     help="c2 = BASELINE configs[1] per GPU (weak scaling, the metric's config); c5 = configs[4], the "
                          "whole-box chr20-scale batch LPT-sharded over the ranks (strong scaling); snv = the workload of "
                          "the reference's trie path (same-length haplotypes that differ by SNVs), engine with prefix "
                          "sharing on: value / e2e are EFFECTIVE GCUPS (R x H of every pair), the roofline counts only "
-                         "the cells actually swept (SURVEY.md 8f N4)")
+                         "the cells actually swept (SURVEY.md 8f N4); c1 / c3 / c4 = BASELINE configs[0] / [2] / [3] (one region; "
+                         "one rescue-heavy region; long haplotypes), every rank the same batch")
     ap.add_argument("--cpu-sample-regions", type=int, default=0, help="regions in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -209,6 +210,12 @@ def main():
         batch = synth.config5(args.regions, select=synth.lpt_shard(cost, world)[rank] if world > 1 else None)
         workload = ("BASELINE configs[4]: chr20-scale synthetic batch, %d regions x 200 reads x 10 haps, 150 bp reads, "
                     "300-500 bp haps, whole job LPT-sharded over %d GPU(s)" % (args.regions, world))
+    elif args.workload in ("c1", "c3", "c4"):
+        batch = {"c1": synth.config1, "c3": synth.config3, "c4": synth.config4}[args.workload]()
+        args.regions = batch.n_regions
+        workload = {"c1": "BASELINE configs[0]: one active region, 64 reads x 8 haplotypes, 150 bp reads, 300 bp haps (launch-bound: one step = one region)",
+                    "c3": "BASELINE configs[2]: high-depth region, 2000 reads x 32 haplotypes, 150 bp reads, ~600 bp haps, low qualities (rescue-heavy)",
+                    "c4": "BASELINE configs[3]: 64 regions x 128 reads x 8 haplotypes, 250 bp reads, 1-2 kb haplotypes of mixed lengths"}[args.workload]
     elif args.workload == "snv":
         batch = synth.snv_family(args.regions, 200, 12, 150, 300, dup_frac=0.0, seed_extra=rank)
         workload = ("SNV family (the reference's trie workload, VectorLoglessPairHMM.cpp:35): %d regions x 200 reads x 12 "
@@ -330,13 +337,15 @@ def main():
                   "rescue_set_pairs_checked": int(n_g), "against": cpu["kind"]}
         cpu["value_tables_prebuilt"] = cpu["cells"] / secs_pre / 1e9
         cpu = {k: cpu[k] for k in ("value", "value_tables_prebuilt", "unit", "cores", "kind", "isa", "sample")}
+    in_bytes = batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4
     line = {"metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.workload == "c5" else "weak",
             "vs_baseline": None,
             "dtype": "f32+f64-rescue", "data": "synthetic",
             "config": {"workload": workload, "pairs_per_gpu": pairs, "cells_per_gpu": cells, "rescued_frac": float(resc.mean()),
-                       "l2": "inputs (%.2f GB of read planes + haplotype words per GPU) exceed the 126 MB L2" %
-                             ((batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4) / 1e9),
+                       "l2": ("inputs (%.3f GB of read planes + haplotype words per GPU) exceed the 126 MB L2" if in_bytes > 126e6 else
+                              "inputs (%.3f GB) fit the 126 MB L2 and are not flushed between steps: the path is FMA-pipe-bound at "
+                              "~0.002 B per cell (roofline.algorithmic_hbm_GBps), L2 residency does not change the step time") % (in_bytes / 1e9),
                        "parallelism": "%d rank(s), regions LPT-sharded by DP cells, no collective on the data path" % world},
             "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"] // args.steps,
                     "d2h_bytes_per_step": st["d2h_bytes"] // args.steps, "ms_per_step": e2e_s * 1e3,
