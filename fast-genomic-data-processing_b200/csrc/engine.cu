@@ -166,11 +166,18 @@ uint8_t pcr_adjusted_qual(int repeat_length, int rate_factor) {
 }
 
 // haplotypes per work unit of a region when the batch is large enough to fill the GPU
+// runs of (nearly) equal length: the same number of units as runs of at most g haplotypes, without a short last one
+// (a region of 32 haplotypes cut at 5 would give 6 units of 5 and one of 2: the warps that draw the short ones idle)
+uint32_t balanced_unit_haps(int n_haps, uint32_t g) {
+    if (n_haps <= 0 || g == 0) return std::max(1u, g);
+    const uint32_t n = (uint32_t)n_haps, units = (n + g - 1) / g;
+    return (n + units - 1) / units;
+}
 uint32_t default_unit_haps(int n_haps, int32_t hmax) {
     uint32_t g = (uint32_t)std::max(1, n_haps);
     const uint32_t cap_cols = 16384u / (uint32_t)(hmax + 1);
     g = std::min(g, std::max(1u, cap_cols));
-    return std::min(g, (uint32_t)kMaxUnitHaps);
+    return balanced_unit_haps(n_haps, std::min(g, (uint32_t)kMaxUnitHaps));
 }
 
 // Pass A for one region: read de-duplication (VectorLoglessPairHMM.cpp:83-103) and sizes.
@@ -243,6 +250,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     uint32_t g = default_unit_haps(rv.n_haps, hmax);
     if (group_hint) g = std::min(g, group_hint);
     if (h->cfg.reserved[5] > 0) g = (uint32_t)std::min<int>(std::min(h->cfg.reserved[5], (int)kMaxUnitHaps), std::max(1, rv.n_haps));
+    g = balanced_unit_haps(rv.n_haps, g);
     pl.group = g;
     pl.n_groups = rv.n_haps ? ((uint32_t)rv.n_haps + g - 1) / g : 0;
     return PAIRHMM_OK;
@@ -356,13 +364,28 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // group hint: if there are few reads, split haplotype runs so that every warp slot gets work
     uint64_t total_reads = 0;
     for (size_t i = 0; i < n_regs; ++i) total_reads += (uint64_t)std::max(0, regs[i].n_reads);
-    const uint64_t want_units = (uint64_t)h->sm_count * 24u * 3u;
+    // the packed kernels keep 8 warps per SM resident (2 CTAs of 4 warps): aim at three waves of warp units. Counted in
+    // warps, not reads -- a warp takes 2-8 reads (tools/unit_sweep.py: C3 2699 -> 3162, C4 2954 -> 3093 GCUPS in the FP32
+    // pass against the former reads-based rule, which cut the runs of mid-sized chunks too short or raggedly)
+    const uint64_t want_units = (uint64_t)h->sm_count * 8u * 3u;
     uint32_t group_hint = 0;
-    if (total_reads && total_reads < want_units) {
-        uint64_t splits = (want_units + total_reads - 1) / total_reads;      // units wanted per read
-        uint32_t maxh = 1;
-        for (size_t i = 0; i < n_regs; ++i) maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
-        group_hint = (uint32_t)std::max<uint64_t>(1, maxh / std::min<uint64_t>(splits, maxh));
+    if (total_reads && total_reads < want_units * 8u) {
+        double warps = 0.0;
+        const int forced = h->cfg.reserved[1];
+        for (size_t i = 0; i < n_regs; ++i) {
+            if (regs[i].n_reads <= 0 || (!regs[i].reads && !regs[i].raw)) continue;
+            for (int r = 0; r < regs[i].n_reads; ++r) {
+                const int len = read_ref(regs[i], (size_t)r).len;
+                if (len < 1 || len > kMaxReadLen) continue;
+                warps += 1.0 / (double)reads_per_warp(Variant::F32_PK, choose_width(len, Variant::F32_PK, forced));
+            }
+        }
+        if (warps >= 1.0 && warps < (double)want_units) {
+            const uint64_t splits = (uint64_t)std::ceil((double)want_units / warps);   // units wanted per warp of reads
+            uint32_t maxh = 1;
+            for (size_t i = 0; i < n_regs; ++i) maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
+            group_hint = (uint32_t)std::max<uint64_t>(1, maxh / std::min<uint64_t>(splits, maxh));
+        }
     }
     std::atomic<int> status{PAIRHMM_OK};
     parallel_for(n_regs, threads, 8, [&](size_t i) {

@@ -93,7 +93,7 @@ typedef struct pairhmm_cuda_config {
                              /* [1] = 8|16|32: force that lane-group width where it fits (tuning)    */
                              /* [2] != 0: scalar instead of packed (FFMA2) uniform-gcp kernels (testing) */
                              /* [3] > 0: at most that many resident CTAs per SM (tuning)              */
-                             /* [5] > 0: haplotypes per work unit (tuning; default: all of a region's, fewer */
+                             /* [5] > 0: at most that many haplotypes per work unit (tuning; default: all of a region's, fewer */
                              /*     when the batch is too small to fill the GPU otherwise)                  */
                              /* [4] != 0: prefix sharing -- same-length haplotypes of a region that share  */
                              /*     a prefix are swept from a checkpoint (the reference's trie,            */

@@ -29,7 +29,12 @@ def _replay(haps, unit_haps):
     lens = [len(haps[i]) for i in p["order"]]
     assert lens == sorted(lens), "sweep order is by length first"
     hmax = max([len(h) for h in haps] + [0])
-    group = min(unit_haps, 32) if unit_haps > 0 else min(max(1, n), max(1, 16384 // (hmax + 1)), 32)   # default_unit_haps (engine.cu)
+    if unit_haps > 0:
+        group = min(unit_haps, 32)
+    else:                                         # default_unit_haps (engine.cu): runs of equal length
+        g0 = min(max(1, n), max(1, 16384 // (hmax + 1)), 32)
+        units = (max(1, n) + g0 - 1) // g0
+        group = (max(1, n) + units - 1) // units
     slots = {}
     swept = shared = 0
     for q in range(n):
