@@ -87,8 +87,9 @@ int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
 // counters layout in d_counters, one word per (K,KL) bin each: work queues of the FP32 launches,
 // rescue counts, work queues of the FP64 launches
 // (zeroed per run), then the device copy of Slot::rescue_base
-constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32, kQueueLong = kNumBins + 2 * kNumBinsW32;
-constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32 + 1;
+constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32, kQueueLong = kNumBins + 2 * kNumBinsW32,
+              kRescuedPairs = kNumBins + 2 * kNumBinsW32 + 1;
+constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32 + 2;
 constexpr int kRescueBaseDev = kZeroedWords;
 constexpr int kCounterWords = kZeroedWords + kNumBinsW32 + 4;
 
@@ -655,14 +656,14 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
             h->stats.kernel_launches += 1;
         }
         CU(h, cudaEventRecord(s.ev_fwd_done, st));
-        FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f};
+        FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f, s.d_counters.p + kRescuedPairs};
         CU(h, launch_finalize(f, st));
         if (s.n_upairs) h->stats.kernel_launches += 1;
         RescueScanArgs r{s.d_units.p, s.bin_start[kNumBins], s.d_reads.p, s.d_fres.p, s.d_rescue.p,
                          s.d_counters.p + kRescueBaseDev, s.d_counters.p + kRescueCount,
-                         // few reads (a region per call): one FP64 unit per underflowed pair, the pass is as short as one
-                         // sweep; many reads: the read's whole row in one unit (one pipeline fill per read)
-                         s.n_uniq <= 4096u ? 1u : s.n_uniq <= 16384u ? 2u : (uint32_t)kMaxUnitHaps};
+                         // 0 = chosen on the device from the number of underflowed pairs finalize_kernel counted
+                         h->cfg.reserved[6] > 0 ? (uint32_t)h->cfg.reserved[6] : 0u, s.d_counters.p + kRescuedPairs,
+                         (uint32_t)h->sm_count * 12u};
         CU(h, launch_rescue_scan(r, st));
         if (r.n_units) h->stats.kernel_launches += 1;
     }

@@ -33,9 +33,11 @@ __global__ void prep_haps_kernel(const uint8_t *__restrict__ hap_bytes, const ui
 // FP32 results -> log10 (IntelPairHmm.cc:348): the subtraction happens in float.
 __global__ void finalize_kernel(const FinalizeArgs a) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.n) return;
-    const float f = a.fres[i];
-    if (f < 1e-28f) return;                           // the FP64 kernel owns this entry
+    const float f = i < a.n ? a.fres[i] : 1.0f;
+    const bool resc = f < 1e-28f;                      // the FP64 kernel owns this entry (IntelPairHmm.cc:342)
+    const uint32_t m = __ballot_sync(0xffffffffu, resc);
+    if (m && (threadIdx.x & 31) == 0) atomicAdd(a.rescued_pairs, (uint32_t)__popc(m));
+    if (i >= a.n || resc) return;
     const float l = (float)log10((double)f);          // correctly rounded float log10
     a.out[i] = (double)__fsub_rn(l, a.log10_init_f);
     a.flag[i] = 0;
@@ -57,10 +59,15 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     // a run of the read's haplotypes with at most max_pairs underflowed ones becomes one FP64 unit: the whole row in a big
     // chunk (one pipeline fill per read), single pairs in a small one (one region per call: the FP64 pass is as long as
     // its longest unit, and a sweep of one 150 x 400 pair alone takes ~25 us)
+    // few underflowed pairs in the chunk: single pairs, so that the FP64 launch is as short as one sweep and its warps are
+    // all busy; many: runs of pairs, up to the read's whole row (one pipeline fill per unit) -- about four units per
+    // resident warp of the FP64 kernel
+    const uint32_t max_pairs = a.max_pairs ? a.max_pairs
+                               : min((uint32_t)kMaxUnitHaps, max(1u, *a.rescued_pairs / (4u * a.fp64_warp_slots)));
     uint32_t first = 0, cnt = 0;
     for (uint32_t i = 0; i < nh; ++i) {
         cnt += a.fres[out + i] < 1e-28f ? 1u : 0u;
-        if (cnt && (cnt == a.max_pairs || i + 1 == nh)) {
+        if (cnt && (cnt == max_pairs || i + 1 == nh)) {
             const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
             a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list + first, unit_shape(i + 1 - first, 1u, 0u), out + first};
             first = i + 1; cnt = 0;

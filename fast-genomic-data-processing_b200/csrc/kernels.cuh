@@ -118,7 +118,10 @@ struct RescueScanArgs {
     DevUnit *rescue_units;
     const uint32_t *rescue_base;
     uint32_t *rescue_count;
-    uint32_t max_pairs;           // underflowed pairs per FP64 unit (>= 1; kMaxUnitHaps = the read's whole row)
+    uint32_t max_pairs;           // underflowed pairs per FP64 unit (>= 1; kMaxUnitHaps = the read's whole row); 0 = chosen
+                                  // on the device from the chunk's number of underflowed pairs:
+    const uint32_t *rescued_pairs;  //   counted by finalize_kernel
+    uint32_t fp64_warp_slots;     //   warps of the FP64 kernel resident on the device
 };
 constexpr int kMaxUnitReads = 8;  // reads of one work unit: 2 * 32 / 8 (packed kernel, 8-lane groups)
 
@@ -169,6 +172,7 @@ struct FinalizeArgs {
     uint8_t *flag;
     uint32_t n;
     float log10_init_f;           // log10f(2^120), host libm (Context.h:184)
+    uint32_t *rescued_pairs;      // += pairs left to the FP64 pass (one atomic per warp); read by the rescue scan
 };
 
 // Work bins. A read of length R is swept by a group of W lanes (W = 32, 16 or 8; 32/W reads per warp),

@@ -188,7 +188,7 @@ class Engine:
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
                  chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0,
-                 prefix_sharing=False, unit_haps=0):
+                 prefix_sharing=False, unit_haps=0, rescue_pairs_per_unit=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
@@ -202,6 +202,7 @@ class Engine:
         # 2 = always (testing)
         cfg.reserved[4] = int(prefix_sharing)
         cfg.reserved[5] = int(unit_haps)       # haplotypes per work unit (tuning / testing)
+        cfg.reserved[6] = int(rescue_pairs_per_unit)   # underflowed pairs per FP64 unit (tuning; 0 = by chunk size)
         self.h = C.c_void_p()
         st = self.lib.pairhmm_cuda_create(C.byref(cfg), C.byref(self.h))
         if st != 0:
