@@ -30,14 +30,15 @@ __device__ T long_sweep(const LongArgs &a, const DevRead rr, const uint8_t *__re
     for (int s = 0; s < n_stripes; ++s) {
         // ---- per-row constants of this lane's rows (ReadForPairHMM.cpp:72-80; stripeINITIALIZATION template.h:150-152)
         T pMM[kLongRows], pMX[kLongRows], pMY[kLongRows], pXY[kLongRows], pG[kLongRows], d1[kLongRows], d3[kLongRows];
-        uint32_t rb[kLongRows];
+        uint32_t mm[kLongRows];                                                     // bit b: the row matches haplotype base b (A C T G N)
 #pragma unroll
         for (int k = 0; k < kLongRows; ++k) {
             const int g = s * kStripe + lane * kLongRows + k;                       // 0-based read row
-            pMM[k] = pMX[k] = pMY[k] = pXY[k] = pG[k] = d1[k] = d3[k] = (T)0; rb[k] = 5u;   // dead slot below the read
+            pMM[k] = pMX[k] = pMY[k] = pXY[k] = pG[k] = d1[k] = d3[k] = (T)0; mm[k] = 0u;   // dead slot below the read: e = d3 = 0
             if (g < R) {
                 const uint8_t *p = a.rd + rr.off + g;
-                rb[k] = base_index(p[0]);
+                const uint32_t rb = base_index(p[0]);
+                mm[k] = rb == 4u ? 0x1fu : ((1u << rb) | 0x10u);                    // N on either side matches (template.h:38,48-51)
                 const int bq = p[a.plane] & 127, iq = p[2 * a.plane] & 127, dq = p[3 * a.plane] & 127, cq = p[4 * a.plane] & 127;
                 const int mx = max(iq, dq), mn = min(iq, dq);
                 pMM[k] = mmt[((mx * (mx + 1)) >> 1) + mn];
@@ -65,7 +66,7 @@ __device__ T long_sweep(const LongArgs &a, const DevRead rr, const uint8_t *__re
                 for (int k = 0; k < kLongRows; ++k) {
                     const T aM = k ? M[k - 1] : dgM, aX = k ? X[k - 1] : dgX, aY = k ? Y[k - 1] : dgY;   // (r-1, c-1)
                     const T uM = k ? Mn[k - 1] : upM, uX = k ? Xn[k - 1] : upX;                           // (r-1, c)
-                    const T e = rb[k] == 5u ? (T)0 : ((rb[k] == hb || rb[k] == 4u || hb == 4u) ? d1[k] : d3[k]);
+                    const T e = ((mm[k] >> hb) & 1u) ? d1[k] : d3[k];
                     const T sm = N::template mad<false>(aY, pG[k], N::template mad<false>(aX, pG[k], aM * pMM[k]));
                     Mn[k] = sm * e;
                     Xn[k] = N::template mad<false>(uX, pXY[k], uM * pMX[k]);
