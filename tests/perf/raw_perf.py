@@ -1,8 +1,8 @@
 """Development helper: end-to-end time of the raw-read entry point (quality pre-pass on the device, 2 bytes per base over
 PCIe) against the plain one (5 bytes per base, qualities prepared on the host beforehand), same reads."""
 import sys, os, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "oracle"))
 import numpy as np
 import fgdp_b200
 from fgdp_b200 import synth

@@ -1,7 +1,7 @@
 """Development helper: throughput of the batched CUDA Smith-Waterman against the reference's own aligner on the host
 cores (oracle/_ref/libref_sw.so), on read-vs-haplotype pairs like the post-PairHMM realignment (150 bp x ~400 bp)."""
 import sys, os, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import numpy as np
 import oracle_py
