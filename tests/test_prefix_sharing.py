@@ -185,6 +185,36 @@ def test_prefix_sharing_against_the_oracle_through_the_region_call(oracle):
 
 
 @pytest.mark.gpu
+def test_prefix_sharing_across_many_chunks_and_mixed_batches(oracle):
+    """a batch cut into many launch groups (chunk_cells), SNV families and indel-only regions interleaved: the choice is made
+    per launch group, the results do not depend on it"""
+    a, c = synth.snv_family(10, 40, 12, 150, 300), synth.config2(10)
+    parts = []
+    for g in range(10):
+        parts += [a.subset([g]), c.subset([g])]
+    cat = lambda f: np.concatenate([getattr(p, f) for p in parts])
+    b = synth.RegionBatch(cat("read_bases"), cat("base_q"), cat("ins_q"), cat("del_q"), cat("gcp"), None, cat("read_len"),
+                          cat("hap_bases"), None, cat("hap_len"),
+                          np.concatenate([[0], np.cumsum([p.n_reads for p in parts])]).astype(np.int64),
+                          np.concatenate([[0], np.cumsum([p.n_haps for p in parts])]).astype(np.int64), "mixed")
+    b.read_off = synth._offsets(b.read_len); b.hap_off = synth._offsets(b.hap_len)
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=4)
+    outs = []
+    for kw in ({}, {"prefix_sharing": True, "unit_haps": 32, "chunk_cells": 150_000_000}, {"prefix_sharing": 2, "unit_haps": 32, "chunk_cells": 400_000_000}):
+        e = fgdp_b200.Engine(**kw)
+        try:
+            got, gresc = e.compute_batch(b)
+            st = e.stats()
+        finally:
+            e.close()
+        assert_parity(got, gresc, want, wresc, what="mixed %s" % kw)
+        outs.append((got, gresc, st))
+    for got, gresc, _ in outs[1:]:
+        assert np.array_equal(got.view(np.uint64), outs[0][0].view(np.uint64)) and np.array_equal(gresc, outs[0][1])
+    assert outs[1][2]["cells_swept"] < outs[0][2]["cells_swept"] and outs[2][2]["cells_swept"] <= outs[1][2]["cells_swept"]
+
+
+@pytest.mark.gpu
 def test_prefix_sharing_is_taken_only_where_it_pays():
     """prefix_sharing=True (config.reserved[4] == 1): a batch whose haplotypes all differ in length is swept by the plain
     packed kernel, an SNV family by the sharing one"""
