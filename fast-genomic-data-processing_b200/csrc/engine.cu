@@ -381,7 +381,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
                 warps += 1.0 / (double)reads_per_warp(Variant::F32_PK, choose_width(len, Variant::F32_PK, forced));
             }
         }
-        if (warps >= 1.0 && warps < (double)want_units) {
+        if (warps > 0.0 && warps < (double)want_units) {
             const uint64_t splits = (uint64_t)std::ceil((double)want_units / warps);   // units wanted per warp of reads
             uint32_t maxh = 1;
             for (size_t i = 0; i < n_regs; ++i) maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
