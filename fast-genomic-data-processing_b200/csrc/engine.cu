@@ -27,7 +27,7 @@ template <class T> cudaError_t PinnedBuf<T>::reserve(size_t n) {
     p = q; cap = want;
     return cudaSuccess;
 }
-template <class T> void PinnedBuf<T>::release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+template <class T> void PinnedBuf<T>::release() { if (p && !view) cudaFreeHost(p); p = nullptr; cap = 0; view = false; }
 template <class T> cudaError_t DevBuf<T>::reserve(size_t n) {
     if (n <= cap) return cudaSuccess;
     size_t want = std::max<size_t>(n + n / 4, 1024);
@@ -38,9 +38,10 @@ template <class T> cudaError_t DevBuf<T>::reserve(size_t n) {
     p = q; cap = want;
     return cudaSuccess;
 }
-template <class T> void DevBuf<T>::release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+template <class T> void DevBuf<T>::release() { if (p && !view) cudaFree(p); p = nullptr; cap = 0; view = false; }
 
 void Slot::release() {
+    h_meta.release(); d_meta.release();
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
     h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); d_long_scratch.release(); h_units.release(); h_out.release(); h_rescue_base.release();
     h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
@@ -470,12 +471,28 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 
     cudaError_t e;
 #define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
-    RES(h_rd, s.plane * 5 + 16); RES(h_reads, nu + 1); RES(h_hapbytes, hbytes + 16); RES(h_hapoff, nh + 1);
-    RES(h_haps, nh + 1); RES(h_haplist, hl + 1); RES(h_units, n_units + 1); RES(h_out, up + 1); RES(h_flag, up + 1);
+    RES(h_rd, s.plane * 5 + 16); RES(h_out, up + 1); RES(h_flag, up + 1);
     RES(h_rescue_base, kNumBinsW32 + 1);
+    {   // one arena for everything small that goes to the device, same layout on both sides (256-byte aligned parts)
+        const bool pfx = s.float_variant == Variant::F32_PFX;
+        uint64_t off = 0;
+        auto part = [&](uint64_t bytes) { const uint64_t o = off; off = (off + bytes + 255) & ~255ull; return o; };
+        const uint64_t o_reads = part(sizeof(DevRead) * ((uint64_t)nu + 1)), o_hapoff = part(sizeof(uint64_t) * ((uint64_t)nh + 1)),
+                       o_haps = part(sizeof(DevHap) * ((uint64_t)nh + 1)), o_haplist = part(sizeof(uint32_t) * ((uint64_t)hl + 1)),
+                       o_happlan = part(pfx ? sizeof(uint2) * ((uint64_t)hl + 1) : 0), o_units = part(sizeof(DevUnit) * ((uint64_t)n_units + 1)),
+                       o_hapbytes = part(hbytes + 16);
+        s.meta_bytes = off;
+        RES(h_meta, off); RES(d_meta, off);
+        s.h_reads.set_view(s.h_meta.p + o_reads); s.d_reads.set_view(s.d_meta.p + o_reads);
+        s.h_hapoff.set_view(s.h_meta.p + o_hapoff); s.d_hapoff.set_view(s.d_meta.p + o_hapoff);
+        s.h_haps.set_view(s.h_meta.p + o_haps); s.d_haps.set_view(s.d_meta.p + o_haps);
+        s.h_haplist.set_view(s.h_meta.p + o_haplist); s.d_haplist.set_view(s.d_meta.p + o_haplist);
+        s.h_happlan.set_view(s.h_meta.p + o_happlan); s.d_happlan.set_view(s.d_meta.p + o_happlan);
+        s.h_units.set_view(s.h_meta.p + o_units); s.d_units.set_view(s.d_meta.p + o_units);
+        s.h_hapbytes.set_view(s.h_meta.p + o_hapbytes); s.d_hapbytes.set_view(s.d_meta.p + o_hapbytes);
+    }
     std::memcpy(s.h_rescue_base.p, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
-    RES(d_rd, s.plane * 5 + 16); RES(d_reads, nu + 1); RES(d_hapbytes, hbytes + 16); RES(d_hapoff, nh + 1);
-    RES(d_haps, nh + 1); RES(d_haplist, hl + 1); RES(d_units, n_units + 1); RES(d_out, up + 1); RES(d_flag, up + 1);
+    RES(d_rd, s.plane * 5 + 16); RES(d_out, up + 1); RES(d_flag, up + 1);
     RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
     s.ep_on = h->ep_on; s.ep = h->ep;
     s.raw_on = n_regs > 0 && s.regions[0].raw != nullptr; s.model = h->model; s.raw_indel_q = false;
@@ -485,7 +502,6 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         s.raw_indel_q |= s.plans[i].any_indel_q;
     }
     if (s.raw_on) { RES(h_mapq, nu + 1); RES(d_mapq, nu + 1); }
-    if (s.float_variant == Variant::F32_PFX) { RES(h_happlan, hl + 1); RES(d_happlan, hl + 1); }
     if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
@@ -564,8 +580,9 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     uint64_t plane_bytes = s.plane * (s.skip_gcp ? 4 : 5);
     if (s.n_uniq && !s.raw_on) {
         CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, plane_bytes, cudaMemcpyHostToDevice, st));
-        CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
     }
+    // descriptors, haplotype bytes and work units: one copy of the arena
+    if (s.meta_bytes) CU(h, cudaMemcpyAsync(s.d_meta.p, s.h_meta.p, s.meta_bytes, cudaMemcpyHostToDevice, st));
     if (s.n_uniq && s.raw_on) {
         // raw reads: bases + base qualities (+ insertion / deletion qualities if any read has them) cross PCIe; the default
         // indel qualities (ReadUtils.h:40) and the constant gap-continuation plane are written here
@@ -574,7 +591,6 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * (uint64_t)np, cudaMemcpyHostToDevice, st));
         if (!s.raw_indel_q) CU(h, cudaMemsetAsync(s.d_rd.p + 2 * s.plane, 45, 2 * s.plane, st));
         CU(h, cudaMemsetAsync(s.d_rd.p + 4 * s.plane, s.model.constant_gcp & 0xff, s.plane, st));
-        CU(h, cudaMemcpyAsync(s.d_reads.p, s.h_reads.p, sizeof(DevRead) * s.n_uniq, cudaMemcpyHostToDevice, st));
         CU(h, cudaMemcpyAsync(s.d_mapq.p, s.h_mapq.p, sizeof(int32_t) * s.n_uniq, cudaMemcpyHostToDevice, st));
         PrepReadsArgs pa{};
         pa.rd = s.d_rd.p; pa.plane = s.plane; pa.reads = s.d_reads.p; pa.mapq = s.d_mapq.p; pa.n = s.n_uniq;
@@ -583,26 +599,13 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, launch_prep_reads(pa, h->sm_count, st));
         h->stats.kernel_launches += 1;
     }
-    if (s.n_haps) {
-        if (s.hap_bytes) CU(h, cudaMemcpyAsync(s.d_hapbytes.p, s.h_hapbytes.p, s.hap_bytes, cudaMemcpyHostToDevice, st));
-        CU(h, cudaMemcpyAsync(s.d_hapoff.p, s.h_hapoff.p, sizeof(uint64_t) * s.n_haps, cudaMemcpyHostToDevice, st));
-        CU(h, cudaMemcpyAsync(s.d_haps.p, s.h_haps.p, sizeof(DevHap) * s.n_haps, cudaMemcpyHostToDevice, st));
-        CU(h, cudaMemcpyAsync(s.d_haplist.p, s.h_haplist.p, sizeof(uint32_t) * s.n_haplist, cudaMemcpyHostToDevice, st));
-        if (s.float_variant == Variant::F32_PFX) {
-            CU(h, cudaMemcpyAsync(s.d_happlan.p, s.h_happlan.p, sizeof(uint2) * s.n_haplist, cudaMemcpyHostToDevice, st));
-            h->stats.h2d_bytes += sizeof(uint2) * (uint64_t)s.n_haplist;
-        }
-    }
-    if (n_units) CU(h, cudaMemcpyAsync(s.d_units.p, s.h_units.p, sizeof(DevUnit) * n_units, cudaMemcpyHostToDevice, st));
     if (s.ep_on && s.n_uniq) {
         CU(h, cudaMemcpyAsync(s.d_rows.p, s.h_rows.p, sizeof(RowInfo) * s.n_uniq, cudaMemcpyHostToDevice, st));
         h->stats.h2d_bytes += sizeof(RowInfo) * (uint64_t)s.n_uniq;
     }
     CU(h, launch_prep_haps(s.d_hapbytes.p, s.d_hapoff.p, s.d_haps.p, s.n_haps, s.d_hapw.p, st));
     h->stats.kernel_launches += 1;
-    h->stats.h2d_bytes += plane_bytes + sizeof(DevRead) * (uint64_t)s.n_uniq + s.hap_bytes +
-                          (sizeof(uint64_t) + sizeof(DevHap) + sizeof(uint32_t)) * (uint64_t)s.n_haps +
-                          sizeof(DevUnit) * (uint64_t)n_units;
+    h->stats.h2d_bytes += plane_bytes + s.meta_bytes;
     return PAIRHMM_OK;
 }
 

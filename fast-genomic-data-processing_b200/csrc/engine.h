@@ -13,15 +13,18 @@
 namespace phmm {
 
 // Growable pinned-host / device arrays (never shrink; 1.25x growth).
+// A buffer may also be a VIEW into another one (Slot::h_meta / d_meta): it then owns nothing and is never reserved.
 template <class T> struct PinnedBuf {
-    T *p = nullptr; size_t cap = 0;
+    T *p = nullptr; size_t cap = 0; bool view = false;
     cudaError_t reserve(size_t n);
     void release();
+    void set_view(void *q) { if (!view) release(); p = static_cast<T *>(q); cap = 0; view = true; }
 };
 template <class T> struct DevBuf {
-    T *p = nullptr; size_t cap = 0;
+    T *p = nullptr; size_t cap = 0; bool view = false;
     cudaError_t reserve(size_t n);
     void release();
+    void set_view(void *q) { if (!view) release(); p = static_cast<T *>(q); cap = 0; view = true; }
 };
 
 // One region as the packer sees it (pointers borrowed from the caller).
@@ -72,6 +75,11 @@ struct Slot {
     PinnedBuf<uint64_t> h_hapoff;
     PinnedBuf<uint32_t> h_haplist;
     PinnedBuf<uint2> h_happlan;       // F32_PFX: sweep plan per hap_list entry
+    // The descriptors, the haplotype bytes and the work units of a chunk (h_reads, h_hapoff, h_haps, h_haplist, h_happlan,
+    // h_units, h_hapbytes and their device mirrors) are views into one pinned / one device arena with the same layout:
+    // they cross PCIe in ONE copy (a per-region call made seven of them)
+    PinnedBuf<uint8_t> h_meta;
+    uint64_t meta_bytes = 0;          // used bytes of the arena
     PinnedBuf<DevUnit> h_units;
     PinnedBuf<double> h_out;
     PinnedBuf<int32_t> h_mapq;        // raw reads: mapping quality per unique read
@@ -84,6 +92,7 @@ struct Slot {
     DevBuf<uint64_t> d_hapoff;
     DevBuf<uint32_t> d_haplist, d_hapw, d_counters;
     DevBuf<uint2> d_happlan;
+    DevBuf<uint8_t> d_meta;
     DevBuf<uint8_t> d_long_scratch;   // stripe hand-over lines of the long-read kernel
     int32_t hap_max = 0;              // longest haplotype of the chunk
     DevBuf<DevUnit> d_units, d_rescue;
