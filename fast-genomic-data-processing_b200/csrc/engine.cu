@@ -566,6 +566,27 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             ho += (uint64_t)hp.len; wo += hap_words(hp.len);
         }
     });
+    // A chunk of few units (a handful of waves of warps) ends when its slowest warp does: hand the long units out first
+    // (LPT). Large chunks keep the packing order -- their tail is a fraction of a per cent and sorting a million units is not free.
+    if (n_units > (uint32_t)h->sm_count * 8u && n_units <= 65536u) {      // more than one wave of resident warps
+        std::vector<std::pair<uint32_t, DevUnit>> tmp;
+        for (int b = 0; b < kNumBins; ++b) {
+            const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
+            if (n < 2) continue;
+            DevUnit *u = s.h_units.p + s.bin_start[b];
+            tmp.resize(n);
+            bool varied = false;
+            for (uint32_t k = 0; k < n; ++k) {
+                uint32_t cost = 0;
+                for (uint32_t q = 0, nh = u[k].shape & 0xffu; q < nh; ++q) cost += hap_tiles(s.h_haps.p[s.h_haplist.p[u[k].hap_list + q]].len);
+                tmp[k] = {cost, u[k]};
+                varied |= cost != tmp[0].first;
+            }
+            if (!varied) continue;
+            std::stable_sort(tmp.begin(), tmp.end(), [](const auto &x, const auto &y) { return x.first > y.first; });
+            for (uint32_t k = 0; k < n; ++k) u[k] = tmp[k].second;
+        }
+    }
     h->stats.host_ms_pack += ms_since(t0);
     if (trace_on())
         std::fprintf(stderr, "[trace] pack %u reads: plan %.1f | bin %.1f | prefix+reserve %.1f | copy %.1f ms (%d threads)\n", s.n_uniq,
