@@ -187,6 +187,8 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
     pl = RegionPlan();
     if (rv.n_reads < 0 || rv.n_haps < 0 || (rv.n_reads > 0 && !rv.reads && !rv.raw) || (rv.n_haps > 0 && !rv.haps))
         return fail(h, PAIRHMM_ERR_ARG, "null pointer or negative count in region");
+    if (rv.n_reads > 0 && rv.n_haps > 0 && !rv.out && !h->no_output_ok)
+        return fail(h, PAIRHMM_ERR_ARG, "null output array");
     pl.uniq_of_read.assign(rv.n_reads, kNoRead);
     const bool dedup = h->cfg.dedup_reads != 0;
     std::vector<uint32_t> table;   // open addressing: local unique index + 1
@@ -463,8 +465,12 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     s.hap_max = hap_max;
     // the packed FP32 kernels and the wide FP64 kernel take the (uniform) gap-continuation penalty as a launch constant and
     // never read the gcp plane: it is neither staged nor sent (a fifth of the read bytes). The long-read kernel reads it.
-    s.skip_gcp = is_packed_f32(s.float_variant) && s.bin_start[kNumBins + 1] == s.bin_start[kNumBins] &&
-                 !(n_regs > 0 && s.regions[0].raw != nullptr);
+    // the read kind of the chunk = that of its first region that has reads (an empty leading region, e.g. an empty
+    // std::vector's data(), says nothing); mixing kinds is refused below
+    bool chunk_raw = false;
+    for (size_t i = 0; i < n_regs; ++i)
+        if (s.regions[i].n_reads > 0) { chunk_raw = s.regions[i].raw != nullptr; break; }
+    s.skip_gcp = is_packed_f32(s.float_variant) && s.bin_start[kNumBins + 1] == s.bin_start[kNumBins] && !chunk_raw;
     s.plane = (rbytes + 15) & ~15ull;
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
     s.cells = cells; s.pairs = pairs; s.reads_in = reads_in; s.cells_swept = swept;
@@ -495,7 +501,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     RES(d_rd, s.plane * 5 + 16); RES(d_out, up + 1); RES(d_flag, up + 1);
     RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
     s.ep_on = h->ep_on; s.ep = h->ep;
-    s.raw_on = n_regs > 0 && s.regions[0].raw != nullptr; s.model = h->model; s.raw_indel_q = false;
+    s.raw_on = chunk_raw; s.model = h->model; s.raw_indel_q = false;
     for (size_t i = 0; i < n_regs; ++i) {
         if ((s.regions[i].raw != nullptr) != s.raw_on && s.regions[i].n_reads > 0)
             return fail(h, PAIRHMM_ERR_ARG, "raw and processed reads mixed in one call");
@@ -824,6 +830,7 @@ int pack_threads(const pairhmm_cuda_handle *h) {
 }
 
 int submit_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n, int threads) {
+    h->resident_loaded = false;      // the slots are re-packed: a batch staged by _resident_load is gone
     int st = pack_chunk(h, s, regs, n, threads);
     if (st != PAIRHMM_OK) return st;
     s.busy = true;
@@ -879,7 +886,7 @@ int pairhmm_cuda_prefix_plan(const phmm_hap *haps, int n_haps, int unit_haps, ui
     RegionView rv{};
     rv.haps = haps; rv.n_haps = n_haps;
     RegionPlan pl;
-    pl.group = unit_haps > 0 ? (uint32_t)std::min(unit_haps, (int)kMaxUnitHaps) : default_unit_haps(n_haps, hmax);
+    pl.group = unit_haps > 0 ? balanced_unit_haps(n_haps, (uint32_t)std::min(unit_haps, (int)kMaxUnitHaps)) : default_unit_haps(n_haps, hmax);
     plan_prefix(rv, pl);
     for (int q = 0; q < n_haps; ++q) {
         const uint2 w = pl.hap_plan[q];
@@ -1303,7 +1310,9 @@ int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_
     h->resident_loaded = false;
     RegionView rv{nullptr, reads.data(), (int32_t)n_reads, nullptr, 0, nullptr, nullptr, nullptr};
     Slot &s = h->slots[0];
+    h->no_output_ok = true;
     st = pack_chunk(h, s, &rv, 1, pack_threads(h));
+    h->no_output_ok = false;
     h->cfg.dedup_reads = dedup ? 1 : 0;
     if (st != PAIRHMM_OK) return st;
     if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
@@ -1378,7 +1387,10 @@ int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases
     for (int64_t i = 0; i < n_regions; ++i)
         views[i] = RegionView{v.regions[i].reads, nullptr, v.regions[i].n_reads, v.regions[i].haps, v.regions[i].n_haps, nullptr, nullptr, nullptr};
     Slot &s = h->slots[0];
-    if ((st = pack_chunk(h, s, views.data(), views.size(), pack_threads(h))) != PAIRHMM_OK) return st;
+    h->no_output_ok = true;
+    st = pack_chunk(h, s, views.data(), views.size(), pack_threads(h));
+    h->no_output_ok = false;
+    if (st != PAIRHMM_OK) return st;
     if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
     CU(h, cudaStreamSynchronize(s.stream));
     // the views point into `v`, which dies here: keep only the shapes (plans hold everything scatter needs)
@@ -1389,9 +1401,10 @@ int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases
 
 int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms) {
     if (!h) return PAIRHMM_ERR_ARG;
-    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_run: nothing loaded");
+    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_run: nothing loaded (or the batch was replaced by a later compute call)");
     CU(h, cudaSetDevice(h->device));
     Slot &s = h->slots[0];
+    if (s.busy) return fail(h, PAIRHMM_ERR_STATE, "resident_run: a submitted chunk is in flight on this handle");
     int st = run_kernels(h, s);
     if (st != PAIRHMM_OK) return st;
     CU(h, cudaStreamSynchronize(s.stream));
@@ -1407,9 +1420,10 @@ int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *f
 
 int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out) {
     if (!h || !log10_out) return PAIRHMM_ERR_ARG;
-    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: nothing loaded");
+    if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: nothing loaded (or the batch was replaced by a later compute call)");
     CU(h, cudaSetDevice(h->device));
     Slot &s = h->slots[0];
+    if (s.busy) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: a submitted chunk is in flight on this handle");
     size_t off = 0;
     for (auto &rv : s.regions) {
         rv.out = log10_out + off; rv.resc = rescued_out ? rescued_out + off : nullptr;

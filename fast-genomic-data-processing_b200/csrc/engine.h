@@ -145,6 +145,7 @@ struct pairhmm_cuda_handle {
     int64_t slot_ticket[2] = {0, 0};
     cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk (kernels of the next one wait on it)
     bool resident_loaded = false;
+    bool no_output_ok = false;        // resident_load / prepare_reads pack regions without result arrays
     bool ep_on = false;               // set for the duration of a *_normalized call
     pairhmm_cuda_epilogue ep{};
     pairhmm_cuda_read_model model{};  // of the current *_raw call

@@ -27,6 +27,13 @@ namespace phmm {
 
 constexpr unsigned kFull = 0xffffffffu;
 
+// initNative sets MXCSR flush-to-zero on the reference's threads (IntelPairHmm.cc:230), which also flushes DOUBLE denormals;
+// nvcc's -ftz covers FP32 only. A 2^1020-scaled FP64 sum that ends below DBL_MIN is zero in the reference (log10 = -inf):
+// flushed here, at the one place it is visible. Intermediate FP64 denormals are not flushed (no FP64 FTZ mode on the GPU):
+// a pair whose true log10 likelihood lies in about [-631, -600] may come out finite here and -inf in the reference
+// (tests/test_gpu_parity.py::test_fp64_underflow_window; such a read is removed by filterPoorlyModeledEvidence either way).
+__device__ __forceinline__ double flush_denormal(double r) { return r < 2.2250738585072014e-308 ? 0.0 : r; }
+
 template <typename T> struct Num;
 template <> struct Num<float> {
     static __device__ __forceinline__ float init_const() { return 1.329227995784916e+36f; }  // 2^120
@@ -258,7 +265,7 @@ __global__ void __launch_bounds__(kThreads, PHMM_MINB(T, W, K)) forward_kernel(c
                         a.fres[my_out + cur] = r;
                     } else {
                         const uint32_t o = my_out + hap_info[cur].idx;
-                        a.out[o] = log10(r) - a.log10_init_d;                      // IntelPairHmm.cc:344
+                        a.out[o] = log10(flush_denormal(r)) - a.log10_init_d;      // IntelPairHmm.cc:344
                         a.flag[o] = 1;
                     }
                 }

@@ -296,7 +296,7 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 a.fres[my_out + cur] = r;
             } else {
                 const uint32_t o = my_out + hap_info[cur].idx;
-                a.out[o] = log10(r) - a.log10_init_d;                              // IntelPairHmm.cc:344
+                a.out[o] = log10(flush_denormal(r)) - a.log10_init_d;              // IntelPairHmm.cc:344
                 a.flag[o] = 1;
             }
         };

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(128) forward_long_kernel(const LongArgs a) {
                                    reinterpret_cast<float *>(line + 2 * w));
         if (a.use_double || rf < 1e-28f) {                                           // IntelPairHmm.cc:340-344
             const double rd = H <= 0 ? 0.0 : long_sweep<double>(a, rr, hap, H, line, line + w, line + 2 * w);
-            out = log10(rd) - a.log10_init_d;
+            out = log10(flush_denormal(rd)) - a.log10_init_d;
             flag = 1;
         } else {
             out = (double)__fsub_rn((float)log10((double)rf), a.log10_init_f);       // as finalize_kernel; IntelPairHmm.cc:348

@@ -61,6 +61,12 @@ class PhmmHap(C.Structure):
     _fields_ = [("bases", C.c_void_p), ("len", C.c_int32)]
 
 
+class PhmmRawRead(C.Structure):
+    """phmm_raw_read: a read as the BAM record holds it (ins_q / del_q NULL = default 45)"""
+    _fields_ = [("bases", C.c_void_p), ("base_q", C.c_void_p), ("ins_q", C.c_void_p), ("del_q", C.c_void_p),
+                ("len", C.c_int32), ("mapq", C.c_int32)]
+
+
 class PhmmRegion(C.Structure):
     _fields_ = [("reads", C.POINTER(PhmmRead)), ("n_reads", C.c_int32), ("haps", C.POINTER(PhmmHap)),
                 ("n_haps", C.c_int32), ("log10_out", C.c_void_p), ("rescued_out", C.c_void_p)]
@@ -130,6 +136,7 @@ def load_library():
     lib.pairhmm_cuda_default_read_model.argtypes = [C.POINTER(ReadModel)]
     lib.pairhmm_cuda_default_read_model.restype = None
     lib.pairhmm_cuda_compute_flat_raw.argtypes = [vp] + flat + [C.POINTER(ReadModel), vp, vp]
+    lib.pairhmm_cuda_compute_raw.argtypes = [vp, C.POINTER(PhmmRawRead), i32, C.POINTER(PhmmHap), i32, C.POINTER(ReadModel), vp, vp]
     lib.pairhmm_cuda_prepare_reads_flat.argtypes = [vp] * 6 + [vp, vp, i64, C.POINTER(ReadModel), vp, vp, vp, vp]
     lib.pairhmm_cuda_resident_load.argtypes = [vp] + flat
     lib.pairhmm_cuda_resident_run.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
@@ -323,6 +330,26 @@ class Engine:
             None if dq is None else dq.ctypes.data, mq.ctypes.data, b.read_off.ctypes.data, b.read_len.ctypes.data,
             b.n_reads, C.byref(m), *[o.ctypes.data for o in outs]))
         return tuple(outs)
+
+    def compute_raw(self, reads, haps, model=None):
+        """one region of raw reads: reads = list of (bases, base_q, ins_q | None, del_q | None, mapq) ->
+        (log10[n_reads, n_haps], rescued[n_reads, n_haps]); the quality pre-pass runs on the device"""
+        m = model or ReadModel()
+        keep = []
+        ra = (PhmmRawRead * max(1, len(reads)))()
+        for i, (bases, bq, iq, dq, mapq) in enumerate(reads):
+            arrs = [_u8(bases), _u8(bq), None if iq is None else _u8(iq), None if dq is None else _u8(dq)]
+            keep.append(arrs)
+            ra[i] = PhmmRawRead(*[None if x is None else x.ctypes.data for x in arrs], len(arrs[0]), int(mapq))
+        ha = (PhmmHap * max(1, len(haps)))()
+        for i, hp in enumerate(haps):
+            a = _u8(hp); keep.append(a)
+            ha[i] = PhmmHap(a.ctypes.data, len(a))
+        out = np.zeros((len(reads), len(haps)), np.float64)
+        resc = np.zeros((len(reads), len(haps)), np.uint8)
+        self._check(self.lib.pairhmm_cuda_compute_raw(self.h, ra, len(reads), ha, len(haps), C.byref(m), out.ctypes.data,
+                                                      resc.ctypes.data))
+        return out, resc
 
     def compute_batch_raw(self, b, base_q_raw, mapq, ins_q=None, del_q=None, model=None):
         """RegionBatch b (bases, offsets, haplotypes, regions) with raw qualities -> (log10[n_pairs], rescued[n_pairs])"""

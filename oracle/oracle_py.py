@@ -87,17 +87,19 @@ class Oracle(_Lib):
         return m, best, second, bh, pm
 
     def prepare_reads(self, read_bases, base_q, mapq, read_off, read_len, ins_q=None, del_q=None, pcr_rate_factor=3,
-                      base_q_threshold=18, constant_gcp=10):
-        """the caller's quality pre-pass (modifyReadQualities) on flat read arrays -> (base_q, ins_q, del_q, gcp)"""
+                      base_q_threshold=18, constant_gcp=10, has_indel_q=None):
+        """the caller's quality pre-pass (modifyReadQualities) on flat read arrays -> (base_q, ins_q, del_q, gcp);
+        has_indel_q[i] == 0: read i has no BI / BD arrays even though ins_q / del_q are given"""
         bases = np.ascontiguousarray(read_bases, np.uint8); bq = np.ascontiguousarray(base_q, np.uint8)
         outs = [np.zeros(bq.shape[0], np.uint8) for _ in range(4)]
         iq = None if ins_q is None else np.ascontiguousarray(ins_q, np.uint8)
         dq = None if del_q is None else np.ascontiguousarray(del_q, np.uint8)
         for i in range(len(read_len)):
             o, n = int(read_off[i]), int(read_len[i])
+            own = iq is not None and (has_indel_q is None or has_indel_q[i])
             self.lib.oracle_prepare_read(bases.ctypes.data + o, bq.ctypes.data + o,
-                                         None if iq is None else iq.ctypes.data + o,
-                                         None if dq is None else dq.ctypes.data + o, n, int(mapq[i]), pcr_rate_factor,
+                                         iq.ctypes.data + o if own else None,
+                                         dq.ctypes.data + o if own else None, n, int(mapq[i]), pcr_rate_factor,
                                          base_q_threshold, constant_gcp, *[x.ctypes.data + o for x in outs])
         return tuple(outs)
 
@@ -212,3 +214,76 @@ def reference_sw(p, params=(10, -15, -30, -5), strategy=SW_SOFTCLIP, threads=1):
     lib = C.CDLL(os.path.join(HERE, "_ref", "libref_sw.so"))
     lib.ref_sw_align_batch.argtypes = _SW_ARGS + [C.c_int]; lib.ref_sw_align_batch.restype = C.c_double
     return _sw_call(lib.ref_sw_align_batch, p, params, strategy, (int(threads),))
+
+
+# ---- the reference's caller side (oracle/_ref/libref_m2.so) ----
+class ReferenceM2:
+    """PairHMMLikelihoodCalculationEngine / VectorLoglessPairHMM / SAMRecord / Haplotype / AlleleLikelihoods ... of the
+    reference, compiled unmodified (oracle/Makefile, ref_m2_driver.cpp). `replay=True` loads integration/replay/libm2_replay.so
+    instead: the same harness with integration/CudaPairHMM.cpp linked in (use_cuda=True swaps the engine's pairHMM member)."""
+
+    def __init__(self, replay=False):
+        path = (os.path.join(HERE, "..", "integration", "replay", "libm2_replay.so") if replay
+                else os.path.join(HERE, "_ref", "libref_m2.so"))
+        self.path = os.path.abspath(path)
+        self.lib = C.CDLL(self.path)
+        self.lib.ref_m2_last_error.restype = C.c_char_p
+        self.lib.ref_m2_log10_min_true_likelihood.argtypes = [C.c_int, C.c_double]
+        self.lib.ref_m2_log10_min_true_likelihood.restype = C.c_double
+        self.lib.ref_m2_prepass.argtypes = [C.c_void_p] * 8 + [C.c_int64, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4
+        self.lib.ref_m2_region.argtypes = ([C.c_void_p] * 9 + [C.c_int64, C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_int] +
+                                           [C.c_int] * 3 + [C.c_double] + [C.c_int] * 3 + [C.c_void_p] * 3)
+
+    @staticmethod
+    def _reads(read_bases, base_q, ins_q, del_q, has_indel_q, mapq, read_off, read_len):
+        n = len(read_len)
+        bases = np.ascontiguousarray(read_bases, np.uint8); bq = np.ascontiguousarray(base_q, np.uint8)
+        iq = None if ins_q is None else np.ascontiguousarray(ins_q, np.uint8)
+        dq = None if del_q is None else np.ascontiguousarray(del_q, np.uint8)
+        if has_indel_q is None:
+            has = np.full(n, 0 if iq is None else 1, np.uint8)
+        else:
+            has = np.ascontiguousarray(has_indel_q, np.uint8)
+        mq = np.ascontiguousarray(mapq, np.int32); ro = np.ascontiguousarray(read_off, np.int64); rl = np.ascontiguousarray(read_len, np.int32)
+        ptr = lambda a: None if a is None else a.ctypes.data
+        return (bases, bq, iq, dq, has, mq, ro, rl), [ptr(bases), ptr(bq), ptr(iq), ptr(dq), ptr(has), ptr(mq)], ptr(ro), ptr(rl), n
+
+    def log10_min_true_likelihood(self, read_len, max_error_per_base=0.02):
+        return float(self.lib.ref_m2_log10_min_true_likelihood(int(read_len), float(max_error_per_base)))
+
+    def prepare_reads(self, read_bases, base_q, mapq, read_off, read_len, ins_q=None, del_q=None, has_indel_q=None,
+                      pcr_rate_factor=3, base_q_threshold=18, constant_gcp=10):
+        """modifyReadQualities + buildGapContinuationPenalties -> (base_q, ins_q, del_q, gcp), laid out like base_q"""
+        keep, ptrs, ro, rl, n = self._reads(read_bases, base_q, ins_q, del_q, has_indel_q, mapq, read_off, read_len)
+        outs = [np.zeros(keep[1].shape[0], np.uint8) for _ in range(4)]
+        st = self.lib.ref_m2_prepass(*ptrs, ro, rl, n, int(pcr_rate_factor), int(base_q_threshold), int(constant_gcp),
+                                     *[x.ctypes.data for x in outs])
+        if st != 0:
+            raise RuntimeError("ref_m2_prepass: " + self.lib.ref_m2_last_error().decode())
+        return tuple(outs)
+
+    def region(self, read_bases, base_q, mapq, read_off, read_len, hap_bases, hap_off, hap_len, read_sample=None, n_samples=1,
+               ins_q=None, del_q=None, has_indel_q=None, hap_ref=0, pcr_rate_factor=3, base_q_threshold=18, constant_gcp=10,
+               log10_mismapping=-4.5, use_double=False, stage=0, use_cuda=False):
+        """one active region through PairHMMLikelihoodCalculationEngine -> (matrix[n_reads, n_haps] in INPUT haplotype order,
+        removed[n_reads], allele_order[n_haps])"""
+        keep, ptrs, ro, rl, n = self._reads(read_bases, base_q, ins_q, del_q, has_indel_q, mapq, read_off, read_len)
+        rs = np.zeros(n, np.int32) if read_sample is None else np.ascontiguousarray(read_sample, np.int32)
+        hb = np.ascontiguousarray(hap_bases, np.uint8); ho = np.ascontiguousarray(hap_off, np.int64); hl = np.ascontiguousarray(hap_len, np.int32)
+        nh = len(hl)
+        out = np.zeros((n, nh), np.float64); removed = np.zeros(n, np.uint8); order = np.zeros(nh, np.int32)
+        st = self.lib.ref_m2_region(*ptrs, rs.ctypes.data, ro, rl, n, int(n_samples), hb.ctypes.data, ho.ctypes.data, hl.ctypes.data, nh,
+                                    int(hap_ref), int(pcr_rate_factor), int(base_q_threshold), int(constant_gcp),
+                                    float(log10_mismapping), int(use_double), int(stage), int(use_cuda), out.ctypes.data,
+                                    removed.ctypes.data, order.ctypes.data)
+        if st != 0:
+            raise RuntimeError("ref_m2_region: " + self.lib.ref_m2_last_error().decode())
+        return out, removed, order
+
+
+def reference_m2_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_m2.so"))
+
+
+def replay_available():
+    return os.path.exists(os.path.join(HERE, "..", "integration", "replay", "libm2_replay.so"))

@@ -4,7 +4,7 @@ import pytest
 
 import fgdp_b200
 from fgdp_b200 import synth
-from util import assert_parity, load_golden, GOLDEN, TOL
+from util import assert_parity, load_golden, GOLDEN, TOL, raw_quals, repeat_rich_batch
 
 pytestmark = pytest.mark.gpu
 
@@ -218,6 +218,105 @@ def test_empty_and_errors(engine):
     assert np.isneginf(out).all() and resc.all()
 
 
+def test_null_outputs_and_resident_state_are_refused(engine, oracle):
+    """a null result array is PAIRHMM_ERR_ARG (not a segfault after the GPU work); a batch staged by
+    _resident_load is gone once another call re-packs the slot (ERR_STATE instead of replaying the wrong batch)"""
+    import ctypes as C
+    b = synth.config1("clean")
+    reads = [tuple(a[int(o):int(o) + int(n)] for a in (b.read_bases, b.base_q, b.ins_q, b.del_q, b.gcp))
+             for o, n in zip(b.read_off, b.read_len)]
+    haps = [b.hap_bases[int(o):int(o) + int(n)] for o, n in zip(b.hap_off, b.hap_len)]
+    ra, ha, keep = engine._structs(reads, haps)
+    st = engine.lib.pairhmm_cuda_compute(engine.h, ra, len(reads), ha, len(haps), None, None)
+    assert st == -1 and b"null output" in engine.lib.pairhmm_cuda_last_error(engine.h)
+    t = C.c_int64()
+    assert engine.lib.pairhmm_cuda_submit(engine.h, ra, len(reads), ha, len(haps), None, None, C.byref(t)) == -1
+    reg = (fgdp_b200.pairhmm.PhmmRegion * 1)()
+    reg[0] = fgdp_b200.pairhmm.PhmmRegion(ra, len(reads), ha, len(haps), None, None)
+    assert engine.lib.pairhmm_cuda_compute_batch(engine.h, reg, 1) == -1
+    # resident state
+    engine.resident_load(b)
+    engine.resident_run()
+    other = synth.config2(2)
+    engine.compute_batch(other)
+    with pytest.raises(fgdp_b200.PairHMMError) as ei:
+        engine.resident_run()
+    assert ei.value.status == -5
+    with pytest.raises(fgdp_b200.PairHMMError):
+        engine.resident_fetch()
+    engine.resident_load(b)
+    engine.resident_run()
+    got, gresc = engine.resident_fetch()
+    want, wresc, _ = oracle.compute(b.as_flat(), threads=2)
+    assert_parity(got, gresc, want, wresc, what="resident after reload")
+
+
+def test_raw_batch_with_an_empty_leading_region(engine, oracle):
+    """the read kind of a chunk comes from its first region WITH reads: an empty first region (reads == NULL) in a
+    raw batch is valid input"""
+    import ctypes as C
+    P = fgdp_b200.pairhmm
+    b = synth.config1("clean")
+    bq, mapq, _, _ = raw_quals(b, 4, False)
+
+    class RawRegion(C.Structure):
+        _fields_ = [("reads", C.c_void_p), ("n_reads", C.c_int32), ("haps", C.c_void_p), ("n_haps", C.c_int32),
+                    ("log10_out", C.c_void_p), ("rescued_out", C.c_void_p)]
+    rr = (P.PhmmRawRead * b.n_reads)()
+    for i, (o, n) in enumerate(zip(b.read_off, b.read_len)):
+        rr[i] = P.PhmmRawRead(b.read_bases.ctypes.data + int(o), bq.ctypes.data + int(o), None, None, int(n), int(mapq[i]))
+    ha = (P.PhmmHap * b.n_haps)()
+    for i, (o, n) in enumerate(zip(b.hap_off, b.hap_len)):
+        ha[i] = P.PhmmHap(b.hap_bases.ctypes.data + int(o), int(n))
+    out = np.zeros(b.n_pairs); resc = np.zeros(b.n_pairs, np.uint8)
+    regs = (RawRegion * 3)()
+    regs[0] = RawRegion(None, 0, C.cast(ha, C.c_void_p), b.n_haps, None, None)
+    regs[1] = RawRegion(C.cast(rr, C.c_void_p), b.n_reads, C.cast(ha, C.c_void_p), b.n_haps, out.ctypes.data, resc.ctypes.data)
+    regs[2] = RawRegion(None, 0, None, 0, None, None)
+    m = P.ReadModel()
+    engine.lib.pairhmm_cuda_compute_batch_raw.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(P.ReadModel)]
+    st = engine.lib.pairhmm_cuda_compute_batch_raw(engine.h, C.cast(regs, C.c_void_p), 3, C.byref(m))
+    assert st == 0, engine.lib.pairhmm_cuda_last_error(engine.h)
+    want, wresc = engine.compute_batch_raw(b, bq, mapq)
+    assert np.array_equal(out, want) and np.array_equal(resc, wresc)
+
+
+def test_fp64_underflow_window(oracle):
+    """the reference runs with MXCSR flush-to-zero (IntelPairHmm.cc:230), which also flushes DOUBLE denormals; a
+    2^1020-scaled FP64 sum below DBL_MIN is -inf there. The engine flushes the final sum (forward.cuh: flush_denormal);
+    intermediate FP64 denormals cannot be flushed on the GPU, so inside the window (true log10 about -631 .. -600) a pair may
+    be finite here and -inf in the reference. Checked on all-mismatch reads with very high qualities, through the wide FP64
+    kernel (uniform gcp), the general FP64 kernel (per-base gcp) and the long-read kernel: identical wherever the reference
+    is finite and above the window; where the reference says -inf the engine says -inf or a value below -600."""
+    def batch(R, H, q, jitter):
+        read = np.full(R, ord("A"), np.uint8); hap = np.full(H, ord("C"), np.uint8)
+        g = np.full(R, q, np.uint8)
+        if jitter:
+            g[::2] -= 1
+        return synth.RegionBatch(read, np.full(R, q, np.uint8), np.full(R, q, np.uint8), np.full(R, q, np.uint8), g,
+                                 np.array([0], np.int64), np.array([R], np.int32), hap, np.array([0], np.int64),
+                                 np.array([H], np.int32), np.array([0, 1], np.int64), np.array([0, 1], np.int64), "w")
+    e = fgdp_b200.Engine()
+    seen_inf = seen_finite = 0
+    try:
+        for jitter in (False, True):
+            for R in list(range(120, 161, 2)) + [400, 450, 460, 470, 480, 490, 500, 520]:    # > 384 rows: long.cu
+                q = 45 if R < 200 else 14
+                b = batch(R, 200 if R < 200 else 500, q, jitter)
+                want, wresc, _ = oracle.compute(b.as_flat())
+                got, gresc = e.compute_batch(b)
+                assert np.array_equal(gresc, wresc)
+                if np.isfinite(want[0]):
+                    assert np.isfinite(got[0]) and abs(got[0] - want[0]) <= TOL, (R, jitter, got, want)
+                    seen_finite += 1
+                else:
+                    assert np.isneginf(got[0]) or got[0] < -600.0, (R, jitter, got, want)
+                    seen_inf += 1
+    finally:
+        e.close()
+    assert seen_inf > 4 and seen_finite > 4
+
+
 def test_resident_replay_matches(engine, oracle):
     b = synth.config2(6)
     want, wresc, _ = oracle.compute(b.as_flat(), threads=8)
@@ -305,36 +404,7 @@ def test_fused_epilogue_region_call_duplicates_and_empty_reads(engine, oracle):
     assert np.array_equal(again, raw)
 
 
-def _raw_quals(b, seed, with_indel):
-    """raw (BAM-like) qualities for the reads of batch b: base qualities 2..41, mapping quality 0..60 per read"""
-    rng = np.random.default_rng(seed)
-    n = b.read_bases.shape[0]
-    bq = rng.integers(2, 42, n).astype(np.uint8)
-    mapq = rng.integers(0, 61, b.n_reads).astype(np.int32)
-    iq = rng.integers(0, 61, n).astype(np.uint8) if with_indel else None
-    dq = rng.integers(0, 61, n).astype(np.uint8) if with_indel else None
-    return bq, mapq, iq, dq
-
-
-def _repeat_rich_batch(seed=5):
-    """reads full of homopolymers and short tandem repeats (what the PCR error model keys on), lengths 1..384"""
-    rng = np.random.default_rng(seed)
-    lens = [1, 2, 3, 8, 9, 31, 32, 33, 150, 151, 250, 384] + [int(x) for x in rng.integers(10, 300, 60)]
-    reads = []
-    for n in lens:
-        s = []
-        while len(s) < n:
-            unit = rng.choice(list(b"ACGT"), int(rng.integers(1, 9)))
-            s.extend(list(unit) * int(rng.integers(1, 12)))
-            if rng.random() < 0.3:
-                s.append(ord("N"))
-        reads.append(np.array(s[:n], np.uint8))
-    b = synth.config1("clean")
-    return synth.RegionBatch(np.concatenate(reads), np.zeros(sum(lens), np.uint8), np.zeros(sum(lens), np.uint8),
-                             np.zeros(sum(lens), np.uint8), np.zeros(sum(lens), np.uint8),
-                             np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64), np.array(lens, np.int32),
-                             b.hap_bases, b.hap_off, b.hap_len, np.array([0, len(lens)], np.int64),
-                             np.array([0, b.n_haps], np.int64), "repeat-rich")
+_raw_quals, _repeat_rich_batch = raw_quals, repeat_rich_batch
 
 
 @pytest.mark.parametrize("with_indel", [False, True])
@@ -349,6 +419,66 @@ def test_device_read_prepass_equals_oracle(engine, oracle, with_indel, pcr):
         want = oracle.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq, pcr, 18, 10)
         for g, w, name in zip(got, want, ("base_q", "ins_q", "del_q", "gcp")):
             assert np.array_equal(g, w), (b.name, name, np.nonzero(g != w)[0][:5])
+
+
+def test_device_read_prepass_equals_reference_golden(engine):
+    """prep_reads_kernel against tests/golden/prepass.npz = outputs of the reference's OWN modifyReadQualities &
+    buildGapContinuationPenalties (PairHMMLikelihoodCalculationEngine.cpp:123-292, GATKVariantContextUtils.cpp:59-105;
+    oracle/_ref/libref_m2.so): every byte equal -- row N1 pinned on the reference, not on a restatement"""
+    from test_oracle import _prepass_cases
+    n = 0
+    for k, (pcr, thr, gcp), mode, i, want in _prepass_cases():
+        if mode == 2:
+            continue        # BI / BD on every other read: the flat pre-pass takes them for all reads or none; see the region test below
+        b = synth.RegionBatch(i["bases"], i["base_q"], i["base_q"], i["base_q"], i["base_q"], i["read_off"], i["read_len"],
+                              np.zeros(0, np.uint8), np.zeros(0, np.int64), np.zeros(0, np.int32), np.array([0, len(i["read_len"])], np.int64),
+                              np.array([0, 0], np.int64), "prepass-golden")
+        got = engine.prepare_reads(b, i["base_q"], i["mapq"], i["ins_q"], i["del_q"], fgdp_b200.pairhmm.ReadModel(pcr, thr, gcp))
+        for g, w, name in zip(got, want, ("base_q", "ins_q", "del_q", "gcp")):
+            assert np.array_equal(g, w), (k, name, np.nonzero(g != w)[0][:5])
+        n += 1
+    assert n >= 12
+
+
+def test_raw_regions_equal_the_reference_callers_matrices(engine):
+    """pairhmm_cuda_compute_raw / _compute_normalized against tests/golden/m2_region.npz = whole regions through the
+    reference's own PairHMMLikelihoodCalculationEngine::computeReadLikelihoods (pre-pass, VectorLoglessPairHMM incl. its trie
+    path and de-dup, normalizeLikelihoods, filterPoorlyModeledEvidence): raw matrix within 1e-4; fused epilogue: same reads
+    flagged, same normalised values"""
+    from test_oracle import _m2_region_cases
+    n = 0
+    for name, d, out0, out1, removed1, order in _m2_region_cases():
+        ro, rl = d["read_off"], d["read_len"]
+        cut = lambda a, i: a[int(ro[i]):int(ro[i]) + int(rl[i])]
+        has = d.get("has_indel_q")
+        reads = []
+        for i in range(len(rl)):
+            own = "ins_q" in d and (has is None or has[i])
+            reads.append((cut(d["read_bases"], i), cut(d["base_q"], i), cut(d["ins_q"], i) if own else None,
+                          cut(d["del_q"], i) if own else None, int(d["mapq"][i])))
+        haps = [d["hap_bases"][int(o):int(o) + int(m)] for o, m in zip(d["hap_off"], d["hap_len"])]
+        model = fgdp_b200.pairhmm.ReadModel(d.get("pcr_rate_factor", 3), d.get("base_q_threshold", 18), 10)
+        e = fgdp_b200.Engine(use_double=True) if d.get("use_double") else engine
+        got, _ = e.compute_raw(reads, haps, model)
+        assert np.abs(got - out0).max() <= TOL, (name, np.abs(got - out0).max())
+        if e is not engine:
+            e.close()
+            continue
+        # the fused epilogue on the device-prepared reads: same rows removed, same normalised values as the reference's stage 1
+        b = synth.RegionBatch(d["read_bases"], d["base_q"], d["base_q"], d["base_q"], d["base_q"], ro, rl, d["hap_bases"],
+                              d["hap_off"], d["hap_len"], np.array([0, len(rl)], np.int64), np.array([0, len(haps)], np.int64), name)
+        if has is None:
+            pb, pi, pd, pg = engine.prepare_reads(b, d["base_q"], d["mapq"], d.get("ins_q"), d.get("del_q"), model)
+            preads = [(cut(d["read_bases"], i), cut(pb, i), cut(pi, i), cut(pd, i), cut(pg, i)) for i in range(len(rl))]
+            norm, _, summ = engine.compute_normalized(preads, haps)
+            thr = np.minimum(2.0, np.ceil(rl * 0.02)) * -4.0
+            sure = np.abs(out0.max(axis=1) - thr) > TOL
+            assert np.array_equal(summ["poorly_modeled"][sure], removed1[sure]), name
+            kept = (removed1 == 0) & sure
+            if kept.any():
+                assert np.abs(norm[kept] - out1[kept]).max() <= TOL, name
+        n += 1
+    assert n >= 18
 
 
 @pytest.mark.parametrize("with_indel", [False, True])

@@ -127,10 +127,118 @@ def test_epilogue_oracle_vs_live_reference(oracle):
         assert np.array_equal(mo, mr) and np.array_equal(pm, removed), t
 
 
+def _prepass_cases():
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "prepass.npz"))
+    for k in range(int(z["n_cases"])):
+        pcr, thr, gcp, bi, mode = (int(x) for x in z["par%d" % k])
+        key = "b%d_i%d_" % (bi, mode)
+        inp = {f: z[key + f] for f in ("bases", "base_q", "mapq", "read_off", "read_len")}
+        inp["ins_q"] = z[key + "ins_q"] if mode else None
+        inp["del_q"] = z[key + "del_q"] if mode else None
+        inp["has"] = z[key + "has"] if mode == 2 else None
+        yield k, (pcr, thr, gcp), mode, inp, tuple(z["%s%d" % (n, k)] for n in ("bq", "iq", "dq", "gcp"))
+
+
+def test_read_prepass_oracle_matches_reference_golden(oracle):
+    """oracle_prepare_read against tests/golden/prepass.npz = outputs of the reference's OWN modifyReadQualities /
+    applyPCRErrorModel / findTandemRepeatUnits / capMinimumReadQualities / buildGapContinuationPenalties
+    (PairHMMLikelihoodCalculationEngine.cpp:123-292 + GATKVariantContextUtils.cpp:59-105, compiled unmodified into
+    oracle/_ref/libref_m2.so): every byte equal. Repeat-rich reads with N of 1..600 bases and WES-like reads; no / all /
+    every-other read with BI + BD arrays; MAPQ 0..60; the three PCR models; thresholds 18 / 6 / 25; gcp 10 / 12."""
+    n = 0
+    for k, (pcr, thr, gcp), mode, i, want in _prepass_cases():
+        got = oracle.prepare_reads(i["bases"], i["base_q"], i["mapq"], i["read_off"], i["read_len"], i["ins_q"], i["del_q"],
+                                   pcr, thr, gcp, has_indel_q=i["has"])
+        for g, w, name in zip(got, want, ("base_q", "ins_q", "del_q", "gcp")):
+            assert np.array_equal(g, w), (k, name, np.nonzero(g != w)[0][:5])
+        n += 1
+    assert n >= 20
+
+
+def test_log10_min_true_likelihood_matches_reference_golden(oracle):
+    """the filterPoorlyModeledEvidence threshold inside oracle_epilogue against the reference's own log10MinTrueLikelihood
+    (PairHMMLikelihoodCalculationEngine.cpp:294-299, via libref_m2.so) for read lengths 0..399"""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "prepass.npz"))
+    lens, lmt = z["lmt_len"], z["lmt"]
+    assert np.array_equal(lmt, np.minimum(2.0, np.ceil(lens * 0.02)) * -4.0)
+    # a row whose best value sits exactly on the threshold is kept, just below it is flagged
+    m = np.stack([lmt, lmt - 1.0], axis=1)
+    _, _, _, _, pm = oracle.epilogue(m, lens)
+    assert not pm.any()
+    _, _, _, _, pm = oracle.epilogue(np.nextafter(m, -np.inf), lens)
+    assert pm.all()
+
+
+def _m2_region_cases():
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "m2_region.npz"))
+    for name in z["names"]:
+        name = str(name)
+        d = {k[len(name) + 4:]: z[k] for k in z.files if k.startswith(name + ".in.")}
+        for k in ("n_samples", "pcr_rate_factor", "base_q_threshold", "use_double"):
+            if k in d:
+                d[k] = int(d[k])
+        yield name, d, z[name + ".out0"], z[name + ".out1"], z[name + ".removed1"], z[name + ".order"]
+
+
+def test_reference_caller_golden_equals_oracle_pipeline(oracle):
+    """tests/golden/m2_region.npz = whole regions through the reference's own PairHMMLikelihoodCalculationEngine::
+    computeReadLikelihoods (raw reads -> modifyReadQualities -> VectorLoglessPairHMM (per-pair and trie paths, de-dup,
+    allele-order scatter into the SampleMatrix) -> normalizeLikelihoods -> filterPoorlyModeledEvidence). The oracle's
+    three restatements chained (prepare_read -> forward -> epilogue) must give the same matrices: stage 0 within 1e-4
+    (observed 4e-6: FMA vs no FMA), stage 1 the same kept / removed reads."""
+    n = 0
+    for name, d, out0, out1, removed1, order in _m2_region_cases():
+        pb, pi, pd, pg = oracle.prepare_reads(d["read_bases"], d["base_q"], d["mapq"], d["read_off"], d["read_len"],
+                                              d.get("ins_q"), d.get("del_q"), d.get("pcr_rate_factor", 3),
+                                              d.get("base_q_threshold", 18), 10, has_indel_q=d.get("has_indel_q"))
+        nr, nh = out0.shape
+        b = synth.RegionBatch(d["read_bases"], pb, pi, pd, pg, d["read_off"], d["read_len"], d["hap_bases"], d["hap_off"],
+                              d["hap_len"], np.array([0, nr], np.int64), np.array([0, nh], np.int64), name)
+        got, _, _ = oracle.compute(b.as_flat(), use_double=bool(d.get("use_double", 0)), threads=4)
+        got = got.reshape(nr, nh)
+        assert np.isfinite(out0).all() and np.abs(got - out0).max() <= TOL, (name, np.abs(got - out0).max())
+        m, best, second, bh, pm = oracle.epilogue(got, d["read_len"])
+        # reads whose best value is within 1e-4 of the threshold may legitimately fall on either side
+        thr = np.minimum(2.0, np.ceil(d["read_len"] * 0.02)) * -4.0
+        sure = np.abs(got.max(axis=1) - thr) > TOL
+        assert np.array_equal(pm[sure], removed1[sure]), name
+        kept = removed1 == 0
+        assert np.isnan(out1[~kept]).all()
+        if (kept & sure).any():
+            assert np.abs(m[kept & sure] - out1[kept & sure]).max() <= TOL, name
+        assert sorted(order.tolist()) == list(range(nh))
+        n += 1
+    assert n >= 20
+
+
+def test_oracle_and_goldens_vs_live_reference_caller(oracle):
+    """when oracle/_ref/libref_m2.so is present (the container with /root/reference): fresh random reads through the
+    reference's own pre-pass, and the committed goldens reproduced by it"""
+    import oracle_py
+    if not oracle_py.reference_m2_available():
+        pytest.skip("oracle/_ref/libref_m2.so not built (needs /root/reference at build time)")
+    from util import raw_quals, repeat_rich_batch
+    m2 = oracle_py.ReferenceM2()
+    for seed in (41, 42):
+        b = repeat_rich_batch(seed=seed, max_len=600)
+        for with_indel in (False, True):
+            bq, mapq, iq, dq = raw_quals(b, seed, with_indel)
+            for pcr in (1, 2, 3):
+                want = m2.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq, None, pcr, 18, 10)
+                got = oracle.prepare_reads(b.read_bases, bq, mapq, b.read_off, b.read_len, iq, dq, pcr, 18, 10)
+                for g, w in zip(got, want):
+                    assert np.array_equal(g, w)
+    for name, d, out0, out1, removed1, order in list(_m2_region_cases())[:6]:
+        o0, _, od = m2.region(stage=0, **d)
+        assert np.array_equal(o0, out0) and np.array_equal(od, order), name
+
+
 def test_read_prepass_oracle_known_answers(oracle):
     """oracle_prepare_read / oracle_tandem_repeat_length (restating PairHMMLikelihoodCalculationEngine.cpp:123-267):
-    hand-derived known answers. PARITY UNPINNED for this row -- the reference functions sit in translation units that do
-    not compile without the whole Mutect2Cpp build (oracle/pairhmm_oracle.h)."""
+    hand-derived known answers, kept beside the reference-generated goldens above (which are what pins the row)."""
     s = b"ACGTTTTTTGCACACACACAGGATTCTTC"
     # offset 2 ('G' before T x 6): BW unit G x1, FW unit T x6, FW unit does not repeat backwards -> 6;
     # offset 8 (last T): BW unit T x6 but FW unit G x1 differs and does not repeat backwards -> 1 (GATK's behaviour);

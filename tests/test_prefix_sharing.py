@@ -29,8 +29,10 @@ def _replay(haps, unit_haps):
     lens = [len(haps[i]) for i in p["order"]]
     assert lens == sorted(lens), "sweep order is by length first"
     hmax = max([len(h) for h in haps] + [0])
-    if unit_haps > 0:
-        group = min(unit_haps, 32)
+    if unit_haps > 0:                             # as plan_region: runs of (nearly) equal length, balanced_unit_haps()
+        g0 = min(unit_haps, 32)
+        units = (max(1, n) + g0 - 1) // g0
+        group = (max(1, n) + units - 1) // units
     else:                                         # default_unit_haps (engine.cu): runs of equal length
         g0 = min(max(1, n), max(1, 16384 // (hmax + 1)), 32)
         units = (max(1, n) + g0 - 1) // g0
@@ -75,6 +77,16 @@ def test_plan_replay_on_snv_families():
             s, f = _replay(_haps_of(b, g), unit)
             tot_swept += s; tot_full += f
     assert tot_swept < 0.85 * tot_full, "SNV families share a good part of their columns"
+
+
+def test_plan_uses_the_packers_balanced_groups():
+    """10 haplotypes at 8 per unit are swept as two runs of 5 (balanced_unit_haps), not 8 + 2: the plan the test hook
+    returns is the one the packer runs -- sharing must not cross position 5"""
+    b = synth.snv_family(1, 2, 10, 20, 120, seed_extra=77)
+    haps = _haps_of(b, 0)
+    p = fgdp_b200.prefix_plan(haps, 8)
+    assert int(p["t_start"][5]) == 0 and int(p["restore_slot"][5]) == -1
+    _replay(haps, 8)
 
 
 def test_plan_special_cases():
