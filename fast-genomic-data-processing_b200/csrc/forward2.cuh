@@ -260,7 +260,7 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
         Tile w = tp[-1], w1 = tp[0];                  // current and next tile; tix1 = index of w1
 
         // one DP column for this lane's K rows (computeMXY, template.h:177-192)
-        auto column = [&](uint32_t cw, V Dd, V Uu) {
+        auto column = [&](uint32_t cw, V Dd, V Uu, auto dirty_tag) {
             const Quad *ep = etab + ((cw >> 25) & 7u) * (KP * 32);   // bits 25..27 of a word = base index (5 if flagged)
             V e[2 * KP];
 #pragma unroll
@@ -268,7 +268,12 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
             // a flagged word resets the lane's state arithmetically instead of in a divergent branch: its match
             // factors are 0 (M = 0, hence X = 0) and its Y coefficient is 0; two flagged words in a row (every SEP is
             // followed by a PAD, kernels.cuh) leave M = X = Y = 0, i.e. column 0 of the next haplotype's matrix
-            const V cYY = P::coef_y(a, cw);
+            // In a CLEAN step the only flagged words a lane can meet are the PADs that fill a haplotype's last code tile
+            // (lead-in, drain and every SEP tile fall into dirty steps). They need no zero Y coefficient: their match
+            // factors are 0, so M = X = 0 and nothing reads Y until the SEP tile -- a dirty step -- resets it with its
+            // own flagged columns. So the clean instance takes the Y coefficient as the uniform-register operand it is
+            // (FFMA2 pair x UR + pair); per lane it would be a third vector operand (5 register reads per FFMA2).
+            const V cYY = decltype(dirty_tag)::value ? P::coef_y(a, cw) : cXY;
             V Mn[K], Xn[K], Yn[K];
             Mn[0] = P::mul(Dd, e[0]);
             Xn[0] = Uu;
@@ -343,7 +348,7 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
             V Dout[C], Uout[C];
 #pragma unroll
             for (int j = 0; j < C; ++j) {
-                column(tw_get(w, j), j == 0 ? Dprev : Din[j - 1], Uin[j]);
+                column(tw_get(w, j), j == 0 ? Dprev : Din[j - 1], Uin[j], dirty_tag);
                 emit_down(Dout[j], Uout[j]);
             }
             Dprev = Din[C - 1];   // D of the last column of the PREVIOUS exchange: diagonal of next step's first column

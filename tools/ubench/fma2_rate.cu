@@ -49,6 +49,8 @@ __global__ void k(float *out, const P p, int n) {
                 a[i] = mul2(s, pk(e0, e1));
             }
             if (V == 8) { a[i] = fma2(a[i], k1, c[i]); c[i] = mul2(c[i], b[i]); }   // FFMA2c + FMUL2 mix
+            if (V == 9) { const float sv = lo(b[i]); a[i] = fma2(a[i], pk(sv, sv), c[i]); }   // 2 pairs + per-lane scalar broadcast (R.F32): 5 register reads
+            if (V == 10) { const float sv = lo(b[i]); a[i] = fma2(a[i], pk(sv, sv), c[i]); c[i] = mul2(c[i], b[(i + 1) % NCH]); }   // the same mixed 1:1 with FMUL2
         }
         if (V == 6 || V == 7) m = m * 1664525u + 1013904223u;
     }
@@ -84,5 +86,7 @@ int main() {
     run<6>("FFMA2c + (SHF,LOP,SEL..) per packed op", 1, 3);
     run<7>("kernel-like M: FMUL2,FFMA2c,FFMA2c,FMUL2 + 2 SEL", 4, 6);
     run<8>("FFMA2c + FMUL2 mix", 2, 0);
+    run<9>("FFMA2 a=a*bcast(per-lane scalar)+c (R.F32 form)", 1, 0);
+    run<10>("FFMA2 R.F32 form + FMUL2 mix", 2, 0);
     return 0;
 }
