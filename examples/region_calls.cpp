@@ -4,7 +4,11 @@
 // Synthetic regions shaped like BASELINE configs[1] (~200 reads x 4-16 haplotypes, 150-base reads, 250-500-base
 // haplotypes); the per-region results are compared with one pairhmm_cuda_compute_batch call over the same regions.
 //
-//   bash examples/build.sh && examples/region_calls [regions=1200] [--submit]
+//   bash examples/build.sh && examples/region_calls [regions=1200] [--submit] [--batch-window US] [--devices MASK]
+// --batch-window US: the handles are created with config.batch_window_us = US, i.e. the blocking calls of all threads go
+//   through the library's process-wide batcher (regions of different threads share launch groups);
+// --devices MASK: multi-device handles (config.device_mask) -- the batch call is split over the devices, per-region calls
+//   go to them in turn.
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -68,8 +72,13 @@ static void make_region(Region &g, uint64_t seed) {
 }
 
 int main(int argc, char **argv) {
-    int n_regions = 1200; bool use_submit = false;
-    for (int i = 1; i < argc; ++i) { if (!std::strcmp(argv[i], "--submit")) use_submit = true; else n_regions = std::atoi(argv[i]); }
+    int n_regions = 1200; bool use_submit = false; int window_us = 0; unsigned mask = 0;
+    for (int i = 1; i < argc; ++i) {
+        if (!std::strcmp(argv[i], "--submit")) use_submit = true;
+        else if (!std::strcmp(argv[i], "--batch-window") && i + 1 < argc) window_us = std::atoi(argv[++i]);
+        else if (!std::strcmp(argv[i], "--devices") && i + 1 < argc) mask = (unsigned)std::strtoul(argv[++i], nullptr, 0);
+        else n_regions = std::atoi(argv[i]);
+    }
     if (pairhmm_cuda_device_count() < 1) { std::fprintf(stderr, "no sm_100 device: the engine has no CPU fallback\n"); return 2; }
     std::vector<Region> regs((size_t)n_regions);
     {
@@ -80,6 +89,7 @@ int main(int argc, char **argv) {
     uint64_t cells = 0;
     for (auto &g : regs) cells += g.cells;
     pairhmm_cuda_config cfg; pairhmm_cuda_default_config(&cfg);
+    cfg.device_mask = mask;
     {   // reference result: the same regions in one batch call
         pairhmm_cuda_handle *h = nullptr;
         if (pairhmm_cuda_create(&cfg, &h)) return 3;
@@ -93,7 +103,8 @@ int main(int argc, char **argv) {
         }
         pairhmm_cuda_destroy(h);
     }
-    cfg.pack_threads = 1;
+    cfg.pack_threads = window_us > 0 ? 0 : 1;
+    cfg.batch_window_us = window_us;
     for (int T : {1, 2, 4, 8, 16, 32}) {
         std::vector<pairhmm_cuda_handle *> hs((size_t)T, nullptr);
         for (auto &h : hs) { if (pairhmm_cuda_create(&cfg, &h)) return 3; pairhmm_cuda_initialize(h, 150, 512); }
@@ -125,7 +136,7 @@ int main(int argc, char **argv) {
         bool same = true;
         for (auto &g : regs) same = same && !std::memcmp(g.out.data(), g.out_batch.data(), g.out.size() * sizeof(double));
         std::printf("{\"mode\": \"%s per region\", \"threads\": %d, \"regions\": %d, \"seconds\": %.4f, \"gcups\": %.1f, \"mean_call_ms\": %.3f, "
-                    "\"errors\": %d, \"identical_to_batch_call\": %s}\n", use_submit ? "submit/wait" : "compute", T, n_regions, dt,
+                    "\"errors\": %d, \"identical_to_batch_call\": %s}\n", use_submit ? "submit/wait" : window_us > 0 ? "compute (shared batcher)" : "compute", T, n_regions, dt,
                     cells / dt / 1e9, dt * T / n_regions * 1e3, errors.load(), same ? "true" : "false");
         std::fflush(stdout);
         for (auto &h : hs) pairhmm_cuda_destroy(h);

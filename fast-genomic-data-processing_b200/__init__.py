@@ -6,5 +6,5 @@ Python host binding used by the tests and bench.py; it mirrors the reference's P
 sm_100 GPU every compute call raises.
 """
 from .pairhmm import (CudaPairHMM, Engine, PairHMMError, lib_path, load_library, device_count,  # noqa: F401
-                      EXPORTED_SYMBOLS, prefix_plan)
+                      EXPORTED_SYMBOLS, prefix_plan, device_plan)
 from . import synth  # noqa: F401

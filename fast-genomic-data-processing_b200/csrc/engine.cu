@@ -11,6 +11,7 @@
 #include <mutex>
 #include <thread>
 
+#include "hostpool.h"
 #include "tables.h"
 
 using namespace phmm;
@@ -70,10 +71,14 @@ bool trace_on() { static const bool on = std::getenv("PAIRHMM_CUDA_TRACE") != nu
 clk::time_point g_trace_t0;
 cudaEvent_t g_trace_base = nullptr;
 
-int fail(pairhmm_cuda_handle *h, int status, const std::string &msg) {
+}  // namespace
+// plan_region runs on several pool threads and may report through fail(): the text is written under a lock (the status
+// itself travels through an atomic in pack_chunk), and only the first error of a call is kept by its caller
+int phmm::fail(pairhmm_cuda_handle *h, int status, const std::string &msg) {
     if (h) { std::lock_guard<std::mutex> lk(g_err_mutex); h->last_error = msg; }
     return status;
 }
+namespace {
 int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
     cudaGetLastError();  // clear sticky-less error state
     return fail(h, e == cudaErrorMemoryAllocation ? PAIRHMM_ERR_OOM : PAIRHMM_ERR_CUDA,
@@ -94,24 +99,10 @@ constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32 + 2;
 constexpr int kRescueBaseDev = kZeroedWords;
 constexpr int kCounterWords = kZeroedWords + kNumBinsW32 + 4;
 
-// Runs fn(i) for i in [0,n) on up to `threads` std::threads (dynamic chunks of `grain`).
+// Runs fn(i) for i in [0,n) on the calling thread plus up to `threads` - 1 threads of the process-wide pool
+// (dynamic chunks of `grain`; hostpool.h).
 template <class F> void parallel_for(size_t n, int threads, size_t grain, F fn) {
-    if (threads <= 1 || n <= grain) { for (size_t i = 0; i < n; ++i) fn(i); return; }
-    std::atomic<size_t> next{0};
-    auto body = [&] {
-        for (;;) {
-            size_t b = next.fetch_add(grain);
-            if (b >= n) break;
-            size_t e = std::min(n, b + grain);
-            for (size_t i = b; i < e; ++i) fn(i);
-        }
-    };
-    int nt = (int)std::min<size_t>((size_t)threads, (n + grain - 1) / grain);
-    std::vector<std::thread> th;
-    th.reserve(nt - 1);
-    for (int t = 1; t < nt; ++t) th.emplace_back(body);
-    body();
-    for (auto &t : th) t.join();
+    HostPool::instance().parallel_for(n, threads, grain, fn);
 }
 
 inline uint64_t mix64(uint64_t x) {
@@ -182,6 +173,25 @@ uint32_t default_unit_haps(int n_haps, int32_t hmax) {
     return balanced_unit_haps(n_haps, std::min(g, (uint32_t)kMaxUnitHaps));
 }
 
+}  // namespace
+// what plan_region refuses, without planning (the shared batcher validates a caller's region before it joins a chunk
+// of other callers' regions, so that one bad region cannot fail theirs)
+int phmm::check_region_args(pairhmm_cuda_handle *h, const RegionView &rv) {
+    if (rv.n_reads < 0 || rv.n_haps < 0 || (rv.n_reads > 0 && !rv.reads && !rv.raw) || (rv.n_haps > 0 && !rv.haps))
+        return fail(h, PAIRHMM_ERR_ARG, "null pointer or negative count in region");
+    if (rv.n_reads > 0 && rv.n_haps > 0 && !rv.out && !h->no_output_ok)
+        return fail(h, PAIRHMM_ERR_ARG, "null output array");
+    if ((uint32_t)rv.n_haps > 0xffffu) return fail(h, PAIRHMM_ERR_ARG, "more than 65535 haplotypes in one region");
+    for (int i = 0; i < rv.n_haps; ++i)
+        if (rv.haps[i].len < 0 || (rv.haps[i].len > 0 && !rv.haps[i].bases)) return fail(h, PAIRHMM_ERR_ARG, "bad haplotype");
+    for (int i = 0; i < rv.n_reads; ++i) {
+        const ReadRef r = read_ref(rv, (size_t)i);
+        if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || (!rv.raw && (!r.ins_q || !r.del_q || !r.gcp)))))
+            return fail(h, PAIRHMM_ERR_ARG, "bad read");
+    }
+    return PAIRHMM_OK;
+}
+namespace {
 // Pass A for one region: read de-duplication (VectorLoglessPairHMM.cpp:83-103) and sizes.
 int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, uint32_t group_hint) {
     pl = RegionPlan();
@@ -371,23 +381,53 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // the packed kernels keep 8 warps per SM resident (2 CTAs of 4 warps): aim at three waves of warp units. Counted in
     // warps, not reads -- a warp takes 2-8 reads (tools/unit_sweep.py: C3 2699 -> 3162, C4 2954 -> 3093 GCUPS in the FP32
     // pass against the former reads-based rule, which cut the runs of mid-sized chunks too short or raggedly)
-    const uint64_t want_units = (uint64_t)h->sm_count * 8u * 3u;
+    // Other chunks in flight on this device (other host threads' handles, this handle's other slot): the more there are,
+    // the fewer units this chunk needs to keep the device full, and the longer -- cheaper per cell -- they may be.
+    const int others = device_chunks_in_flight(h->device);
+    const uint64_t want_units = std::max<uint64_t>((uint64_t)h->sm_count * 8u * 3u / (uint64_t)(1 + std::max(0, others)), 64u);
     uint32_t group_hint = 0;
-    if (total_reads && total_reads < want_units * 8u) {
+    int chunk_w = h->cfg.reserved[1];       // lane-group width forced for this chunk (0 = the narrowest that fits, per read)
+    if (total_reads && total_reads < (uint64_t)h->sm_count * 8u * 3u * 8u) {
         double warps = 0.0;
         const int forced = h->cfg.reserved[1];
+        uint64_t warps_at[kNumWidths] = {0, 0, 0};
+        bool fits_at[kNumWidths] = {true, true, true};
+        int rmax = 1;
+        uint32_t maxh = 1;
+        double tiles = 0.0, nhaps = 0.0;
         for (size_t i = 0; i < n_regs; ++i) {
+            maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
+            if (regs[i].haps) for (int q = 0; q < regs[i].n_haps; ++q) { tiles += hap_tiles(std::max(0, regs[i].haps[q].len)); nhaps += 1.0; }
             if (regs[i].n_reads <= 0 || (!regs[i].reads && !regs[i].raw)) continue;
+            uint32_t n_ok = 0;
             for (int r = 0; r < regs[i].n_reads; ++r) {
                 const int len = read_ref(regs[i], (size_t)r).len;
                 if (len < 1 || len > kMaxReadLen) continue;
+                ++n_ok; rmax = std::max(rmax, len);
                 warps += 1.0 / (double)reads_per_warp(Variant::F32_PK, choose_width(len, Variant::F32_PK, forced));
             }
+            for (int wi = 0; wi < kNumWidths; ++wi) {
+                const uint32_t per_warp = (uint32_t)reads_per_warp(Variant::F32_PK, kWidths[wi]);
+                warps_at[wi] += (n_ok + per_warp - 1) / per_warp;
+            }
         }
-        if (warps > 0.0 && warps < (double)want_units) {
+        for (int wi = 0; wi < kNumWidths; ++wi) fits_at[wi] = bin_of_read(rmax, kWidths[wi]) >= 0;
+        // A chunk so small that ONE wave of warps takes all of it even with a unit per (warp of reads, haplotype) -- a
+        // region per call -- is as slow as its slowest unit: (tiles of one haplotype + W fill steps) x rows per lane. Wide
+        // lane groups make that short (W = 32, K = 5 sweeps a 150-base read in 0.57 of the time of W = 16, K = 10), so
+        // the width that is best for throughput (the narrowest) is not taken here.
+        const uint64_t slots = (uint64_t)h->sm_count * 8u;
+        if (!forced && warps > 0.0 && others == 0) {
+            double best = 0.0;
+            const double t_avg = nhaps > 0.0 ? tiles / nhaps : 1.0;
+            for (int wi = 0; wi < kNumWidths; ++wi) {
+                if (!fits_at[wi] || warps_at[wi] * (uint64_t)maxh > slots) continue;
+                const double t = (t_avg + (double)kWidths[wi]) * (double)((rmax + kWidths[wi] - 1) / kWidths[wi]);
+                if (best == 0.0 || t < best) { best = t; chunk_w = kWidths[wi]; group_hint = 1; }
+            }
+        }
+        if (!group_hint && warps > 0.0 && warps < (double)want_units) {
             const uint64_t splits = (uint64_t)std::ceil((double)want_units / warps);   // units wanted per warp of reads
-            uint32_t maxh = 1;
-            for (size_t i = 0; i < n_regs; ++i) maxh = std::max<uint32_t>(maxh, (uint32_t)std::max(1, regs[i].n_haps));
             group_hint = (uint32_t)std::max<uint64_t>(1, maxh / std::min<uint64_t>(splits, maxh));
         }
     }
@@ -410,7 +450,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // prefix sharing (config.reserved[4]) reorders a region's haplotypes inside the chunk; the fused epilogue reports
     // haplotype indices and breaks ties by position, so it keeps the caller's order
     const bool pfx_candidate = s.float_variant == Variant::F32_PK && h->cfg.reserved[4] && !h->ep_on;
-    const int forced_w = h->cfg.reserved[1];
+    const int forced_w = chunk_w;
     const double ms_plan = ms_since(t0);
     parallel_for(n_regs, threads, 8, [&](size_t i) {
         bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w);
@@ -819,9 +859,16 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     h->stats.pairs += s.pairs; h->stats.unique_pairs += uniq_pairs.load(); h->stats.cells += s.cells;
     h->stats.cells_swept += s.cells_swept;
     h->stats.rescued_pairs += rescued.load();
-    s.busy = false;
+    set_busy(h, s, false);
     return PAIRHMM_OK;
 }
+
+static std::atomic<int> g_chunks_in_flight[64];
+void set_busy(pairhmm_cuda_handle *h, Slot &s, bool busy) {
+    s.busy = busy;
+    if (busy != s.counted) { s.counted = busy; g_chunks_in_flight[h->device & 63].fetch_add(busy ? 1 : -1, std::memory_order_relaxed); }
+}
+int device_chunks_in_flight(int device) { return g_chunks_in_flight[device & 63].load(std::memory_order_relaxed); }
 
 int pack_threads(const pairhmm_cuda_handle *h) {
     if (h->cfg.pack_threads > 0) return h->cfg.pack_threads;
@@ -833,7 +880,7 @@ int submit_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t
     h->resident_loaded = false;      // the slots are re-packed: a batch staged by _resident_load is gone
     int st = pack_chunk(h, s, regs, n, threads);
     if (st != PAIRHMM_OK) return st;
-    s.busy = true;
+    set_busy(h, s, true);
     if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
     if ((st = run_kernels(h, s)) != PAIRHMM_OK) return st;
     return download_chunk(h, s);
@@ -863,7 +910,7 @@ void pairhmm_cuda_default_config(pairhmm_cuda_config *cfg) {
     if (!cfg) return;
     std::memset(cfg, 0, sizeof(*cfg));
     cfg->device = -1; cfg->use_double = 0; cfg->exact_fp32 = 0; cfg->dedup_reads = 1; cfg->pack_threads = 0;
-    cfg->chunk_cells = 0;
+    cfg->chunk_cells = 0; cfg->device_mask = 0; cfg->batch_window_us = 0;
 }
 
 int pairhmm_cuda_tables(float *ph2pr_f, float *mm_f, double *ph2pr_d, double *mm_d) {
@@ -905,6 +952,16 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
     if (cfg) c = *cfg; else pairhmm_cuda_default_config(&c);
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { cudaGetLastError(); return PAIRHMM_ERR_NO_DEVICE; }
+    if (c.device_mask) {          // multi-device handle: one child handle + one host worker per device (multi.cu)
+        auto *m = new (std::nothrow) pairhmm_cuda_handle();
+        if (!m) return PAIRHMM_ERR_OOM;
+        m->cfg = c;
+        std::memset(&m->stats, 0, sizeof m->stats);
+        const int st = multi_create(m);
+        if (st != PAIRHMM_OK) { pairhmm_cuda_destroy(m); return st; }
+        *out = m;
+        return PAIRHMM_OK;
+    }
     int dev = c.device;
     if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) return PAIRHMM_ERR_NO_DEVICE; }
     if (dev >= n) return PAIRHMM_ERR_ARG;
@@ -933,14 +990,17 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
             return bail(PAIRHMM_ERR_CUDA);
     }
     if (forward_blocks_per_sm(Variant::F32_GEN, 32, 1, 0) < 1) return bail(PAIRHMM_ERR_CUDA);   // kernels loadable?
+    if (c.batch_window_us > 0) h->batcher = batcher_acquire(h);      // process-wide, per device (batcher.cu)
     *out = h;
     return PAIRHMM_OK;
 }
 
 int pairhmm_cuda_destroy(pairhmm_cuda_handle *h) {
     if (!h) return PAIRHMM_OK;
+    if (h->is_multi() || h->cfg.device_mask) { multi_destroy(h); delete h; return PAIRHMM_OK; }
+    if (h->batcher) { batcher_release(h->batcher); h->batcher = nullptr; }
     cudaSetDevice(h->device);
-    for (auto &s : h->slots) { if (s.stream) cudaStreamSynchronize(s.stream); s.release(); }
+    for (auto &s : h->slots) { if (s.stream) cudaStreamSynchronize(s.stream); set_busy(h, s, false); s.release(); }
     if (h->d_ph2pr_f) cudaFree(h->d_ph2pr_f);
     if (h->d_mm_f) cudaFree(h->d_mm_f);
     if (h->d_ph2pr_d) cudaFree(h->d_ph2pr_d);
@@ -954,6 +1014,7 @@ int pairhmm_cuda_initialize(pairhmm_cuda_handle *h, int read_max_len, int hap_ma
     if (read_max_len <= 0 || hap_max_len <= 0)   // PairHMM.cpp:16 asserts haplotypeMaxLength > 0
         return fail(h, PAIRHMM_ERR_ARG, "initialize: maximum lengths must be positive");
     h->read_max_len = read_max_len; h->hap_max_len = hap_max_len;
+    for (auto *c : h->children) { c->read_max_len = read_max_len; c->hap_max_len = hap_max_len; }
     return PAIRHMM_OK;
 }
 
@@ -961,18 +1022,22 @@ const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h) { return h ? h->last
 
 int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out) {
     if (!h || !out) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) { multi_stats(h, out); return PAIRHMM_OK; }
     *out = h->stats;
     return PAIRHMM_OK;
 }
 int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h) {
     if (!h) return PAIRHMM_ERR_ARG;
     std::memset(&h->stats, 0, sizeof h->stats);
+    for (auto *c : h->children) std::memset(&c->stats, 0, sizeof c->stats);
     return PAIRHMM_OK;
 }
 
 int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_reads, const phmm_hap *haps,
                         int n_haps, double *log10_out, uint8_t *rescued_out, pairhmm_cuda_ticket *ticket) {
     if (!h || !ticket) return PAIRHMM_ERR_ARG;
+    if (h->is_multi())
+        return multi_submit(h, RegionView{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr}, ticket);
     auto t0 = clk::now();
     CU(h, cudaSetDevice(h->device));
     int si = !h->slots[0].busy ? 0 : (!h->slots[1].busy ? 1 : -1);
@@ -984,7 +1049,7 @@ int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_re
     }
     RegionView rv{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr};
     int st = submit_chunk(h, h->slots[si], &rv, 1, 1);
-    if (st != PAIRHMM_OK) { h->slots[si].busy = false; return st; }
+    if (st != PAIRHMM_OK) { set_busy(h, h->slots[si], false); return st; }
     h->slot_ticket[si] = *ticket = h->next_ticket++;
     h->stats.calls += 1;
     h->stats.host_ms_total += ms_since(t0);
@@ -993,6 +1058,7 @@ int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_re
 
 int pairhmm_cuda_wait(pairhmm_cuda_handle *h, pairhmm_cuda_ticket ticket) {
     if (!h) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) return multi_wait(h, ticket);
     auto t0 = clk::now();
     if (ticket <= 0 || ticket >= h->next_ticket) return fail(h, PAIRHMM_ERR_STATE, "wait: unknown ticket");
     for (int si = 0; si < 2; ++si)
@@ -1010,15 +1076,24 @@ int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_r
                          int n_haps, double *log10_out, uint8_t *rescued_out) {
     if (!h) return PAIRHMM_ERR_ARG;
     if (n_reads == 0) return PAIRHMM_OK;   // VectorLoglessPairHMM.cpp:46-47
+    if (h->batcher)     // merged with the regions other host threads submit meanwhile (config.batch_window_us)
+        return batcher_compute(h, RegionView{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr});
+    if (h->is_multi() && (int64_t)n_reads * n_haps >= 32768) {      // a region worth several devices: cut by reads
+        const RegionView rv{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr};
+        return multi_compute_batch(h, &rv, 1);
+    }
     pairhmm_cuda_ticket t;
     int st = pairhmm_cuda_submit(h, reads, n_reads, haps, n_haps, log10_out, rescued_out, &t);
     if (st != PAIRHMM_OK) return st;
     return pairhmm_cuda_wait(h, t);
 }
 
+}  // extern "C"
+
 // the batch pipeline over regions of either read kind (RegionView::reads or ::raw)
-static int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions) {
+int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions) {
     if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) return multi_compute_batch(h, regions, n_regions);
     auto t0 = clk::now();
     CU(h, cudaSetDevice(h->device));
     for (int si = 0; si < 2; ++si)
@@ -1072,6 +1147,8 @@ static int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions,
     h->stats.host_ms_total += ms_since(t0);
     return status;
 }
+
+extern "C" {
 
 static std::vector<RegionView> views_of(const phmm_region *regions, int64_t n_regions, phmm_read_summary *const *summaries) {
     std::vector<RegionView> v((size_t)std::max<int64_t>(0, n_regions));
@@ -1290,6 +1367,9 @@ int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_
                                     const pairhmm_cuda_read_model *model, uint8_t *out_base_q, uint8_t *out_ins_q,
                                     uint8_t *out_del_q, uint8_t *out_gcp) {
     if (!h) return PAIRHMM_ERR_ARG;
+    if (h->is_multi())
+        return pairhmm_cuda_prepare_reads_flat(h->children[0], read_bases, base_q, ins_q, del_q, mapq, read_off, read_len, n_reads,
+                                               model, out_base_q, out_ins_q, out_del_q, out_gcp);
     int st = check_read_model(h, model);
     if (st != PAIRHMM_OK) return st;
     if (n_reads < 0 || n_reads > 0x7fffffff) return fail(h, PAIRHMM_ERR_ARG, "bad read count");
@@ -1368,6 +1448,31 @@ int pairhmm_cuda_compute_pairs(pairhmm_cuda_handle *h, const phmm_read *reads, i
     return PAIRHMM_OK;
 }
 
+}  // extern "C"
+
+// stage RegionViews on slot 0 of a single-device handle (H2D + layout); out_off[i] = offset of view i's results in the
+// caller's flat arrays at _resident_fetch
+int phmm::resident_load_views(pairhmm_cuda_handle *h, const RegionView *views, size_t n, const size_t *out_off) {
+    CU(h, cudaSetDevice(h->device));
+    for (int si = 0; si < 2; ++si)
+        if (h->slots[si].busy) { int st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
+    h->resident_loaded = false;
+    Slot &s = h->slots[0];
+    h->no_output_ok = true;
+    int st = pack_chunk(h, s, views, n, pack_threads(h));
+    h->no_output_ok = false;
+    if (st != PAIRHMM_OK) return st;
+    if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
+    CU(h, cudaStreamSynchronize(s.stream));
+    // the views point into the caller's arrays, which may die now: keep only the shapes (plans hold everything scatter needs)
+    for (auto &rv : s.regions) { rv.reads = nullptr; rv.raw = nullptr; rv.haps = nullptr; rv.out = nullptr; rv.resc = nullptr; }
+    h->resident_out_off.assign(out_off, out_off + n);
+    h->resident_loaded = true;
+    return PAIRHMM_OK;
+}
+
+extern "C" {
+
 int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases, const uint8_t *base_q,
                                const uint8_t *ins_q, const uint8_t *del_q, const uint8_t *gcp,
                                const int64_t *read_off, const int32_t *read_len, int64_t n_reads,
@@ -1375,32 +1480,23 @@ int pairhmm_cuda_resident_load(pairhmm_cuda_handle *h, const uint8_t *read_bases
                                int64_t n_haps, const int64_t *reg_read_start, const int64_t *reg_hap_start,
                                int64_t n_regions) {
     if (!h) return PAIRHMM_ERR_ARG;
-    CU(h, cudaSetDevice(h->device));
-    for (int si = 0; si < 2; ++si)
-        if (h->slots[si].busy) { int st = finish_chunk(h, h->slots[si], 1); if (st) return st; h->slot_ticket[si] = 0; }
-    h->resident_loaded = false;
     FlatViews v;
     int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
                               hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, nullptr, nullptr);
     if (st != PAIRHMM_OK) return st;
     std::vector<RegionView> views(n_regions);
-    for (int64_t i = 0; i < n_regions; ++i)
+    std::vector<size_t> out_off((size_t)n_regions + 1, 0);
+    for (int64_t i = 0; i < n_regions; ++i) {
         views[i] = RegionView{v.regions[i].reads, nullptr, v.regions[i].n_reads, v.regions[i].haps, v.regions[i].n_haps, nullptr, nullptr, nullptr};
-    Slot &s = h->slots[0];
-    h->no_output_ok = true;
-    st = pack_chunk(h, s, views.data(), views.size(), pack_threads(h));
-    h->no_output_ok = false;
-    if (st != PAIRHMM_OK) return st;
-    if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
-    CU(h, cudaStreamSynchronize(s.stream));
-    // the views point into `v`, which dies here: keep only the shapes (plans hold everything scatter needs)
-    for (auto &rv : s.regions) { rv.reads = nullptr; rv.haps = nullptr; }
-    h->resident_loaded = true;
-    return PAIRHMM_OK;
+        out_off[(size_t)i + 1] = out_off[(size_t)i] + (size_t)v.regions[i].n_reads * (size_t)v.regions[i].n_haps;
+    }
+    if (h->is_multi()) return multi_resident_load(h, views.data(), views.size());
+    return resident_load_views(h, views.data(), views.size(), out_off.data());
 }
 
 int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms) {
     if (!h) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) return multi_resident_run(h, kernel_ms, float_kernel_ms);
     if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_run: nothing loaded (or the batch was replaced by a later compute call)");
     CU(h, cudaSetDevice(h->device));
     Slot &s = h->slots[0];
@@ -1420,14 +1516,14 @@ int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *f
 
 int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out) {
     if (!h || !log10_out) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) return multi_resident_fetch(h, log10_out, rescued_out);
     if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: nothing loaded (or the batch was replaced by a later compute call)");
     CU(h, cudaSetDevice(h->device));
     Slot &s = h->slots[0];
     if (s.busy) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch: a submitted chunk is in flight on this handle");
-    size_t off = 0;
-    for (auto &rv : s.regions) {
-        rv.out = log10_out + off; rv.resc = rescued_out ? rescued_out + off : nullptr;
-        off += (size_t)rv.n_reads * (size_t)rv.n_haps;
+    for (size_t i = 0; i < s.regions.size(); ++i) {
+        const size_t off = h->resident_out_off[i];
+        s.regions[i].out = log10_out + off; s.regions[i].resc = rescued_out ? rescued_out + off : nullptr;
     }
     int st = download_chunk(h, s);
     if (st != PAIRHMM_OK) return st;
@@ -1443,6 +1539,7 @@ int pairhmm_cuda_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8
 // same order as the results (region-major, read-major). For bit-exactness tests of the FP32 kernel.
 int pairhmm_cuda_resident_fetch_raw(pairhmm_cuda_handle *h, float *fres_out, int64_t n) {
     if (!h || !fres_out) return PAIRHMM_ERR_ARG;
+    if (h->is_multi()) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch_raw: a single-device test hook");
     if (!h->resident_loaded) return fail(h, PAIRHMM_ERR_STATE, "resident_fetch_raw: nothing loaded");
     Slot &s = h->slots[0];
     if (n != (int64_t)s.pairs) return fail(h, PAIRHMM_ERR_ARG, "resident_fetch_raw: n != number of pairs");

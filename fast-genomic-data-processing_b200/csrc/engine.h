@@ -4,7 +4,10 @@
 // and all of gkl_pairhmm's dispatch (M2/intel/pairhmm/IntelPairHmm.cc:259-351).
 #pragma once
 #include <cstdint>
+#include <memory>
 #include <string>
+#include <unordered_map>
+#include <utility>
 #include <vector>
 
 #include "../../include/pairhmm_cuda.h"
@@ -117,6 +120,7 @@ struct Slot {
     uint64_t cells = 0, pairs = 0, reads_in = 0;
     uint64_t cells_swept = 0;         // DP cells the FP32 pass sweeps: unique reads x haplotype columns not shared
     bool busy = false;
+    bool counted = false;             // this chunk is in the device's in-flight count (set_busy)
     bool ep_on = false;               // this chunk runs the fused epilogue (pairhmm_cuda_compute_*_normalized)
     pairhmm_cuda_epilogue ep{};
     bool raw_on = false;              // this chunk holds raw reads: quality pre-pass on the device (pairhmm_cuda_compute_*_raw)
@@ -124,6 +128,41 @@ struct Slot {
     pairhmm_cuda_read_model model{};
     void release();
 };
+
+struct DeviceWorker;     // multi.cu: the host worker thread of one device of a multi-device handle
+struct Batcher;          // batcher.cu: process-wide merger of single-region calls (config.batch_window_us)
+
+// one part of a multi-device plan: reads [first_read, first_read + n_reads) of a region, on device `device`
+struct DevicePart { int64_t region; int32_t first_read, n_reads, device; };
+// LPT split of a batch over n_devices (pairhmm_cuda_device_plan); cost of region r = read_len_sum[r] * hap_len_sum[r]
+std::vector<DevicePart> plan_devices(const uint64_t *read_len_sum, const uint64_t *hap_len_sum, const int32_t *n_reads,
+                                     int64_t n_regions, int n_devices);
+
+// ---- internal entry points shared by engine.cu / multi.cu / batcher.cu (single-device handles) ----
+int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions);
+int resident_load_views(pairhmm_cuda_handle *h, const RegionView *views, size_t n, const size_t *out_off);
+int check_region_args(pairhmm_cuda_handle *h, const RegionView &rv);   // the validation plan_region does, without the plan
+int fail(pairhmm_cuda_handle *h, int status, const std::string &msg);
+int pack_threads(const pairhmm_cuda_handle *h);
+// marks a slot's chunk as in flight / retired and keeps the per-device count of chunks in flight (all handles of the
+// process): the packer shapes a small chunk for latency when the device is otherwise idle and for throughput when other
+// host threads keep it busy
+void set_busy(pairhmm_cuda_handle *h, Slot &s, bool busy);
+int device_chunks_in_flight(int device);
+// multi-device handles (multi.cu)
+int multi_create(pairhmm_cuda_handle *h);
+void multi_destroy(pairhmm_cuda_handle *h);
+int multi_compute_batch(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions);
+int multi_submit(pairhmm_cuda_handle *h, const RegionView &rv, pairhmm_cuda_ticket *ticket);
+int multi_wait(pairhmm_cuda_handle *h, pairhmm_cuda_ticket ticket);
+int multi_resident_load(pairhmm_cuda_handle *h, const RegionView *views, size_t n);
+int multi_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *float_kernel_ms);
+int multi_resident_fetch(pairhmm_cuda_handle *h, double *log10_out, uint8_t *rescued_out);
+void multi_stats(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);
+// shared batcher (batcher.cu): one blocking region of handle h through the process-wide batcher of h's device
+int batcher_compute(pairhmm_cuda_handle *h, const RegionView &rv);
+Batcher *batcher_acquire(pairhmm_cuda_handle *h);
+void batcher_release(Batcher *b);
 
 }  // namespace phmm
 
@@ -145,7 +184,16 @@ struct pairhmm_cuda_handle {
     int64_t slot_ticket[2] = {0, 0};
     cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk (kernels of the next one wait on it)
     bool resident_loaded = false;
+    std::vector<size_t> resident_out_off;  // per region of the resident batch: offset of its results in the caller's arrays
     bool no_output_ok = false;        // resident_load / prepare_reads pack regions without result arrays
+    // ---- multi-device handle (cfg.device_mask != 0): one single-device child handle + one host worker thread per device
+    std::vector<pairhmm_cuda_handle *> children;
+    std::vector<phmm::DeviceWorker *> workers;            // owned (multi_destroy)
+    std::unordered_map<int64_t, std::pair<int, int64_t>> ticket_of;   // ticket of this handle -> (child, child's ticket)
+    int next_child = 0;               // single-region calls go to the devices in turn
+    bool is_multi() const { return !children.empty(); }
+    // ---- shared batcher (cfg.batch_window_us > 0)
+    phmm::Batcher *batcher = nullptr; // process-wide, per device; not owned
     bool ep_on = false;               // set for the duration of a *_normalized call
     pairhmm_cuda_epilogue ep{};
     pairhmm_cuda_read_model model{};  // of the current *_raw call

@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_default_read_model", "pairhmm_cuda_compute_raw", "pairhmm_cuda_compute_batch_raw",
     "pairhmm_cuda_compute_flat_raw", "pairhmm_cuda_prepare_reads_flat",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
-    "pairhmm_cuda_prefix_plan",
+    "pairhmm_cuda_prefix_plan", "pairhmm_cuda_device_plan",
 ]
 MM_COUNT = 8256
 
@@ -39,7 +39,9 @@ class PairHMMError(RuntimeError):
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("use_double", C.c_int32), ("exact_fp32", C.c_int32),
                 ("dedup_reads", C.c_int32), ("pack_threads", C.c_int32), ("chunk_cells", C.c_int64),
-                ("reserved", C.c_int32 * 8)]
+                ("reserved", C.c_int32 * 8),
+                # ABI version 2
+                ("device_mask", C.c_uint32), ("batch_window_us", C.c_int32), ("reserved2", C.c_int32 * 6)]
 
 
 class Stats(C.Structure):
@@ -176,6 +178,25 @@ def prefix_plan(haps, unit_haps=0):
     return {"order": order, "t_start": ts, "restore_slot": rs, "t_save": tv, "save_slot": ss, "shared_cols": int(shared.value)}
 
 
+def device_plan(read_len_sum, hap_len_sum, n_reads, n_devices):
+    """the multi-device LPT plan of a batch (pairhmm_cuda_device_plan; host logic, no device): arrays part_region,
+    part_first_read, part_n_reads, part_device in (region, first read) order"""
+    lib = load_library()
+    rl = np.ascontiguousarray(read_len_sum, np.uint64); hl = np.ascontiguousarray(hap_len_sum, np.uint64)
+    nr = np.ascontiguousarray(n_reads, np.int32)
+    n = len(nr)
+    cap = n + 8 * int(n_devices) * 4 + 16
+    pr = np.zeros(cap, np.int64); pf = np.zeros(cap, np.int32); pn = np.zeros(cap, np.int32); pd = np.zeros(cap, np.int32)
+    got = C.c_int64(0)
+    lib.pairhmm_cuda_device_plan.argtypes = [C.c_void_p] * 3 + [C.c_int64, C.c_int, C.c_int64] + [C.c_void_p] * 4 + [C.POINTER(C.c_int64)]
+    st = lib.pairhmm_cuda_device_plan(rl.ctypes.data, hl.ctypes.data, nr.ctypes.data, n, int(n_devices), cap, pr.ctypes.data,
+                                      pf.ctypes.data, pn.ctypes.data, pd.ctypes.data, C.byref(got))
+    if st != 0:
+        raise PairHMMError(st, "pairhmm_cuda_device_plan")
+    k = int(got.value)
+    return pr[:k], pf[:k], pn[:k], pd[:k]
+
+
 def host_tables():
     """the lookup tables the engine uploads: (ph2pr_f32[128], mm_f32[8256], ph2pr_f64[128], mm_f64[8256])"""
     lib = load_library()
@@ -195,7 +216,7 @@ class Engine:
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
                  chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0,
-                 prefix_sharing=False, unit_haps=0, rescue_pairs_per_unit=0):
+                 prefix_sharing=False, unit_haps=0, rescue_pairs_per_unit=0, device_mask=0, batch_window_us=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
@@ -210,6 +231,8 @@ class Engine:
         cfg.reserved[4] = int(prefix_sharing)
         cfg.reserved[5] = int(unit_haps)       # haplotypes per work unit (tuning / testing)
         cfg.reserved[6] = int(rescue_pairs_per_unit)   # underflowed pairs per FP64 unit (tuning; 0 = by chunk size)
+        cfg.device_mask = int(device_mask)     # != 0: one handle over these CUDA ordinals (multi-GPU inside the library)
+        cfg.batch_window_us = int(batch_window_us)   # > 0: blocking region calls of all such handles share one batcher
         self.h = C.c_void_p()
         st = self.lib.pairhmm_cuda_create(C.byref(cfg), C.byref(self.h))
         if st != 0:

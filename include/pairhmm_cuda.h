@@ -32,7 +32,8 @@
  *
  * Threading: one handle per host thread (as Mutect2Cpp keeps one PairHMM per worker thread,
  * M2/main.cpp:199); calls on different handles are fully concurrent. A handle owns its CUDA
- * streams, pinned staging and device buffers.
+ * streams, pinned staging and device buffers. Host-side packing loops of all handles share one
+ * process-wide pool of worker threads (config.pack_threads bounds a call's share of it).
  */
 #ifndef PAIRHMM_CUDA_H
 #define PAIRHMM_CUDA_H
@@ -43,7 +44,7 @@
 extern "C" {
 #endif
 
-#define PAIRHMM_CUDA_ABI_VERSION 1
+#define PAIRHMM_CUDA_ABI_VERSION 2   /* 2: pairhmm_cuda_config gained device_mask / batch_window_us (multi-GPU handles, shared batcher) */
 
 typedef enum pairhmm_cuda_status {
     PAIRHMM_OK = 0,
@@ -103,6 +104,23 @@ typedef struct pairhmm_cuda_config {
                              /*     FP32 pass; calls with the fused epilogue ignore it. 1 = per launch     */
                              /*     group, only when the plan skips enough cells to pay for the checkpoint  */
                              /*     steps (> 12 %); 2 = always (testing)                                    */
+    /* ---- ABI version 2 ---- */
+    uint32_t device_mask;    /* != 0: a MULTI-DEVICE handle over the CUDA ordinals whose bits are set (`device` is ignored). One process,  */
+                             /*     one handle, as Mutect2Cpp is one process with T threads (M2/main.cpp:199,570-574): a batch call      */
+                             /*     (_compute_batch / _flat / _raw / _normalized) splits its regions over the devices by DP cells with   */
+                             /*     the LPT rule -- whole regions first, a region's reads are cut into parts only when the region        */
+                             /*     exceeds 1 / (4 x devices) of the batch -- one host worker thread, one pinned arena and two slots per  */
+                             /*     device, and every device's results land in the caller's ONE result array (that is the gather;        */
+                             /*     there is no collective: pairs are independent, IntelPairHmm.cc:332-351). Single-region calls         */
+                             /*     (_compute, _submit) go to the devices in turn.                                                       */
+    int32_t batch_window_us; /* > 0: blocking single-region calls (_compute, _compute_raw, _compute_normalized) of ALL handles created   */
+                             /*     with it on one device go through one process-wide batcher: regions submitted by different host      */
+                             /*     threads while the GPU is busy (or within this many microseconds of the first one) are packed into    */
+                             /*     ONE launch group and scattered back per caller -- the counterpart of the reference's cross-thread     */
+                             /*     work sharing (computeLikelihoodsNative_concurrent, IntelPairHmm.cc:296-330;                          */
+                             /*     PairHMMConcurrentControl.h:15-53; the stealing loop M2/main.cpp:396-417). 0 = every handle launches  */
+                             /*     for itself.                                                                                         */
+    int32_t reserved2[6];
 } pairhmm_cuda_config;
 
 typedef struct pairhmm_cuda_stats {
@@ -295,6 +313,18 @@ int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_
                                     const pairhmm_cuda_read_model *model, uint8_t *out_base_q, uint8_t *out_ins_q,
                                     uint8_t *out_del_q, uint8_t *out_gcp);
 
+/* ---- multi-device plan (host logic, no device needed; what a multi-device handle computes for a batch call) ----
+ * Region r has n_reads[r] reads whose lengths sum to read_len_sum[r] and haplotypes whose lengths sum to hap_len_sum[r]
+ * (cost = DP cells = the product). Writes at most max_parts parts in (region, first read) order: part p = reads
+ * [part_first_read[p], + part_n_reads[p]) of region part_region[p] on device part_device[p] (an index into the set bits
+ * of device_mask, lowest first). Regions are split into parts of whole reads only when their cost exceeds
+ * 1 / (4 x n_devices) of the batch. Returns PAIRHMM_ERR_ARG if max_parts is too small. */
+int pairhmm_cuda_device_plan(const uint64_t *read_len_sum, const uint64_t *hap_len_sum, const int32_t *n_reads,
+                             int64_t n_regions, int n_devices, int64_t max_parts, int64_t *part_region,
+                             int32_t *part_first_read, int32_t *part_n_reads, int32_t *part_device, int64_t *n_parts);
+
+/* Statistics. On a multi-device handle the counters are summed over the devices; the three gpu_ms_* and host_ms_pack /
+ * host_ms_scatter are the MAXIMUM over the devices (they work concurrently), host_ms_total is the caller's wall time. */
 int pairhmm_cuda_stats_get(pairhmm_cuda_handle *h, pairhmm_cuda_stats *out);
 int pairhmm_cuda_stats_reset(pairhmm_cuda_handle *h);
 const char *pairhmm_cuda_last_error(pairhmm_cuda_handle *h);

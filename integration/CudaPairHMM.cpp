@@ -9,6 +9,10 @@
 #include "ReadUtils.h"
 
 CudaPairHMM::CudaPairHMM(PairHMMNativeArgumentCollection &args, int device) {
+    // the header this file was compiled against and the library it runs with must agree on the layout of the config struct
+    if (pairhmm_cuda_abi_version() != PAIRHMM_CUDA_ABI_VERSION)
+        throw std::runtime_error("CudaPairHMM: libpairhmm_cuda ABI version " + std::to_string(pairhmm_cuda_abi_version()) +
+                                 ", header version " + std::to_string(PAIRHMM_CUDA_ABI_VERSION));
     // initNative(args.useDoublePrecision, args.pairHmmNativeThreads)   VectorLoglessPairHMM.cpp:14-16
     pairhmm_cuda_config cfg;
     pairhmm_cuda_default_config(&cfg);

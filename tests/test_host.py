@@ -24,7 +24,15 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), "libpairhmm_cuda.so does not export %s" % name
     assert sorted(fgdp_b200.EXPORTED_SYMBOLS) == declared
-    assert lib.pairhmm_cuda_abi_version() == 1
+    assert lib.pairhmm_cuda_abi_version() == 2
+    m = re.search(r"#define PAIRHMM_CUDA_ABI_VERSION (\d+)", hdr)
+    assert m and int(m.group(1)) == 2
+    # the ctypes mirror of pairhmm_cuda_config has the size the library assumes (default_config clears the whole struct)
+    cfg = fgdp_b200.pairhmm.Config()
+    ctypes.memset(ctypes.byref(cfg), 0xff, ctypes.sizeof(cfg))
+    lib.pairhmm_cuda_default_config(ctypes.byref(cfg))
+    assert cfg.device == -1 and cfg.dedup_reads == 1 and cfg.device_mask == 0 and cfg.batch_window_us == 0
+    assert list(cfg.reserved) == [0] * 8 and list(cfg.reserved2) == [0] * 6 and ctypes.sizeof(cfg) == 96
     # include/smithwaterman_cuda.h (the Smith-Waterman entry points live in the same library)
     from fgdp_b200 import smithwaterman
     hdr = open(os.path.join(ROOT, "include", "smithwaterman_cuda.h")).read()
@@ -68,6 +76,40 @@ def test_default_config_and_null_handling():
     assert lib.pairhmm_cuda_create(ctypes.byref(cfg), None) == -1
     assert lib.pairhmm_cuda_initialize(None, 10, 10) == -1
     assert lib.pairhmm_cuda_destroy(None) == 0
+
+
+def test_multi_device_plan_balances_cells_and_keeps_regions_whole():
+    """pairhmm_cuda_device_plan = what a multi-device handle does with a batch: LPT over whole regions, a
+    region is cut into row ranges only when it alone exceeds 1 / (4 x devices) of the batch; every read lands on exactly
+    one device; loads are balanced; one device = identity"""
+    b = synth.config2(400)
+    nr = np.diff(b.reg_read_start).astype(np.int32)
+    rl = np.array([b.read_len[b.reg_read_start[g]:b.reg_read_start[g + 1]].sum() for g in range(b.n_regions)], np.uint64)
+    hl = np.array([b.hap_len[b.reg_hap_start[g]:b.reg_hap_start[g + 1]].sum() for g in range(b.n_regions)], np.uint64)
+    cost = rl.astype(np.float64) * hl.astype(np.float64)
+    pr, pf, pn, pd = fgdp_b200.device_plan(rl, hl, nr, 1)
+    assert np.array_equal(pr, np.arange(b.n_regions)) and not pf.any() and np.array_equal(pn, nr) and not pd.any()
+    for nd in (2, 4, 8):
+        pr, pf, pn, pd = fgdp_b200.device_plan(rl, hl, nr, nd)
+        assert len(pr) == b.n_regions, "400 WES-like regions: none is heavy enough to be cut"
+        assert np.array_equal(pr, np.arange(b.n_regions)) and np.array_equal(pn, nr)
+        load = np.array([cost[pr[pd == d]].sum() for d in range(nd)])
+        assert load.min() > 0 and load.max() / load.mean() < 1.02, load
+    # BASELINE configs[2]: ONE region of 2000 reads x 32 haplotypes -> cut into row ranges that cover every read once
+    c3 = synth.config3()
+    nr3 = np.array([c3.n_reads], np.int32)
+    for nd in (2, 8):
+        pr, pf, pn, pd = fgdp_b200.device_plan(np.array([c3.read_len.sum()], np.uint64), np.array([c3.hap_len.sum()], np.uint64), nr3, nd)
+        assert len(pr) >= 4 * nd and not pr.any()
+        assert pf[0] == 0 and np.array_equal(pf[1:], np.cumsum(pn)[:-1]) and pn.sum() == c3.n_reads and pn.min() > 0
+        per_dev = np.array([pn[pd == d].sum() for d in range(nd)])
+        assert per_dev.max() - per_dev.min() <= c3.n_reads // (4 * nd) + 1, per_dev
+    # a heavy region among light ones, empty regions, zero-length inputs
+    rl2 = np.array([30000, 150, 0, 150, 150], np.uint64); hl2 = np.array([4000, 300, 300, 0, 300], np.uint64)
+    nr2 = np.array([200, 1, 0, 1, 1], np.int32)
+    pr, pf, pn, pd = fgdp_b200.device_plan(rl2, hl2, nr2, 4)
+    assert (pr == 0).sum() >= 4 and pn[pr == 0].sum() == 200 and set(pr.tolist()) == {0, 1, 2, 3, 4}
+    assert len(fgdp_b200.device_plan(np.zeros(0, np.uint64), np.zeros(0, np.uint64), np.zeros(0, np.int32), 8)[0]) == 0
 
 
 def test_lpt_shard_balances_cells():

@@ -11,6 +11,7 @@ cp -r $root/fast-genomic-data-processing_b200/csrc $d/pkg/csrc && rm -rf $d/pkg/
 cp $root/include/*.h $d/include/
 cd $d/pkg/csrc
 bash -c "$cmd"
-PHMM_GEN_ONLY=${PHMM_GEN_ONLY:-f32_pk_w16_k8_10,f64_pk_w32_k1_7,f64_gen_w32_k1_8,f32_gen_w32_k1_8} python gen_inst.py >/dev/null
+export PHMM_GEN_ONLY=${PHMM_GEN_ONLY:-f32_pk_w16_k8_10,f64_pk_w32_k1_7,f64_gen_w32_k1_8,f32_gen_w32_k1_8}
+rm -f .gen.stamp     # csrc/Makefile regenerates the instantiation units (only those named above)
 make -s -j16 DEFS="$defs" OUT=$root/fast-genomic-data-processing_b200/libpairhmm_cuda_$name.so
 ls -la $root/fast-genomic-data-processing_b200/libpairhmm_cuda_$name.so
