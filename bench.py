@@ -52,6 +52,9 @@ def parse_args():
                          "one rescue-heavy region; long haplotypes), every rank the same batch")
     ap.add_argument("--cpu-sample-regions", type=int, default=0, help="regions in the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strong-regions", type=int, default=25000,
+                    help="regions of the strong-scaling job in the `strong` block (BASELINE configs[4] = 25000); 0 = no strong block")
+    ap.add_argument("--strong-steps", type=int, default=2)
     return ap.parse_args()
 
 
@@ -131,6 +134,91 @@ def cpu_reference_run(batch, threads, want_seconds=None):
                       % (batch.n_regions, batch.n_pairs, cells)}
 
 
+def parity_gate(batch, n_reg, out, rs, cpu, threads):
+    """the correctness gate of this very run. The engine's end-to-end results on the CPU sample's pairs
+    (the first n_reg regions of the batch) against the CPU reference's: |dlog10| over every pair, the rescue set over
+    EVERY pair of the sample, and the threshold-ambiguous pairs -- those on which the reference built with its default
+    -ffp-contract (FMA in the AVX-512 objects: the canonical build) and built -ffp-contract=off disagree about
+    `float sum < 1e-28f` (MIN_ACCEPTED, pairhmm_common.h:41); for each, which side the GPU took."""
+    import oracle_py
+    n_s = cpu["log10"].shape[0]
+    sub_flat = cpu["flat"]
+    _, want_resc, _ = cpu["lib"].compute(sub_flat, threads=threads)
+    fin = np.isfinite(cpu["log10"])
+    d = np.abs(out[:n_s][fin] - cpu["log10"][fin])
+    parity = {"pairs": int(n_s), "max_abs_dlog10": float(d.max()) if d.size else 0.0,
+              "mean_abs_dlog10": float(d.mean()) if d.size else 0.0, "tolerance": 1e-4,
+              "nonfinite_pattern_identical": bool(np.array_equal(np.isfinite(out[:n_s]), fin)),
+              "rescue_set_identical": bool(np.array_equal(rs[:n_s], want_resc)),
+              "rescue_set_pairs_checked": int(n_s), "rescued_pairs": int(want_resc.sum()), "against": cpu["kind"]}
+    if cpu["kind"] == "reference" and oracle_py.reference_nofma_available():
+        _, resc_nofma, _ = oracle_py.load_reference_nofma().compute(sub_flat, threads=threads)
+        amb = np.nonzero(want_resc != resc_nofma)[0]
+        parity["threshold_ambiguous"] = {"pairs": int(amb.size),
+                                         "gpu_sides_with_canonical_build": int((rs[:n_s][amb] == want_resc[amb]).sum()),
+                                         "definition": "reference default build (FMA-contracted) vs -ffp-contract=off disagree on float sum < 1e-28f"}
+    return parity
+
+
+def strong_block(args, world, peaks_sm_mhz):
+    """BASELINE configs[4] as north_star states it: the WHOLE chr20-scale job (regions x 200 reads x 10 haplotypes) handed to
+    the library in ONE call on ONE multi-device handle (config.device_mask over the `world` GPUs of the box); the library
+    LPT-splits the regions over the devices by DP cells, every device's results land in the caller's one host matrix. One
+    process, T host threads -- Mutect2Cpp's own execution model (M2/main.cpp:199,570-574). Run by rank 0 alone; under
+    torchrun the other ranks wait on a CPU (gloo) barrier meanwhile."""
+    import hashlib
+    import fgdp_b200
+    from fgdp_b200 import synth
+    t0 = time.perf_counter()
+    job = synth.generate_parallel("c5", args.strong_regions)
+    gen_s = time.perf_counter() - t0
+    cells, pairs = job.cells(), job.n_pairs
+    eng = fgdp_b200.Engine(device_mask=(1 << world) - 1)
+    eng.initialize(int(job.read_len.max()), int(job.hap_len.max()))
+    out = np.zeros(pairs, np.float64); rs = np.zeros(pairs, np.uint8)
+    eng.compute_batch(job, out, rs)                               # warm-up: buffers, pinned arenas
+    eng.stats_reset()
+    t0 = time.perf_counter()
+    for _ in range(args.strong_steps):
+        eng.compute_batch(job, out, rs)
+    e2e_s = (time.perf_counter() - t0) / args.strong_steps
+    st = eng.stats()
+    # device-resident replay of the same split: kernels only, max over the devices (they run side by side)
+    eng.resident_load(job)
+    eng.resident_run()
+    ms = 0.0
+    for _ in range(args.strong_steps):
+        a, _ = eng.resident_run()
+        ms += a
+    ms /= args.strong_steps
+    got, gresc = eng.resident_fetch()
+    same = bool(np.array_equal(got, out) and np.array_equal(gresc, rs))
+    eng.close()
+    # identity with a single-device handle on the first regions of the job (the whole job when it is small)
+    n_chk = min(job.n_regions, 1500)
+    sub = job.subset(range(n_chk))
+    one = fgdp_b200.Engine(device=0)
+    o1, r1 = one.compute_batch(sub)
+    one.close()
+    n1 = sub.n_pairs
+    return {"workload": "BASELINE configs[4]: chr20-scale synthetic batch, %d regions x 200 reads x 10 haps, 150 bp reads, "
+                        "300-500 bp haps (%d pairs, %.4g cells): ONE pairhmm_cuda_compute_flat call on ONE multi-device handle, "
+                        "regions LPT-split over %d GPU(s) inside the library, results gathered in one host matrix"
+                        % (job.n_regions, pairs, cells, world),
+            "scaling": "strong", "n_gpus": world, "steps": args.strong_steps,
+            "value": cells / (ms * 1e-3) / 1e9, "ms_per_step": ms,
+            "e2e": {"value": cells / e2e_s / 1e9, "unit": "GCUPS", "ms_per_step": e2e_s * 1e3,
+                    "h2d_bytes_per_step": st["h2d_bytes"] // args.strong_steps, "d2h_bytes_per_step": st["d2h_bytes"] // args.strong_steps,
+                    "host_pack_ms_per_step_max_over_devices": st["host_ms_pack"] / args.strong_steps,
+                    "gpu_ms_per_step_max_over_devices": st["gpu_ms_total"] / args.strong_steps},
+            "unit": "GCUPS", "rescued_frac": float(rs.mean()),
+            "resident_run_identical_to_e2e": same,
+            "identical_to_single_device_handle": bool(np.array_equal(out[:n1], o1) and np.array_equal(rs[:n1], r1)),
+            "single_device_check_pairs": int(n1),
+            "result_sha256": hashlib.sha256(out.tobytes() + rs.tobytes()).hexdigest()[:32],
+            "host_threads": os.cpu_count(), "generate_s": gen_s}
+
+
 def run_reference_arm(args, rank, world):
     """--impl reference: the reference's CPU implementation on this box's host cores, bounded sample per step."""
     if rank != 0:
@@ -139,7 +227,7 @@ def run_reference_arm(args, rank, world):
     threads = os.cpu_count() or 1
     n_reg = args.cpu_sample_regions or 160       # ~1.8e10 cells: a few seconds per step on 16 AVX-512 threads
     sample = synth.config2(args.regions).subset(range(n_reg)) if args.regions <= 2000 else synth.config2(n_reg)
-    for _ in range(max(0, min(args.warmup, 1))):
+    for _ in range(max(0, args.warmup)):          # exactly the W warm-up passes the line reports
         cpu_reference_run(sample, threads)
     secs, res = 0.0, None
     for _ in range(args.steps):
@@ -180,6 +268,9 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # control-plane barrier on the CPU: ranks that wait while rank 0 runs the single-process strong block must not sit
+        # in a kernel on their GPU
+        cpu_group = dist.new_group(backend="gloo")
 
     def barrier():
         if dist is not None:
@@ -222,9 +313,10 @@ def main():
                     "haplotypes of 300 bases that differ by 1-3 SNVs, 150 bp reads, per GPU; prefix sharing on" % args.regions)
     elif world > 1:
         _, _, cost = synth.config2_shapes(args.regions * world)
-        batch = synth.config2(args.regions * world, select=synth.lpt_shard(cost, world)[rank])
+        batch = synth.generate_parallel("c2", args.regions * world, procs=max(1, min(16, (os.cpu_count() or 8) // world)),
+                                        select=synth.lpt_shard(cost, world)[rank])
     else:
-        batch = synth.config2(args.regions)
+        batch = synth.generate_parallel("c2", args.regions)
     if args.workload == "c2":
         workload = ("BASELINE configs[1]: synthetic WES-like batch, %d regions, ~200 reads x 4-16 haps, "
                     "150 bp reads, 250-500 bp haps, per GPU" % args.regions)
@@ -264,10 +356,28 @@ def main():
         eng.compute_batch(batch, out, rs)
     e2e_s = reduce_max((time.perf_counter() - t0) / args.steps)
     barrier()
-    sampler.stop()
     st = eng.stats()
+    # a step shorter than the 200 ms sampling tick (configs[0] is 0.08 ms) leaves no clock record: keep the same step
+    # running, untimed, until the sampler has seen the device under this load
+    clock_extra = 0
+    t_clk = time.perf_counter()
+    while len(sampler.rows) < 5 and time.perf_counter() - t_clk < 3.0:
+        eng.compute_batch(batch, out, rs); clock_extra += 1
+    sampler.stop()
     same = bool(np.array_equal(out, got) and np.array_equal(rs, resc))
     e2e_value = total_cells / e2e_s / 1e9
+    eng.close()
+
+    # ---- strong scaling as north_star states it: one job, one multi-device handle, one host matrix (rank 0 only)
+    strong = None
+    if args.workload == "c2" and args.strong_regions > 0:
+        if rank == 0:
+            try:
+                strong = strong_block(args, world, None)
+            except Exception as ex:      # noqa: BLE001 -- the headline line must still be printed
+                strong = {"error": "%s: %s" % (type(ex).__name__, ex)}
+        if dist is not None:
+            dist.barrier(group=cpu_group)
 
     if dist is not None:
         dist.barrier()
@@ -325,16 +435,7 @@ def main():
         # number has its counterpart), and the correctness gate of this very run: the engine's results on the sample's
         # pairs (the first regions of the batch) against the CPU reference's
         _, _, secs_pre = cpu["lib"].compute(cpu["flat"], threads=threads, tables_in_timed_region=False, want_rescued=False)
-        n_s = cpu["log10"].shape[0]
-        gate_regions = min(n_reg, 24)
-        sub = batch.subset(range(gate_regions))
-        _, want_resc, _ = cpu["lib"].compute(sub.as_flat(), threads=threads)
-        n_g = sub.n_pairs
-        fin = np.isfinite(cpu["log10"])
-        parity = {"pairs": int(n_s), "max_abs_dlog10": float(np.abs(out[:n_s][fin] - cpu["log10"][fin]).max()),
-                  "mean_abs_dlog10": float(np.abs(out[:n_s][fin] - cpu["log10"][fin]).mean()),
-                  "tolerance": 1e-4, "rescue_set_identical": bool(np.array_equal(rs[:n_g], want_resc)),
-                  "rescue_set_pairs_checked": int(n_g), "against": cpu["kind"]}
+        parity = parity_gate(batch, n_reg, out, rs, cpu, threads)
         cpu["value_tables_prebuilt"] = cpu["cells"] / secs_pre / 1e9
         cpu = {k: cpu[k] for k in ("value", "value_tables_prebuilt", "unit", "cores", "kind", "isa", "sample")}
     in_bytes = batch.read_bases.nbytes * 5 + batch.hap_bases.nbytes * 4
@@ -353,6 +454,10 @@ def main():
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks}
     if cpu is not None:
         line["parity"] = parity
+    if clock_extra:
+        line["clocks"]["window"] = "timed region + %d further untimed passes of the same step (the timed steps are shorter than the 200 ms sampling tick)" % clock_extra
+    if strong is not None:
+        line["strong"] = strong
     print(json.dumps(line), flush=True)
     del ctypes
 

@@ -44,7 +44,8 @@ template <class T> void DevBuf<T>::release() { if (p && !view) cudaFree(p); p = 
 void Slot::release() {
     h_meta.release(); d_meta.release();
     h_rd.release(); h_hapbytes.release(); h_flag.release(); h_reads.release(); h_haps.release();
-    h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); d_long_scratch.release(); h_units.release(); h_out.release(); h_rescue_base.release();
+    h_hapoff.release(); h_haplist.release(); h_happlan.release(); d_happlan.release(); d_long_scratch.release(); h_units.release(); h_out.release();
+    h_counters.release(); h_res.release(); d_res.release();
     h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
@@ -515,31 +516,6 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     s.n_uniq = nu; s.n_haps = nh; s.n_hap_words = hw; s.n_haplist = hl; s.n_upairs = up; s.hap_bytes = hbytes;
     s.cells = cells; s.pairs = pairs; s.reads_in = reads_in; s.cells_swept = swept;
 
-    cudaError_t e;
-#define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
-    RES(h_rd, s.plane * 5 + 16); RES(h_out, up + 1); RES(h_flag, up + 1);
-    RES(h_rescue_base, kNumBinsW32 + 1);
-    {   // one arena for everything small that goes to the device, same layout on both sides (256-byte aligned parts)
-        const bool pfx = s.float_variant == Variant::F32_PFX;
-        uint64_t off = 0;
-        auto part = [&](uint64_t bytes) { const uint64_t o = off; off = (off + bytes + 255) & ~255ull; return o; };
-        const uint64_t o_reads = part(sizeof(DevRead) * ((uint64_t)nu + 1)), o_hapoff = part(sizeof(uint64_t) * ((uint64_t)nh + 1)),
-                       o_haps = part(sizeof(DevHap) * ((uint64_t)nh + 1)), o_haplist = part(sizeof(uint32_t) * ((uint64_t)hl + 1)),
-                       o_happlan = part(pfx ? sizeof(uint2) * ((uint64_t)hl + 1) : 0), o_units = part(sizeof(DevUnit) * ((uint64_t)n_units + 1)),
-                       o_hapbytes = part(hbytes + 16);
-        s.meta_bytes = off;
-        RES(h_meta, off); RES(d_meta, off);
-        s.h_reads.set_view(s.h_meta.p + o_reads); s.d_reads.set_view(s.d_meta.p + o_reads);
-        s.h_hapoff.set_view(s.h_meta.p + o_hapoff); s.d_hapoff.set_view(s.d_meta.p + o_hapoff);
-        s.h_haps.set_view(s.h_meta.p + o_haps); s.d_haps.set_view(s.d_meta.p + o_haps);
-        s.h_haplist.set_view(s.h_meta.p + o_haplist); s.d_haplist.set_view(s.d_meta.p + o_haplist);
-        s.h_happlan.set_view(s.h_meta.p + o_happlan); s.d_happlan.set_view(s.d_meta.p + o_happlan);
-        s.h_units.set_view(s.h_meta.p + o_units); s.d_units.set_view(s.d_meta.p + o_units);
-        s.h_hapbytes.set_view(s.h_meta.p + o_hapbytes); s.d_hapbytes.set_view(s.d_meta.p + o_hapbytes);
-    }
-    std::memcpy(s.h_rescue_base.p, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
-    RES(d_rd, s.plane * 5 + 16); RES(d_out, up + 1); RES(d_flag, up + 1);
-    RES(d_counters, kCounterWords); RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
     s.ep_on = h->ep_on; s.ep = h->ep;
     s.raw_on = chunk_raw; s.model = h->model; s.raw_indel_q = false;
     for (size_t i = 0; i < n_regs; ++i) {
@@ -547,8 +523,52 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             return fail(h, PAIRHMM_ERR_ARG, "raw and processed reads mixed in one call");
         s.raw_indel_q |= s.plans[i].any_indel_q;
     }
-    if (s.raw_on) { RES(h_mapq, nu + 1); RES(d_mapq, nu + 1); }
-    if (s.ep_on) { RES(h_rows, nu + 1); RES(d_rows, nu + 1); RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
+    // read planes that cross PCIe: raw reads send bases + base qualities (+ their own indel qualities if any read has them),
+    // processed reads all but the gcp plane when the kernels take the penalty as a constant
+    s.sent_planes = s.raw_on ? (s.raw_indel_q ? 4 : 2) : (s.skip_gcp ? 4 : 5);
+
+    cudaError_t e;
+#define RES(buf, n) if ((e = s.buf.reserve(n)) != cudaSuccess) return fail_cuda(h, e, "reserve " #buf)
+    {   // ONE arena for everything that goes to the device, same layout on both sides (256-byte aligned parts): descriptors,
+        // haplotype bytes, work units, the counter block (zeroed work queues + the rescue list bases), per-read side tables
+        // and, last, the read planes -- a chunk crosses PCIe in ONE copy (a per-region call once made nine driver calls
+        // here; with T host threads the driver's lock, not the GPU, was what a region call waited for). The device arena
+        // has room for all five planes, the host arena for the planes that are sent.
+        const bool pfx = s.float_variant == Variant::F32_PFX;
+        uint64_t off = 0;
+        auto part = [&](uint64_t bytes) { const uint64_t o = off; off = (off + bytes + 255) & ~255ull; return o; };
+        const uint64_t o_reads = part(sizeof(DevRead) * ((uint64_t)nu + 1)), o_hapoff = part(sizeof(uint64_t) * ((uint64_t)nh + 1)),
+                       o_haps = part(sizeof(DevHap) * ((uint64_t)nh + 1)), o_haplist = part(sizeof(uint32_t) * ((uint64_t)hl + 1)),
+                       o_happlan = part(pfx ? sizeof(uint2) * ((uint64_t)hl + 1) : 0), o_units = part(sizeof(DevUnit) * ((uint64_t)n_units + 1)),
+                       o_hapbytes = part(hbytes + 16), o_ctr = part(sizeof(uint32_t) * kCounterWords),
+                       o_mapq = part(s.raw_on ? sizeof(int32_t) * ((uint64_t)nu + 1) : 0),
+                       o_rows = part(s.ep_on ? sizeof(RowInfo) * ((uint64_t)nu + 1) : 0), o_rd = part(0);
+        s.meta_bytes = o_rd + s.plane * (uint64_t)s.sent_planes;
+        s.ctr_off = o_ctr;
+        RES(h_meta, s.meta_bytes + 16); RES(d_meta, o_rd + s.plane * 5 + 16);
+        s.h_reads.set_view(s.h_meta.p + o_reads); s.d_reads.set_view(s.d_meta.p + o_reads);
+        s.h_hapoff.set_view(s.h_meta.p + o_hapoff); s.d_hapoff.set_view(s.d_meta.p + o_hapoff);
+        s.h_haps.set_view(s.h_meta.p + o_haps); s.d_haps.set_view(s.d_meta.p + o_haps);
+        s.h_haplist.set_view(s.h_meta.p + o_haplist); s.d_haplist.set_view(s.d_meta.p + o_haplist);
+        s.h_happlan.set_view(s.h_meta.p + o_happlan); s.d_happlan.set_view(s.d_meta.p + o_happlan);
+        s.h_units.set_view(s.h_meta.p + o_units); s.d_units.set_view(s.d_meta.p + o_units);
+        s.h_hapbytes.set_view(s.h_meta.p + o_hapbytes); s.d_hapbytes.set_view(s.d_meta.p + o_hapbytes);
+        s.h_counters.set_view(s.h_meta.p + o_ctr); s.d_counters.set_view(s.d_meta.p + o_ctr);
+        s.h_mapq.set_view(s.h_meta.p + o_mapq); s.d_mapq.set_view(s.d_meta.p + o_mapq);
+        s.h_rows.set_view(s.h_meta.p + o_rows); s.d_rows.set_view(s.d_meta.p + o_rows);
+        s.h_rd.set_view(s.h_meta.p + o_rd); s.d_rd.set_view(s.d_meta.p + o_rd);
+        std::memset(s.h_counters.p, 0, sizeof(uint32_t) * kCounterWords);
+        std::memcpy(s.h_counters.p + kRescueBaseDev, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
+    }
+    {   // results: the log10 values and, behind them, the rescued flags -- one buffer on either side, ONE copy back
+        const uint64_t flag_off = sizeof(double) * ((uint64_t)up + 1);
+        s.res_bytes = flag_off + (uint64_t)up + 1;
+        RES(h_res, s.res_bytes); RES(d_res, s.res_bytes);
+        s.h_out.set_view(s.h_res.p); s.d_out.set_view(s.d_res.p);
+        s.h_flag.set_view(s.h_res.p + flag_off); s.d_flag.set_view(s.d_res.p + flag_off);
+    }
+    RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+    if (s.ep_on) { RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
     const double ms_reserve = ms_since(t0);
@@ -643,22 +663,13 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
 // H2D of a packed chunk + haplotype word expansion. Asynchronous on the slot's stream.
 int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
     cudaStream_t st = s.stream;
-    const uint32_t n_units = s.bin_start[kNumBins + 1];
-    uint64_t plane_bytes = s.plane * (s.skip_gcp ? 4 : 5);
-    if (s.n_uniq && !s.raw_on) {
-        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, plane_bytes, cudaMemcpyHostToDevice, st));
-    }
-    // descriptors, haplotype bytes and work units: one copy of the arena
+    // descriptors, haplotype bytes, work units, counters, side tables and the read planes: one copy of the arena
     if (s.meta_bytes) CU(h, cudaMemcpyAsync(s.d_meta.p, s.h_meta.p, s.meta_bytes, cudaMemcpyHostToDevice, st));
     if (s.n_uniq && s.raw_on) {
         // raw reads: bases + base qualities (+ insertion / deletion qualities if any read has them) cross PCIe; the default
         // indel qualities (ReadUtils.h:40) and the constant gap-continuation plane are written here
-        const int np = s.raw_indel_q ? 4 : 2;
-        plane_bytes = s.plane * (uint64_t)np + sizeof(int32_t) * (uint64_t)s.n_uniq;
-        CU(h, cudaMemcpyAsync(s.d_rd.p, s.h_rd.p, s.plane * (uint64_t)np, cudaMemcpyHostToDevice, st));
         if (!s.raw_indel_q) CU(h, cudaMemsetAsync(s.d_rd.p + 2 * s.plane, 45, 2 * s.plane, st));
         CU(h, cudaMemsetAsync(s.d_rd.p + 4 * s.plane, s.model.constant_gcp & 0xff, s.plane, st));
-        CU(h, cudaMemcpyAsync(s.d_mapq.p, s.h_mapq.p, sizeof(int32_t) * s.n_uniq, cudaMemcpyHostToDevice, st));
         PrepReadsArgs pa{};
         pa.rd = s.d_rd.p; pa.plane = s.plane; pa.reads = s.d_reads.p; pa.mapq = s.d_mapq.p; pa.n = s.n_uniq;
         pa.pcr_on = s.model.pcr_rate_factor > 0; pa.base_q_threshold = s.model.base_quality_threshold;
@@ -666,13 +677,9 @@ int upload_chunk(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, launch_prep_reads(pa, h->sm_count, st));
         h->stats.kernel_launches += 1;
     }
-    if (s.ep_on && s.n_uniq) {
-        CU(h, cudaMemcpyAsync(s.d_rows.p, s.h_rows.p, sizeof(RowInfo) * s.n_uniq, cudaMemcpyHostToDevice, st));
-        h->stats.h2d_bytes += sizeof(RowInfo) * (uint64_t)s.n_uniq;
-    }
     CU(h, launch_prep_haps(s.d_hapbytes.p, s.d_hapoff.p, s.d_haps.p, s.n_haps, s.d_hapw.p, st));
     h->stats.kernel_launches += 1;
-    h->stats.h2d_bytes += plane_bytes + s.meta_bytes;
+    h->stats.h2d_bytes += s.meta_bytes;
     return PAIRHMM_OK;
 }
 
@@ -684,16 +691,17 @@ static int blocks_for(pairhmm_cuda_handle *h, Variant v, int bin) {
     return n;
 }
 
-int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
+int run_kernels(pairhmm_cuda_handle *h, Slot &s, bool replay) {
     cudaStream_t st = s.stream;
-    CU(h, cudaMemsetAsync(s.d_counters.p, 0, sizeof(uint32_t) * kZeroedWords, st));
-    CU(h, cudaMemcpyAsync(s.d_counters.p + kRescueBaseDev, s.h_rescue_base.p, sizeof(uint32_t) * (kNumBinsW32 + 1),
-                          cudaMemcpyHostToDevice, st));
+    // the counter block (zeroed work queues, rescue list bases) came with the arena; a resident replay sends it again
+    if (replay) CU(h, cudaMemcpyAsync(s.d_counters.p, s.h_counters.p, sizeof(uint32_t) * kCounterWords, cudaMemcpyHostToDevice, st));
+    static const bool force_timing = std::getenv("PAIRHMM_CUDA_TIMING") != nullptr;
+    s.timed = !h->light_call || force_timing || trace_on();
     // The two slots' kernels must not share the GPU: run side by side they finish together, both slots come free at the
     // same moment and the GPU idles while the host packs. Chained on the previous chunk's end event, chunk i is done
     // (and its slot reusable) while chunk i+1 still computes; the copies in front of this point are not held back.
     if (h->prev_end && h->prev_end != s.ev_end) CU(h, cudaStreamWaitEvent(st, h->prev_end, 0));
-    CU(h, cudaEventRecord(s.ev_begin, st));
+    if (s.timed) CU(h, cudaEventRecord(s.ev_begin, st));
     const HostTables &t = host_tables();
     KernelArgs a{};
     a.rd = s.d_rd.p; a.plane = s.plane; a.reads = s.d_reads.p; a.hapw = s.d_hapw.p; a.haps = s.d_haps.p;
@@ -713,7 +721,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         const uint64_t full = (uint64_t)h->sm_count * (uint64_t)blocks_for(h, v, bin);
         return (int)std::min<uint64_t>(full, (work_items + 3) / 4);
     };
-    if (all_double) CU(h, cudaEventRecord(s.ev_fwd_done, st));
+    if (all_double && s.timed) CU(h, cudaEventRecord(s.ev_fwd_done, st));
     if (!all_double) {
         a.ph2pr = h->d_ph2pr_f; a.mm = h->d_mm_f;
         for (int b = 0; b < kNumBins; ++b) {
@@ -725,7 +733,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
             CU(h, launch_forward(vf, W, K, KL, a, grid_for(vf, b, n), st));
             h->stats.kernel_launches += 1;
         }
-        CU(h, cudaEventRecord(s.ev_fwd_done, st));
+        if (s.timed) CU(h, cudaEventRecord(s.ev_fwd_done, st));
         FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f, s.d_counters.p + kRescuedPairs};
         CU(h, launch_finalize(f, st));
         if (s.n_upairs) h->stats.kernel_launches += 1;
@@ -737,7 +745,7 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s) {
         CU(h, launch_rescue_scan(r, st));
         if (r.n_units) h->stats.kernel_launches += 1;
     }
-    CU(h, cudaEventRecord(s.ev_float_done, st));
+    if (s.timed) CU(h, cudaEventRecord(s.ev_float_done, st));
     a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
     a.rescue_filter = all_double ? 0u : 1u;
     for (int b = 0; b < kNumBinsW32; ++b) {
@@ -796,8 +804,8 @@ namespace phmm {
 // D2H of results; asynchronous.
 int download_chunk(pairhmm_cuda_handle *h, Slot &s) {
     if (s.n_upairs) {
-        CU(h, cudaMemcpyAsync(s.h_out.p, s.d_out.p, sizeof(double) * s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
-        CU(h, cudaMemcpyAsync(s.h_flag.p, s.d_flag.p, s.n_upairs, cudaMemcpyDeviceToHost, s.stream));
+        // log10 values and rescued flags lie in one buffer: one copy (the few bytes between them included)
+        CU(h, cudaMemcpyAsync(s.h_res.p, s.d_res.p, s.res_bytes - 1, cudaMemcpyDeviceToHost, s.stream));
         h->stats.d2h_bytes += (sizeof(double) + 1) * (uint64_t)s.n_upairs;
     }
     if (s.ep_on && s.n_uniq) {
@@ -811,9 +819,12 @@ int download_chunk(pairhmm_cuda_handle *h, Slot &s) {
 // (VectorLoglessPairHMM.cpp:123-125: read-major, duplicates share their unique read's row).
 int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     CU(h, cudaStreamSynchronize(s.stream));
+    if (h->prev_end == s.ev_end) h->prev_end = nullptr;      // retired: the next chunk has nothing to wait for
     float ms_f = 0.f, ms_all = 0.f;
-    cudaEventElapsedTime(&ms_f, s.ev_begin, s.ev_float_done);
-    cudaEventElapsedTime(&ms_all, s.ev_begin, s.ev_end);
+    if (s.timed) {
+        cudaEventElapsedTime(&ms_f, s.ev_begin, s.ev_float_done);
+        cudaEventElapsedTime(&ms_all, s.ev_begin, s.ev_end);
+    }
     if (trace_on() && g_trace_base) {
         float b0 = 0.f, b1 = 0.f;
         cudaEventElapsedTime(&b0, g_trace_base, s.ev_begin); cudaEventElapsedTime(&b1, g_trace_base, s.ev_end);
@@ -882,7 +893,7 @@ int submit_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t
     if (st != PAIRHMM_OK) return st;
     set_busy(h, s, true);
     if ((st = upload_chunk(h, s)) != PAIRHMM_OK) return st;
-    if ((st = run_kernels(h, s)) != PAIRHMM_OK) return st;
+    if ((st = run_kernels(h, s, false)) != PAIRHMM_OK) return st;
     return download_chunk(h, s);
 }
 
@@ -986,7 +997,7 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
         if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreate(&s.ev_begin) != cudaSuccess || cudaEventCreate(&s.ev_float_done) != cudaSuccess ||
             cudaEventCreate(&s.ev_fwd_done) != cudaSuccess ||
-            cudaEventCreate(&s.ev_end) != cudaSuccess || s.d_counters.reserve(kCounterWords) != cudaSuccess)
+            cudaEventCreate(&s.ev_end) != cudaSuccess)
             return bail(PAIRHMM_ERR_CUDA);
     }
     if (forward_blocks_per_sm(Variant::F32_GEN, 32, 1, 0) < 1) return bail(PAIRHMM_ERR_CUDA);   // kernels loadable?
@@ -1048,7 +1059,9 @@ int pairhmm_cuda_submit(pairhmm_cuda_handle *h, const phmm_read *reads, int n_re
         h->slot_ticket[si] = 0;
     }
     RegionView rv{reads, nullptr, n_reads, haps, n_haps, log10_out, rescued_out, nullptr};
+    h->light_call = true;
     int st = submit_chunk(h, h->slots[si], &rv, 1, 1);
+    h->light_call = false;
     if (st != PAIRHMM_OK) { set_busy(h, h->slots[si], false); return st; }
     h->slot_ticket[si] = *ticket = h->next_ticket++;
     h->stats.calls += 1;
@@ -1501,7 +1514,7 @@ int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *f
     CU(h, cudaSetDevice(h->device));
     Slot &s = h->slots[0];
     if (s.busy) return fail(h, PAIRHMM_ERR_STATE, "resident_run: a submitted chunk is in flight on this handle");
-    int st = run_kernels(h, s);
+    int st = run_kernels(h, s, true);
     if (st != PAIRHMM_OK) return st;
     CU(h, cudaStreamSynchronize(s.stream));
     float a = 0.f, b = 0.f;

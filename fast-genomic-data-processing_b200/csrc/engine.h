@@ -82,7 +82,14 @@ struct Slot {
     // h_units, h_hapbytes and their device mirrors) are views into one pinned / one device arena with the same layout:
     // they cross PCIe in ONE copy (a per-region call made seven of them)
     PinnedBuf<uint8_t> h_meta;
-    uint64_t meta_bytes = 0;          // used bytes of the arena
+    uint64_t meta_bytes = 0;          // bytes of the arena that cross PCIe (everything up to the last sent read plane)
+    uint64_t ctr_off = 0;             // offset of the counter block inside the arena (resident replays re-send it)
+    int sent_planes = 5;              // read planes that are staged and sent
+    PinnedBuf<uint32_t> h_counters;   // view: zeroed work queues / rescue counts + the rescue list bases
+    PinnedBuf<uint8_t> h_res;         // results: doubles, then the rescued flags (h_out / h_flag are views)
+    DevBuf<uint8_t> d_res;
+    uint64_t res_bytes = 0;
+    bool timed = false;               // this chunk's kernels are bracketed by timing events
     PinnedBuf<DevUnit> h_units;
     PinnedBuf<double> h_out;
     PinnedBuf<int32_t> h_mapq;        // raw reads: mapping quality per unique read
@@ -112,7 +119,6 @@ struct Slot {
     uint64_t hap_bytes = 0;
     uint32_t bin_start[kNumBins + 2] = {0};   // units of bin b are [bin_start[b], bin_start[b+1]); bin kLongBin = long reads (long.cu)
     uint32_t rescue_base[kNumBinsW32 + 1] = {0}; // W=32 bin b appends its rescue units at d_rescue + rescue_base[b]
-    PinnedBuf<uint32_t> h_rescue_base;        // the same, staged for the device
     Variant float_variant = Variant::F32_GEN; // kernels this chunk was binned for
     bool uniform_gcp = false;                 // every gcp byte of the chunk equals gcp_value -> UG kernels
     uint8_t gcp_value = 0;
@@ -182,7 +188,9 @@ struct pairhmm_cuda_handle {
     phmm::Slot slots[2];
     int64_t next_ticket = 1;
     int64_t slot_ticket[2] = {0, 0};
-    cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk (kernels of the next one wait on it)
+    cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk still in flight (kernels of the next one wait on it)
+    bool light_call = false;          // set around a single-region submit: no timing events (stats gpu_ms_* stay 0 for it
+                                      // unless PAIRHMM_CUDA_TIMING is set), fewer driver calls
     bool resident_loaded = false;
     std::vector<size_t> resident_out_off;  // per region of the resident batch: offset of its results in the caller's arrays
     bool no_output_ok = false;        // resident_load / prepare_reads pack regions without result arrays

@@ -118,8 +118,12 @@ class Oracle(_Lib):
 
 
 class Reference(_Lib):
-    def __init__(self):
-        super().__init__(os.path.join(HERE, "_ref", "libref_pairhmm.so"), "ref_pairhmm")
+    """oracle/_ref/libref_pairhmm.so (canonical: default -ffp-contract, as the reference's CMake builds it) or, with
+    nofma=True, libref_pairhmm_nofma.so (the same sources with -ffp-contract=off): the two disagree on `< 1e-28f` only
+    for threshold-ambiguous pairs"""
+
+    def __init__(self, nofma=False):
+        super().__init__(os.path.join(HERE, "_ref", "libref_pairhmm_nofma.so" if nofma else "libref_pairhmm.so"), "ref_pairhmm")
         self.lib.ref_pairhmm_isa.restype = C.c_int
 
     def isa(self):
@@ -163,6 +167,14 @@ def reference_available():
 
 def load_reference():
     return Reference()
+
+
+def reference_nofma_available():
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_pairhmm_nofma.so"))
+
+
+def load_reference_nofma():
+    return Reference(nofma=True)
 
 
 # ---- Smith-Waterman ----

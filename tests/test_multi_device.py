@@ -116,8 +116,8 @@ def test_shared_batcher_merges_regions_of_concurrent_callers(engine, oracle):
             assert not errors, errors
             for g in range(b.n_regions):
                 assert np.array_equal(got[g][0], want[g][0]) and np.array_equal(got[g][1], want[g][1]), g
-        st = engines[0].stats()
-        assert st["regions"] >= 2 * b.n_regions
+        st = engines[0].stats()      # the shared backend's counters as of this handle's last call
+        assert st["regions"] >= b.n_regions and st["kernel_launches"] > 0
         # bad input of one caller is refused for that caller only
         with pytest.raises(fgdp_b200.PairHMMError):
             ra, ha, keep = engines[1]._structs(*regions[0])
