@@ -138,3 +138,157 @@ cudaError_t launch_forward_long(const LongArgs &a, int grid_blocks, cudaStream_t
 }
 
 }  // namespace phmm
+
+// ------------------------------------------------------------------------------------------------------------------------
+// pairhmm_cuda_forward_pairs_noalloc -- the row-striped kernel above for callers that must not allocate (code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+// Everything the kernel needs besides the caller's own device arrays lives in file-scope
+// __device__ storage that every GPU loading this library holds until exit:
+//   g_na_scratch  the work-queue counter (first 256 bytes) and, per resident warp, the three stripe hand-over lines of
+//                 long_sweep: kNaWarps x 3 x (PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN + 8) doubles = 24.1 MiB;
+//   g_na_tables   ph2pr / matchToMatchProb in float and double (Context.h:75-89,139,180), 98 KiB, uploaded at set-up.
+// In host code those names are host-side stand-ins, not device addresses: at set-up -- once per device, with that device
+// current -- cudaGetSymbolAddress gives the real addresses, which are what the kernel is handed. Every call shares the
+// arrays; the queue counter is cleared on the caller's stream before every launch (the lines need no clearing: a stripe
+// writes a column before the next stripe reads it). Calls that overlap on the GPU (different streams) RACE on both.
+// ------------------------------------------------------------------------------------------------------------------------
+#include <algorithm>
+#include <cstdio>
+#include <mutex>
+
+#include "tables.h"
+
+namespace phmm {
+namespace {
+
+constexpr int kNaBlocks = 128, kNaWarps = kNaBlocks * 4;                                  // resident warps of the no-alloc launch
+constexpr uint64_t kNaLineCols = PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN + 8;
+constexpr uint64_t kNaPerWarp = 3 * kNaLineCols * sizeof(double);                          // 49 344 B, a multiple of 64
+constexpr uint64_t kNaHead = 256;                                                          // queue counter
+constexpr uint64_t kNaScratchBytes = kNaHead + (uint64_t)kNaWarps * kNaPerWarp;
+
+static __device__ __align__(256) unsigned char g_na_scratch[kNaScratchBytes];
+static __device__ __align__(256) HostTables g_na_tables;
+
+struct NoAllocArgs {
+    LongArgs base;                  // rd / plane / tables / log10 constants / out / flag / use_double / scratch
+    const uint32_t *read_off; const int32_t *read_len;
+    const uint64_t *hap_off; const int32_t *hap_len;
+    const uint32_t *pair_read, *pair_hap;
+    uint32_t n_pairs;
+};
+
+__global__ void __launch_bounds__(128) forward_long_noalloc_kernel(const NoAllocArgs n) {
+    const LongArgs &a = n.base;
+    const int lane = threadIdx.x & 31;
+    const uint32_t gwarp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    double *line = reinterpret_cast<double *>(a.scratch + kNaHead + (uint64_t)gwarp * kNaPerWarp);
+    const uint64_t w = kNaLineCols;
+    for (;;) {
+        uint32_t u = 0;
+        if (lane == 0) u = atomicAdd(a.queue, 1u);
+        u = __shfl_sync(kFull, u, 0);
+        if (u >= n.n_pairs) break;
+        const uint32_t r = n.pair_read[u], hid = n.pair_hap[u];
+        const DevRead rr{n.read_off[r], n.read_len[r]};
+        const int H = n.hap_len[hid];
+        const uint8_t *hap = a.hap_bytes + n.hap_off[hid];
+        double out;
+        uint8_t flag = 0;
+        if (H > PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN) {                  // longer than the caller stated: no scratch line for it
+            out = __longlong_as_double(0x7ff8000000000000ll); flag = 255;
+        } else if (rr.len <= 0) {                                    // zero-length read: no alignment exists (as the engine reports it)
+            out = __longlong_as_double(0xfff0000000000000ll); flag = 1;
+        } else {
+            float rf = 0.f;
+            if (H > 0 && !a.use_double)
+                rf = long_sweep<float>(a, rr, hap, H, reinterpret_cast<float *>(line), reinterpret_cast<float *>(line + w),
+                                       reinterpret_cast<float *>(line + 2 * w));
+            if (a.use_double || rf < 1e-28f) {                       // IntelPairHmm.cc:340-344
+                const double rd = H <= 0 ? 0.0 : long_sweep<double>(a, rr, hap, H, line, line + w, line + 2 * w);
+                out = log10(flush_denormal(rd)) - a.log10_init_d;
+                flag = 1;
+            } else {
+                out = (double)__fsub_rn((float)log10((double)rf), a.log10_init_f);   // IntelPairHmm.cc:348
+            }
+        }
+        if (lane == 0) { a.out[u] = out; if (a.flag) a.flag[u] = flag; }
+        __syncwarp();
+    }
+}
+
+// per device: the device addresses of the two arrays (0 = not set up yet)
+std::mutex g_na_mutex;
+struct NaDevice { unsigned char *scratch = nullptr; const HostTables *tables = nullptr; };
+NaDevice g_na_dev[64];
+
+void na_error(char *buf, size_t len, const char *msg, const char *detail = nullptr) {
+    if (!buf || !len) return;
+    snprintf(buf, len, "%s%s%s", msg, detail ? ": " : "", detail ? detail : "");
+}
+
+}  // namespace
+}  // namespace phmm
+
+extern "C" int pairhmm_cuda_forward_pairs_noalloc(int device, void *cuda_stream, const uint8_t *d_read_planes, uint64_t plane_stride,
+                                                  const uint32_t *d_read_off, const int32_t *d_read_len,
+                                                  const uint8_t *d_hap_bases, const uint64_t *d_hap_off, const int32_t *d_hap_len,
+                                                  const uint32_t *d_pair_read, const uint32_t *d_pair_hap, uint32_t n_pairs,
+                                                  int32_t max_hap_len, int32_t use_double, double *d_log10_out,
+                                                  uint8_t *d_rescued_out, char *error_buf, size_t error_buf_len) {
+    using namespace phmm;
+    if (error_buf && error_buf_len) error_buf[0] = 0;
+    if (n_pairs == 0) return PAIRHMM_OK;
+    if (!d_read_planes || !d_read_off || !d_read_len || !d_hap_bases || !d_hap_off || !d_hap_len || !d_pair_read || !d_pair_hap ||
+        !d_log10_out) {
+        na_error(error_buf, error_buf_len, "pairhmm_cuda_forward_pairs_noalloc: null device pointer");
+        return PAIRHMM_ERR_ARG;
+    }
+    if (max_hap_len < 0 || max_hap_len > PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "pairhmm_cuda_forward_pairs_noalloc: max_hap_len %d exceeds the static scratch of this build "
+                 "(PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN = %d); use the allocating entry points", max_hap_len, PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN);
+        na_error(error_buf, error_buf_len, msg);
+        return PAIRHMM_ERR_ARG;
+    }
+    int dev = device;
+    cudaError_t e;
+    if (dev < 0) { if ((e = cudaGetDevice(&dev)) != cudaSuccess) { cudaGetLastError(); na_error(error_buf, error_buf_len, "cudaGetDevice", cudaGetErrorString(e)); return PAIRHMM_ERR_NO_DEVICE; } }
+    else if ((e = cudaSetDevice(dev)) != cudaSuccess) { cudaGetLastError(); na_error(error_buf, error_buf_len, "cudaSetDevice", cudaGetErrorString(e)); return PAIRHMM_ERR_ARG; }
+    if (dev >= 64) { na_error(error_buf, error_buf_len, "pairhmm_cuda_forward_pairs_noalloc: device ordinal above 63"); return PAIRHMM_ERR_ARG; }
+    NaDevice nd;
+    {   // set-up, once per device, with that device current: the arrays' DEVICE addresses, and the lookup tables. (The first
+        // call on a device must therefore not sit inside a stream capture: the table upload is a synchronous copy.)
+        std::lock_guard<std::mutex> lk(g_na_mutex);
+        if (!g_na_dev[dev].scratch) {
+            unsigned char *sp = nullptr; HostTables *tp = nullptr;
+            if ((e = cudaGetSymbolAddress((void **)&sp, g_na_scratch)) != cudaSuccess ||
+                (e = cudaGetSymbolAddress((void **)&tp, g_na_tables)) != cudaSuccess) {
+                cudaGetLastError(); na_error(error_buf, error_buf_len, "cudaGetSymbolAddress", cudaGetErrorString(e)); return PAIRHMM_ERR_CUDA;
+            }
+            const HostTables &t = host_tables();
+            if ((e = cudaMemcpy(tp, &t, sizeof t, cudaMemcpyHostToDevice)) != cudaSuccess) {
+                cudaGetLastError(); na_error(error_buf, error_buf_len, "table upload", cudaGetErrorString(e)); return PAIRHMM_ERR_CUDA;
+            }
+            g_na_dev[dev].tables = tp; g_na_dev[dev].scratch = sp;
+        }
+        nd = g_na_dev[dev];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    // the work-queue counter must start at zero; the lines keep the last call's contents and need no clearing
+    if ((e = cudaMemsetAsync(nd.scratch, 0, kNaHead, st)) != cudaSuccess) { cudaGetLastError(); na_error(error_buf, error_buf_len, "cudaMemsetAsync", cudaGetErrorString(e)); return PAIRHMM_ERR_CUDA; }
+    NoAllocArgs n{};
+    LongArgs &a = n.base;
+    a.rd = d_read_planes; a.plane = plane_stride; a.hap_bytes = d_hap_bases;
+    a.queue = reinterpret_cast<uint32_t *>(nd.scratch);
+    a.ph2pr_f = nd.tables->ph2pr_f; a.mm_f = nd.tables->mm_f; a.ph2pr_d = nd.tables->ph2pr_d; a.mm_d = nd.tables->mm_d;   // address arithmetic only
+    a.log10_init_f = log10f(ldexpf(1.f, 120)); a.log10_init_d = log10(ldexp(1.0, 1020));                                 // Context.h:184,143
+    a.scratch = nd.scratch; a.scratch_per_warp = kNaPerWarp;
+    a.out = d_log10_out; a.flag = d_rescued_out; a.use_double = use_double ? 1 : 0;
+    n.read_off = d_read_off; n.read_len = d_read_len; n.hap_off = d_hap_off; n.hap_len = d_hap_len;
+    n.pair_read = d_pair_read; n.pair_hap = d_pair_hap; n.n_pairs = n_pairs;
+    const int grid = (int)std::min<uint64_t>((uint64_t)kNaBlocks, ((uint64_t)n_pairs + 3) / 4);
+    forward_long_noalloc_kernel<<<grid, 128, 0, st>>>(n);
+    if ((e = cudaGetLastError()) != cudaSuccess) { na_error(error_buf, error_buf_len, "kernel launch", cudaGetErrorString(e)); return PAIRHMM_ERR_CUDA; }
+    return PAIRHMM_OK;
+}

@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = [
     "pairhmm_cuda_default_read_model", "pairhmm_cuda_compute_raw", "pairhmm_cuda_compute_batch_raw",
     "pairhmm_cuda_compute_flat_raw", "pairhmm_cuda_prepare_reads_flat",
     "pairhmm_cuda_stats_get", "pairhmm_cuda_stats_reset", "pairhmm_cuda_last_error", "pairhmm_cuda_tables",
-    "pairhmm_cuda_prefix_plan", "pairhmm_cuda_device_plan",
+    "pairhmm_cuda_prefix_plan", "pairhmm_cuda_device_plan", "pairhmm_cuda_forward_pairs_noalloc",
 ]
 MM_COUNT = 8256
 

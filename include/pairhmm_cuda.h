@@ -313,6 +313,35 @@ int pairhmm_cuda_prepare_reads_flat(pairhmm_cuda_handle *h, const uint8_t *read_
                                     const pairhmm_cuda_read_model *model, uint8_t *out_base_q, uint8_t *out_ins_q,
                                     uint8_t *out_del_q, uint8_t *out_gcp);
 
+/* ---- allocation-free entry point ---------------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). It calls no cudaMalloc / cudaFree and no
+ * allocating library routine, takes no handle, and touches nothing of the engine's state.
+ *
+ * Explicit pair list on DEVICE arrays the caller owns: pair p = read d_pair_read[p] x haplotype d_pair_hap[p];
+ * d_read_planes = five byte planes plane_stride apart (bases | base qualities | insertion | deletion | gap-continuation
+ * qualities, as phmm_read), read r at byte d_read_off[r] of every plane, d_read_len[r] bases (any length >= 1; a
+ * zero-length read yields -inf, rescued 1); haplotype h = d_hap_bases[d_hap_off[h] .. + d_hap_len[h]). Writes
+ * d_log10_out[p] (double) and, unless NULL, d_rescued_out[p] -- same numerics as every other entry point (FP32 pass,
+ * < 1e-28f -> FP64, log10), computed by the row-striped kernel (one warp per pair: ~0.8 TCUPS, a quarter of the packed
+ * kernels' rate -- the price of needing no per-call layout pass). The launch is asynchronous on cuda_stream (a
+ * cudaStream_t; NULL = the default stream); the caller synchronises.
+ *
+ * Limit: the kernel's scratch -- three hand-over lines per resident warp -- lives in a static __device__ array of 24.1 MiB
+ * (+ 98 KiB of lookup tables) that every GPU loading this library holds until exit, sized for haplotypes of at most
+ * PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN bases. max_hap_len = the caller's bound on d_hap_len[]; a larger bound is refused
+ * with PAIRHMM_ERR_ARG and a message (a haplotype that nevertheless exceeds the limit gets NaN, rescued 255). ALL calls on
+ * a device share that array: calls that overlap on the GPU (different streams, or threads) race -- serialise them. The
+ * first call on each device performs a one-time set-up (symbol addresses, table upload: a synchronous copy) and must not
+ * sit inside a stream capture. error_buf (nullable, error_buf_len bytes) receives the text of an error. */
+#define PAIRHMM_CUDA_NOALLOC_MAX_HAP_LEN 2048
+int pairhmm_cuda_forward_pairs_noalloc(int device, void *cuda_stream, const uint8_t *d_read_planes, uint64_t plane_stride,
+                                       const uint32_t *d_read_off, const int32_t *d_read_len,
+                                       const uint8_t *d_hap_bases, const uint64_t *d_hap_off, const int32_t *d_hap_len,
+                                       const uint32_t *d_pair_read, const uint32_t *d_pair_hap, uint32_t n_pairs,
+                                       int32_t max_hap_len, int32_t use_double, double *d_log10_out, uint8_t *d_rescued_out,
+                                       char *error_buf, size_t error_buf_len);
+
 /* ---- multi-device plan (host logic, no device needed; what a multi-device handle computes for a batch call) ----
  * Region r has n_reads[r] reads whose lengths sum to read_len_sum[r] and haplotypes whose lengths sum to hap_len_sum[r]
  * (cost = DP cells = the product). Writes at most max_parts parts in (region, first read) order: part p = reads
