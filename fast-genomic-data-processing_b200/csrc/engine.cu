@@ -69,8 +69,10 @@ std::mutex g_err_mutex;   // plan_region runs on several threads and may report 
 // PAIRHMM_CUDA_TRACE=1: per-chunk timeline of a batch on stderr (host ms since the batch began; GPU ms since the
 // base event recorded at the same moment)
 bool trace_on() { static const bool on = std::getenv("PAIRHMM_CUDA_TRACE") != nullptr; return on; }
-clk::time_point g_trace_t0;
-cudaEvent_t g_trace_base = nullptr;
+clk::time_point g_trace_t0_[64];          // per device: several devices of one multi-device handle trace side by side
+cudaEvent_t g_trace_base_[64] = {nullptr};
+#define g_trace_t0 g_trace_t0_[h->device & 63]
+#define g_trace_base g_trace_base_[h->device & 63]
 
 }  // namespace
 // plan_region runs on several pool threads and may report through fail(): the text is written under a lock (the status
@@ -655,7 +657,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     }
     h->stats.host_ms_pack += ms_since(t0);
     if (trace_on())
-        std::fprintf(stderr, "[trace] pack %u reads: plan %.1f | bin %.1f | prefix+reserve %.1f | copy %.1f ms (%d threads)\n", s.n_uniq,
+        std::fprintf(stderr, "[trace d%d] pack %u reads: plan %.1f | bin %.1f | prefix+reserve %.1f | copy %.1f ms (%d threads)\n", h->device, s.n_uniq,
                      ms_plan, ms_bin - ms_plan, ms_reserve - ms_bin, ms_since(t0) - ms_reserve, threads);
     return PAIRHMM_OK;
 }
@@ -828,8 +830,8 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     if (trace_on() && g_trace_base) {
         float b0 = 0.f, b1 = 0.f;
         cudaEventElapsedTime(&b0, g_trace_base, s.ev_begin); cudaEventElapsedTime(&b1, g_trace_base, s.ev_end);
-        std::fprintf(stderr, "[trace] chunk done: host %.1f ms | gpu kernels %.1f .. %.1f ms (%.1f) | cells %.3g\n",
-                     ms_since(g_trace_t0), b0, b1, b1 - b0, (double)s.cells);
+        std::fprintf(stderr, "[trace d%d] chunk done: host %.1f ms | gpu kernels %.1f .. %.1f ms (%.1f) | cells %.3g\n",
+                     h->device, ms_since(g_trace_t0), b0, b1, b1 - b0, (double)s.cells);
     }
     h->stats.gpu_ms_float += ms_f; h->stats.gpu_ms_double += ms_all - ms_f; h->stats.gpu_ms_total += ms_all;
     auto t0 = clk::now();
@@ -1123,11 +1125,21 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
     int si = 0;
     int status = PAIRHMM_OK;
     int chunk_no = 0;
+    int64_t prev_cells = 0;
+    double pack_rate = 9.0e9;
     while (i < n_regions && status == PAIRHMM_OK) {
         views.clear();
         // the GPU idles while the first chunk is packed: start small (packing is ~3x faster than the kernels, so each
         // chunk may be 3x the previous one without starving the GPU)
-        const int64_t chunk_limit = chunk_no == 0 ? chunk_cells / 8 : chunk_no == 1 ? chunk_cells * 3 / 8 : chunk_cells;
+        // The GPU idles while the first chunk is packed, so that one is small; every later chunk is as large as the host can
+        // pack while the GPU works on the one before it: its size follows the packing rate just measured (uncontended, 16
+        // threads pack ~3x faster than the kernels compute; eight devices sharing the host's threads ~1.7x) against the
+        // kernels' rate (~3e9 cells / ms on a B200), within [1.5x, 4x] of the previous chunk.
+        int64_t chunk_limit = chunk_cells / 16;
+        if (chunk_no > 0) {
+            const double growth = std::min(4.0, std::max(1.5, 0.85 * pack_rate / 3.0e9));
+            chunk_limit = (int64_t)std::min((double)chunk_cells, (double)prev_cells * growth);
+        }
         ++chunk_no;
         int64_t cells = 0;
         uint64_t pairs = 0, rbytes = 0;
@@ -1136,8 +1148,11 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
             if (r.n_reads > 0 && !r.reads && !r.raw) { status = fail(h, PAIRHMM_ERR_ARG, "null read array"); break; }
             if (r.n_haps > 0 && !r.haps) { status = fail(h, PAIRHMM_ERR_ARG, "null haplotype array"); break; }
             uint64_t rl = 0, hl = 0;
-            for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
-            for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
+            if (r.read_len_sum >= 0 && r.hap_len_sum >= 0) { rl = (uint64_t)r.read_len_sum; hl = (uint64_t)r.hap_len_sum; }
+            else {
+                for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
+                for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
+            }
             const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
             if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_limit || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
             views.push_back(r);
@@ -1145,11 +1160,14 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
             ++i;
         }
         Slot &s = h->slots[si];
-        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: chunk of %zu regions cut\n", ms_since(g_trace_t0), views.size());
+        if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: chunk of %zu regions cut\n", h->device, ms_since(g_trace_t0), views.size());
         if (s.busy) status = finish_chunk(h, s, threads);
-        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: slot free, packing\n", ms_since(g_trace_t0));
+        if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: slot free, packing\n", h->device, ms_since(g_trace_t0));
+        const double pack_ms0 = h->stats.host_ms_pack;
         if (status == PAIRHMM_OK) status = submit_chunk(h, s, views.data(), views.size(), threads);
-        if (trace_on()) std::fprintf(stderr, "[trace] host %.1f ms: submitted\n", ms_since(g_trace_t0));
+        prev_cells = std::max<int64_t>(cells, 1);
+        pack_rate = (double)prev_cells / std::max(0.05, h->stats.host_ms_pack - pack_ms0);      // cells per ms of packing
+        if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: submitted\n", h->device, ms_since(g_trace_t0));
         si ^= 1;
     }
     for (int k = 0; k < 2; ++k) {
@@ -1266,6 +1284,11 @@ int pairhmm_cuda_compute_flat(pairhmm_cuda_handle *h, const uint8_t *read_bases,
                               int64_t n_regions, double *log10_out, uint8_t *rescued_out) {
     if (!h) return PAIRHMM_ERR_ARG;
     auto t0 = clk::now();
+    if (h->is_multi()) {     // every device's worker builds the views of its own share (multi.cu)
+        const FlatBatch fb{read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases, hap_off, hap_len, n_haps,
+                           reg_read_start, reg_hap_start, n_regions, log10_out, rescued_out};
+        return multi_compute_flat(h, fb);
+    }
     static thread_local FlatViews v;     // kept between calls: 48 B per read, page-faulting it in every call costs more than filling it
     int st = build_flat_views(h, v, read_bases, base_q, ins_q, del_q, gcp, read_off, read_len, n_reads, hap_bases,
                               hap_off, hap_len, n_haps, reg_read_start, reg_hap_start, n_regions, log10_out, rescued_out);

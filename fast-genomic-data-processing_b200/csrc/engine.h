@@ -38,6 +38,7 @@ struct RegionView {
     const phmm_hap *haps; int32_t n_haps;
     double *out; uint8_t *resc;
     phmm_read_summary *summ;          // per-read epilogue results (nullable; only with an active epilogue)
+    int64_t read_len_sum = -1, hap_len_sum = -1;   // sums of the lengths if a caller up the stack has them already (else -1)
 };
 
 // Sizes/offsets of one region inside a packed chunk (filled by pass A + prefix sums).
@@ -159,6 +160,13 @@ int device_chunks_in_flight(int device);
 int multi_create(pairhmm_cuda_handle *h);
 void multi_destroy(pairhmm_cuda_handle *h);
 int multi_compute_batch(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions);
+// the arguments of pairhmm_cuda_compute_flat
+struct FlatBatch {
+    const uint8_t *read_bases, *base_q, *ins_q, *del_q, *gcp; const int64_t *read_off; const int32_t *read_len; int64_t n_reads;
+    const uint8_t *hap_bases; const int64_t *hap_off; const int32_t *hap_len; int64_t n_haps;
+    const int64_t *reg_read_start, *reg_hap_start; int64_t n_regions; double *log10_out; uint8_t *rescued_out;
+};
+int multi_compute_flat(pairhmm_cuda_handle *h, const FlatBatch &fb);
 int multi_submit(pairhmm_cuda_handle *h, const RegionView &rv, pairhmm_cuda_ticket *ticket);
 int multi_wait(pairhmm_cuda_handle *h, pairhmm_cuda_ticket ticket);
 int multi_resident_load(pairhmm_cuda_handle *h, const RegionView *views, size_t n);

@@ -21,6 +21,7 @@
 #include <thread>
 
 #include "engine.h"
+#include "hostpool.h"
 
 namespace phmm {
 
@@ -111,7 +112,9 @@ int multi_create(pairhmm_cuda_handle *h) {
     for (int d : devs) if (d >= n) return fail(h, PAIRHMM_ERR_ARG, "device_mask names a CUDA ordinal this process does not see");
     // the children share the box's host threads: an equal share of the pool each unless the caller fixed pack_threads
     unsigned hc = std::thread::hardware_concurrency();
-    const int share = (int)std::max(2u, (hc ? hc : 16u) / (unsigned)devs.size());
+    // (twice the equal share: packing comes in bursts, one chunk at a time per device, and a burst that ends sooner starts
+    // the device's next chunk sooner; the pool hands its threads to whichever jobs are open)
+    const int share = (int)std::max(4u, 2u * (hc ? hc : 16u) / (unsigned)devs.size());
     for (int d : devs) {
         pairhmm_cuda_config c = h->cfg;
         c.device_mask = 0; c.device = d; c.batch_window_us = 0;
@@ -151,13 +154,19 @@ Split split_regions(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n
     std::vector<int32_t> nr((size_t)n_regions, 0);
     std::vector<size_t> region_off;
     if (want_offsets) region_off.resize((size_t)n_regions + 1, 0);
-    for (int64_t i = 0; i < n_regions; ++i) {
+    // the length sums walk every read descriptor of the batch (5 million for BASELINE configs[4]: 240 MB): on the pool,
+    // not on the calling thread alone (20 ms of a 130 ms eight-device call)
+    HostPool::instance().parallel_for((size_t)n_regions, 32, 64, [&](size_t i) {
         const RegionView &r = regions[i];
-        nr[(size_t)i] = r.n_reads;
-        if (r.reads || r.raw) for (int q = 0; q < r.n_reads; ++q) rl[(size_t)i] += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
-        if (r.haps) for (int q = 0; q < r.n_haps; ++q) hl[(size_t)i] += (uint64_t)std::max(0, r.haps[q].len);
-        if (want_offsets) region_off[(size_t)i + 1] = region_off[(size_t)i] + (size_t)std::max(0, r.n_reads) * (size_t)std::max(0, r.n_haps);
-    }
+        nr[i] = r.n_reads;
+        uint64_t a = 0, b = 0;
+        if (r.reads || r.raw) for (int q = 0; q < r.n_reads; ++q) a += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
+        if (r.haps) for (int q = 0; q < r.n_haps; ++q) b += (uint64_t)std::max(0, r.haps[q].len);
+        rl[i] = a; hl[i] = b;
+    });
+    if (want_offsets)
+        for (int64_t i = 0; i < n_regions; ++i)
+            region_off[(size_t)i + 1] = region_off[(size_t)i] + (size_t)std::max(0, regions[i].n_reads) * (size_t)std::max(0, regions[i].n_haps);
     const std::vector<DevicePart> parts = plan_devices(rl.data(), hl.data(), nr.data(), n_regions, nd);
     Split s;
     s.views.resize((size_t)nd);
@@ -169,6 +178,8 @@ Split split_regions(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n
         if (r.reads) v.reads = r.reads + p.first_read;
         if (r.raw) v.raw = r.raw + p.first_read;
         v.n_reads = p.n_reads;
+        // whole regions carry their length sums down, so that the device's chunk cutter does not walk the reads again
+        if (p.n_reads == r.n_reads) { v.read_len_sum = (int64_t)rl[(size_t)p.region]; v.hap_len_sum = (int64_t)hl[(size_t)p.region]; }
         if (r.out) v.out = r.out + row0;
         if (r.resc) v.resc = r.resc + row0;
         if (r.summ) v.summ = r.summ + p.first_read;
@@ -203,6 +214,87 @@ int multi_compute_batch(pairhmm_cuda_handle *h, const RegionView *regions, int64
     for (size_t d = 0; d < h->children.size(); ++d) {
         pairhmm_cuda_handle *c = h->children[d];
         h->workers[d]->post([c, split, d] { return compute_batch_impl(c, split->views[d].data(), (int64_t)split->views[d].size()); });
+    }
+    const int status = collect(h);
+    h->stats.calls += 1;
+    h->stats.host_ms_total += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return status;
+}
+
+// pairhmm_cuda_compute_flat on a multi-device handle. The generic path (views of the whole batch on the calling thread,
+// then the split) walks 48 bytes per read twice before any device starts: 14 ms of a 130 ms eight-device call on BASELINE
+// configs[4]. Here the split works on the flat length arrays (4 bytes per read, on the pool) and every device's worker
+// builds the views of ITS regions only, side by side with the other workers.
+int multi_compute_flat(pairhmm_cuda_handle *h, const FlatBatch &fb) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (fb.n_reads < 0 || fb.n_haps < 0 || fb.n_regions < 0) return fail(h, PAIRHMM_ERR_ARG, "negative count");
+    if (fb.n_reads && (!fb.read_bases || !fb.base_q || !fb.ins_q || !fb.del_q || !fb.gcp || !fb.read_off || !fb.read_len))
+        return fail(h, PAIRHMM_ERR_ARG, "null read array");
+    if (fb.n_haps && (!fb.hap_bases || !fb.hap_off || !fb.hap_len)) return fail(h, PAIRHMM_ERR_ARG, "null haplotype array");
+    if (fb.n_regions && (!fb.reg_read_start || !fb.reg_hap_start)) return fail(h, PAIRHMM_ERR_ARG, "null region array");
+    const size_t nreg = (size_t)fb.n_regions;
+    std::vector<uint64_t> rl(nreg, 0), hl(nreg, 0);
+    std::vector<int32_t> nr(nreg, 0);
+    std::vector<size_t> out_off(nreg + 1, 0);
+    for (size_t r = 0; r < nreg; ++r) {
+        const int64_t r0 = fb.reg_read_start[r], r1 = fb.reg_read_start[r + 1], h0 = fb.reg_hap_start[r], h1 = fb.reg_hap_start[r + 1];
+        if (r0 < 0 || r1 < r0 || r1 > fb.n_reads || h0 < 0 || h1 < h0 || h1 > fb.n_haps || r1 - r0 > 0x7fffffff || h1 - h0 > 0x7fffffff)
+            return fail(h, PAIRHMM_ERR_ARG, "region bounds out of range");
+        nr[r] = (int32_t)(r1 - r0);
+        out_off[r + 1] = out_off[r] + (size_t)(r1 - r0) * (size_t)(h1 - h0);
+        if ((r1 - r0) * (h1 - h0) > 0 && !fb.log10_out) return fail(h, PAIRHMM_ERR_ARG, "null output");
+    }
+    HostPool::instance().parallel_for(nreg, 32, 256, [&](size_t r) {
+        uint64_t a = 0, b = 0;
+        for (int64_t q = fb.reg_read_start[r]; q < fb.reg_read_start[r + 1]; ++q) a += (uint64_t)std::max(0, fb.read_len[q]);
+        for (int64_t q = fb.reg_hap_start[r]; q < fb.reg_hap_start[r + 1]; ++q) b += (uint64_t)std::max(0, fb.hap_len[q]);
+        rl[r] = a; hl[r] = b;
+    });
+    for (auto &kv : h->ticket_of) { const int st = pairhmm_cuda_wait(h->children[(size_t)kv.second.first], kv.second.second); if (st != PAIRHMM_OK) return st; }
+    h->ticket_of.clear();
+    h->resident_loaded = false;
+    propagate_call_state(h);
+    const int nd = (int)h->children.size();
+    auto parts = std::make_shared<std::vector<std::vector<DevicePart>>>((size_t)nd);
+    for (const DevicePart &p : plan_devices(rl.data(), hl.data(), nr.data(), fb.n_regions, nd)) (*parts)[(size_t)p.device].push_back(p);
+    auto sums = std::make_shared<std::pair<std::vector<uint64_t>, std::vector<uint64_t>>>(std::move(rl), std::move(hl));
+    auto offs = std::make_shared<std::vector<size_t>>(std::move(out_off));
+    for (size_t d = 0; d < (size_t)nd; ++d) {
+        pairhmm_cuda_handle *c = h->children[d];
+        h->workers[d]->post([c, parts, sums, offs, fb, d] {
+            const std::vector<DevicePart> &mine = (*parts)[d];
+            // per worker thread, kept between calls (page-faulting 48 B per read in on every call costs more than filling it)
+            static thread_local std::vector<phmm_read> reads;
+            static thread_local std::vector<phmm_hap> haps;
+            static thread_local std::vector<RegionView> views;
+            static thread_local std::vector<size_t> r_at, h_at;
+            r_at.assign(mine.size() + 1, 0); h_at.assign(mine.size() + 1, 0);
+            for (size_t i = 0; i < mine.size(); ++i) {
+                r_at[i + 1] = r_at[i] + (size_t)mine[i].n_reads;
+                h_at[i + 1] = h_at[i] + (size_t)(fb.reg_hap_start[mine[i].region + 1] - fb.reg_hap_start[mine[i].region]);
+            }
+            reads.resize(r_at.back()); haps.resize(h_at.back()); views.resize(mine.size());
+            phmm_read *rp = reads.data(); phmm_hap *hp = haps.data(); RegionView *vp = views.data();   // pool threads have their own thread_locals
+            const size_t *ra = r_at.data(), *ha = h_at.data();
+            HostPool::instance().parallel_for(mine.size(), pack_threads(c), 16, [&, rp, hp, vp, ra, ha](size_t i) {
+                const DevicePart &p = mine[i];
+                const int64_t r0 = fb.reg_read_start[p.region] + p.first_read, h0 = fb.reg_hap_start[p.region];
+                const int32_t nh = (int32_t)(fb.reg_hap_start[p.region + 1] - h0);
+                for (int32_t q = 0; q < p.n_reads; ++q) {
+                    const int64_t o = fb.read_off[r0 + q];
+                    rp[ra[i] + (size_t)q] = phmm_read{fb.read_bases + o, fb.base_q + o, fb.ins_q + o, fb.del_q + o, fb.gcp + o, fb.read_len[r0 + q]};
+                }
+                for (int32_t q = 0; q < nh; ++q) hp[ha[i] + (size_t)q] = phmm_hap{fb.hap_bases + fb.hap_off[h0 + q], fb.hap_len[h0 + q]};
+                const size_t o = (*offs)[(size_t)p.region] + (size_t)p.first_read * (size_t)nh;
+                RegionView v{rp + ra[i], nullptr, p.n_reads, hp + ha[i], nh, fb.log10_out ? fb.log10_out + o : nullptr,
+                             fb.rescued_out ? fb.rescued_out + o : nullptr, nullptr};
+                if ((int64_t)p.n_reads == fb.reg_read_start[p.region + 1] - fb.reg_read_start[p.region]) {
+                    v.read_len_sum = (int64_t)sums->first[(size_t)p.region]; v.hap_len_sum = (int64_t)sums->second[(size_t)p.region];
+                }
+                vp[i] = v;
+            });
+            return compute_batch_impl(c, vp, (int64_t)mine.size());
+        });
     }
     const int status = collect(h);
     h->stats.calls += 1;
