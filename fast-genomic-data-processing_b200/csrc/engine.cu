@@ -579,25 +579,39 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         const RegionView &rv = s.regions[i];
         const RegionPlan &p = s.plans[i];
         uint64_t ro = p.read_byte_off;
+        // Reads that follow one another in the caller's arrays (the flat entry points; a BAM slice) are copied as ONE run per
+        // plane: a region of 200 reads is 4 memcpys of 30 KB instead of 800 of 150 bytes (the per-call cost of the small
+        // copies, not memory bandwidth, was what the copy phase spent its time on)
+        ReadRef run0{}; uint64_t run_ro = 0, run_len = 0;
+        auto flush = [&] {
+            if (!run_len) return;
+            uint8_t *d = s.h_rd.p + run_ro;
+            std::memcpy(d, run0.bases, run_len); std::memcpy(d + s.plane, run0.base_q, run_len);
+            if (!s.raw_on) {
+                std::memcpy(d + 2 * s.plane, run0.ins_q, run_len); std::memcpy(d + 3 * s.plane, run0.del_q, run_len);
+                if (!s.skip_gcp) std::memcpy(d + 4 * s.plane, run0.gcp, run_len);
+            } else if (s.raw_indel_q) {
+                // planes 2-4 are filled on the device unless some read of the chunk has its own indel qualities
+                if (run0.ins_q) std::memcpy(d + 2 * s.plane, run0.ins_q, run_len); else std::memset(d + 2 * s.plane, 45, run_len);
+                if (run0.del_q) std::memcpy(d + 3 * s.plane, run0.del_q, run_len); else std::memset(d + 3 * s.plane, 45, run_len);
+            }
+            run_len = 0;
+        };
         for (uint32_t j = 0; j < p.n_uniq; ++j) {
             const ReadRef r = read_ref(rv, p.uniq_src[j]);
-            uint8_t *d = s.h_rd.p + ro;
-            std::memcpy(d, r.bases, r.len); std::memcpy(d + s.plane, r.base_q, r.len);
-            if (!s.raw_on) {
-                std::memcpy(d + 2 * s.plane, r.ins_q, r.len); std::memcpy(d + 3 * s.plane, r.del_q, r.len);
-                if (!s.skip_gcp) std::memcpy(d + 4 * s.plane, r.gcp, r.len);
-            } else {
-                // planes 2-4 are filled on the device unless some read of the chunk has its own indel qualities
-                if (s.raw_indel_q) {
-                    if (r.ins_q) std::memcpy(d + 2 * s.plane, r.ins_q, r.len); else std::memset(d + 2 * s.plane, 45, r.len);
-                    if (r.del_q) std::memcpy(d + 3 * s.plane, r.del_q, r.len); else std::memset(d + 3 * s.plane, 45, r.len);
-                }
-                s.h_mapq.p[p.first_uniq + j] = r.mapq;
-            }
+            const bool follows = run_len && r.bases == run0.bases + run_len && r.base_q == run0.base_q + run_len &&
+                                 (s.raw_on ? ((r.ins_q != nullptr) == (run0.ins_q != nullptr) && (!r.ins_q || r.ins_q == run0.ins_q + run_len) &&
+                                              (r.del_q != nullptr) == (run0.del_q != nullptr) && (!r.del_q || r.del_q == run0.del_q + run_len))
+                                           : (r.ins_q == run0.ins_q + run_len && r.del_q == run0.del_q + run_len &&
+                                              (s.skip_gcp || r.gcp == run0.gcp + run_len)));
+            if (!follows) { flush(); run0 = r; run_ro = ro; }
+            run_len += (uint64_t)r.len;
+            if (s.raw_on) s.h_mapq.p[p.first_uniq + j] = r.mapq;
             s.h_reads.p[p.first_uniq + j] = DevRead{(uint32_t)ro, r.len};
             if (s.ep_on) s.h_rows.p[p.first_uniq + j] = RowInfo{p.upair_off + j * (uint32_t)rv.n_haps, (uint32_t)rv.n_haps};
             ro += (uint64_t)r.len;
         }
+        flush();
         // work units: per bin run, 32/W consecutive reads per warp, one unit per haplotype group
         const uint32_t nhap = (uint32_t)rv.n_haps;
         for (const auto &run : p.runs) {
@@ -636,7 +650,9 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     });
     // A chunk of few units (a handful of waves of warps) ends when its slowest warp does: hand the long units out first
     // (LPT). Large chunks keep the packing order -- their tail is a fraction of a per cent and sorting a million units is not free.
-    if (n_units > (uint32_t)h->sm_count * 8u && n_units <= 65536u) {      // more than one wave of resident warps
+    // (up to ~14 waves of resident warps: beyond that the tail is below one per cent, and the sort -- serial, 3 ms for the
+    // 42 000 units of a full chunk -- was most of what the copy phase of a large chunk cost)
+    if (n_units > (uint32_t)h->sm_count * 8u && n_units <= 16384u) {      // more than one wave of resident warps
         std::vector<std::pair<uint32_t, DevUnit>> tmp;
         for (int b = 0; b < kNumBins; ++b) {
             const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
@@ -1106,7 +1122,8 @@ int pairhmm_cuda_compute(pairhmm_cuda_handle *h, const phmm_read *reads, int n_r
 }  // extern "C"
 
 // the batch pipeline over regions of either read kind (RegionView::reads or ::raw)
-int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions) {
+int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions,
+                             const std::function<void(int64_t)> *ensure) {
     if (!h || n_regions < 0 || (n_regions > 0 && !regions)) return PAIRHMM_ERR_ARG;
     if (h->is_multi()) return multi_compute_batch(h, regions, n_regions);
     auto t0 = clk::now();
@@ -1126,24 +1143,22 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
     int status = PAIRHMM_OK;
     int chunk_no = 0;
     int64_t prev_cells = 0;
+    int ladder = 0;
     double pack_rate = 9.0e9;
     while (i < n_regions && status == PAIRHMM_OK) {
         views.clear();
-        // the GPU idles while the first chunk is packed: start small (packing is ~3x faster than the kernels, so each
-        // chunk may be 3x the previous one without starving the GPU)
-        // The GPU idles while the first chunk is packed, so that one is small; every later chunk is as large as the host can
-        // pack while the GPU works on the one before it: its size follows the packing rate just measured (uncontended, 16
-        // threads pack ~3x faster than the kernels compute; eight devices sharing the host's threads ~1.7x) against the
-        // kernels' rate (~3e9 cells / ms on a B200), within [1.5x, 4x] of the previous chunk.
-        int64_t chunk_limit = chunk_cells / 16;
-        if (chunk_no > 0) {
-            const double growth = std::min(4.0, std::max(1.5, 0.85 * pack_rate / 3.0e9));
-            chunk_limit = (int64_t)std::min((double)chunk_cells, (double)prev_cells * growth);
-        }
+        // The GPU idles while the first chunk is packed, so that one is small (1/16 of a full chunk); the following ones
+        // climb a fixed ladder of sizes -- x2 per chunk, x4 when the host packs more than ~4x faster than the kernels compute
+        // (~3e9 cells / ms on a B200; the packing rate is the one just measured: 16 uncontended threads ~3x, eight devices
+        // sharing the host's threads ~1.7x) -- so that packing chunk i+1 fits under the kernels of chunk i. A ladder, not a
+        // free size: the slots' grow-only buffers then reach their final size in a handle's first large call.
+        if (chunk_no > 0 && ladder < 4) ladder = std::min(4, ladder + (0.85 * pack_rate / 3.0e9 >= 3.5 ? 2 : 1));
+        const int64_t chunk_limit = chunk_cells >> (4 - ladder);
         ++chunk_no;
         int64_t cells = 0;
         uint64_t pairs = 0, rbytes = 0;
         while (i < n_regions) {
+            if (ensure) (*ensure)(i);
             const RegionView &r = regions[i];
             if (r.n_reads > 0 && !r.reads && !r.raw) { status = fail(h, PAIRHMM_ERR_ARG, "null read array"); break; }
             if (r.n_haps > 0 && !r.haps) { status = fail(h, PAIRHMM_ERR_ARG, "null haplotype array"); break; }

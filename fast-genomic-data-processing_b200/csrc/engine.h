@@ -4,6 +4,7 @@
 // and all of gkl_pairhmm's dispatch (M2/intel/pairhmm/IntelPairHmm.cc:259-351).
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <memory>
 #include <string>
 #include <unordered_map>
@@ -146,7 +147,10 @@ std::vector<DevicePart> plan_devices(const uint64_t *read_len_sum, const uint64_
                                      int64_t n_regions, int n_devices);
 
 // ---- internal entry points shared by engine.cu / multi.cu / batcher.cu (single-device handles) ----
-int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions);
+// ensure (nullable): called with i before regions[i] is first read -- a caller that fills the array lazily (multi.cu builds a
+// device's views block by block, under the kernels of the chunks already submitted) completes regions[0 .. i] there
+int compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, int64_t n_regions,
+                       const std::function<void(int64_t)> *ensure = nullptr);
 int resident_load_views(pairhmm_cuda_handle *h, const RegionView *views, size_t n, const size_t *out_off);
 int check_region_args(pairhmm_cuda_handle *h, const RegionView &rv);   // the validation plan_region does, without the plan
 int fail(pairhmm_cuda_handle *h, int status, const std::string &msg);
