@@ -414,7 +414,13 @@ def main():
                 "tflops_flop_form": cells * FLOP_PER_CELL / (float_ms_step * 1e-3) / 1e12,
                 "float_kernel_gcups": cells / (float_ms_step * 1e-3) / 1e9, "float_kernel_ms": float_ms_step,
                 "algorithmic_bytes": algo_bytes, "algorithmic_hbm_GBps": algo_bytes / (float_ms_step * 1e-3) / 1e9,
-                "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None}
+                "hbm_peak_GBps_measured": peaks.get("hbm_gbs"), "traffic": None,
+                # what the pipe gives to the kernel's own instruction mix in a microbenchmark (no dependencies, no loads):
+                # FFMA2 (pair x uniform + pair) + FMUL2, 0.466 packed instr/clk/SMSP = 29.8 of the 32 lane-ops/clk/SMSP
+                "peak_attainable_measured": peak_ops / 1e12 * (29.8 / 32.0),
+                "peak_attainable_source": "profiles/r2_ubench_fma2_rate.txt (tools/ubench/fma2_rate.cu on B200 @1965 MHz): FFMA2c + FMUL2 mix "
+                                          "29.8 of 32 FP32 lane-ops/clk/SMSP = 93 % of the derived peak",
+                "frac_of_attainable": achieved_ops / (peak_ops * 29.8 / 32.0)}
     if args.workload == "snv":
         roofline["kernel"] = "forward2p_kernel<W, K, KL> (packed FP32 with prefix sharing between same-length haplotypes)"
         roofline["swept_frac"] = swept_cells / cells

@@ -1142,17 +1142,16 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
     int si = 0;
     int status = PAIRHMM_OK;
     int chunk_no = 0;
-    int64_t prev_cells = 0;
     int ladder = 0;
-    double pack_rate = 9.0e9;
     while (i < n_regions && status == PAIRHMM_OK) {
         views.clear();
         // The GPU idles while the first chunk is packed, so that one is small (1/16 of a full chunk); the following ones
-        // climb a fixed ladder of sizes -- x2 per chunk, x4 when the host packs more than ~4x faster than the kernels compute
-        // (~3e9 cells / ms on a B200; the packing rate is the one just measured: 16 uncontended threads ~3x, eight devices
-        // sharing the host's threads ~1.7x) -- so that packing chunk i+1 fits under the kernels of chunk i. A ladder, not a
-        // free size: the slots' grow-only buffers then reach their final size in a handle's first large call.
-        if (chunk_no > 0 && ladder < 4) ladder = std::min(4, ladder + (0.85 * pack_rate / 3.0e9 >= 3.5 ? 2 : 1));
+        // double until the full size is reached: packing chunk i+1 then fits under the kernels of chunk i both when the
+        // host packs ~3x faster than the kernels compute (one device, 16 uncontended threads) and when it packs ~1.7x
+        // faster (eight devices sharing the host's threads). A FIXED ladder on purpose: sizes that followed the measured
+        // packing rate differed from call to call, and the slots' grow-only pinned buffers were re-allocated (tens of ms
+        // each) in a handle's second and third large call.
+        if (chunk_no > 0 && ladder < 4) ++ladder;
         const int64_t chunk_limit = chunk_cells >> (4 - ladder);
         ++chunk_no;
         int64_t cells = 0;
@@ -1178,10 +1177,7 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: chunk of %zu regions cut\n", h->device, ms_since(g_trace_t0), views.size());
         if (s.busy) status = finish_chunk(h, s, threads);
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: slot free, packing\n", h->device, ms_since(g_trace_t0));
-        const double pack_ms0 = h->stats.host_ms_pack;
         if (status == PAIRHMM_OK) status = submit_chunk(h, s, views.data(), views.size(), threads);
-        prev_cells = std::max<int64_t>(cells, 1);
-        pack_rate = (double)prev_cells / std::max(0.05, h->stats.host_ms_pack - pack_ms0);      // cells per ms of packing
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: submitted\n", h->device, ms_since(g_trace_t0));
         si ^= 1;
     }
