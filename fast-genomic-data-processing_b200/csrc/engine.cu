@@ -1143,6 +1143,8 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
     int status = PAIRHMM_OK;
     int chunk_no = 0;
     int ladder = 0;
+    std::vector<uint64_t> sums;
+    size_t summed = 0, sum_block = 128;
     while (i < n_regions && status == PAIRHMM_OK) {
         views.clear();
         // The GPU idles while the first chunk is packed, so that one is small (1/16 of a full chunk); the following ones
@@ -1164,8 +1166,20 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
             uint64_t rl = 0, hl = 0;
             if (r.read_len_sum >= 0 && r.hap_len_sum >= 0) { rl = (uint64_t)r.read_len_sum; hl = (uint64_t)r.hap_len_sum; }
             else {
-                for (int q = 0; q < r.n_reads; ++q) rl += (uint64_t)std::max(0, r.raw ? r.raw[q].len : r.reads[q].len);
-                for (int q = 0; q < r.n_haps; ++q) hl += (uint64_t)std::max(0, r.haps[q].len);
+                // the length sums walk every read descriptor (48 bytes each): block by block on the pool, ahead of the cutter
+                if ((size_t)i >= summed) {
+                    const size_t b0 = summed, b1 = std::min((size_t)n_regions, summed + sum_block);
+                    if (sums.size() < 2 * (size_t)n_regions) sums.resize(2 * (size_t)n_regions);
+                    parallel_for(b1 - b0, threads, 32, [&, b0](size_t k) {
+                        const RegionView &q = regions[b0 + k];
+                        uint64_t a = 0, b = 0;
+                        if (q.reads || q.raw) for (int t = 0; t < q.n_reads; ++t) a += (uint64_t)std::max(0, q.raw ? q.raw[t].len : q.reads[t].len);
+                        if (q.haps) for (int t = 0; t < q.n_haps; ++t) b += (uint64_t)std::max(0, q.haps[t].len);
+                        sums[2 * (b0 + k)] = a; sums[2 * (b0 + k) + 1] = b;
+                    });
+                    summed = b1; sum_block = std::min<size_t>(sum_block * 2, 4096);
+                }
+                rl = sums[2 * (size_t)i]; hl = sums[2 * (size_t)i + 1];
             }
             const uint64_t p = (uint64_t)std::max(0, r.n_reads) * (uint64_t)std::max(0, r.n_haps);
             if (!views.empty() && (cells + (int64_t)(rl * hl) > chunk_limit || pairs + p > 0x30000000ull || rbytes + rl > 0xc0000000ull)) break;
