@@ -49,13 +49,16 @@ void Slot::release() {
     h_rows.release(); h_summ.release(); d_rows.release(); d_summ.release(); h_mapq.release(); d_mapq.release();
     d_rd.release(); d_hapbytes.release(); d_flag.release(); d_reads.release(); d_haps.release();
     d_hapoff.release(); d_haplist.release(); d_hapw.release(); d_counters.release(); d_units.release();
-    d_rescue.release(); d_fres.release(); d_out.release();
+    d_rescue.release(); d_pair_table.release(); d_fres.release(); d_out.release();
     if (ev_begin) cudaEventDestroy(ev_begin);
     if (ev_float_done) cudaEventDestroy(ev_float_done);
     if (ev_fwd_done) cudaEventDestroy(ev_fwd_done);
     if (ev_end) cudaEventDestroy(ev_end);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    if (ev_join) cudaEventDestroy(ev_join);
+    if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
-    ev_begin = ev_float_done = ev_fwd_done = ev_end = nullptr; stream = nullptr;
+    ev_begin = ev_float_done = ev_fwd_done = ev_end = ev_fork = ev_join = nullptr; stream = stream2 = nullptr;
 }
 
 }  // namespace phmm
@@ -98,9 +101,11 @@ int fail_cuda(pairhmm_cuda_handle *h, cudaError_t e, const char *what) {
 // (zeroed per run), then the device copy of Slot::rescue_base
 constexpr int kQueueF = 0, kRescueCount = kNumBins, kQueueD = kNumBins + kNumBinsW32, kQueueLong = kNumBins + 2 * kNumBinsW32,
               kRescuedPairs = kNumBins + 2 * kNumBinsW32 + 1;
-constexpr int kZeroedWords = kNumBins + 2 * kNumBinsW32 + 2;
-constexpr int kRescueBaseDev = kZeroedWords;
-constexpr int kCounterWords = kZeroedWords + kNumBinsW32 + 4;
+// ... the same for the W = 16 lists of the FP64 pass (units of two reads) and the number of pairing candidates
+constexpr int kRescueCount16 = kRescuedPairs + 1, kQueueD16 = kRescueCount16 + kNumBinsW16, kPendingCount = kQueueD16 + kNumBinsW16;
+constexpr int kZeroedWords = kPendingCount + 1;
+constexpr int kRescueBaseDev = kZeroedWords, kRescueBase16Dev = kRescueBaseDev + kNumBinsW32 + 1;
+constexpr int kCounterWords = kRescueBase16Dev + kNumBinsW16 + 1 + 3;
 
 // Runs fn(i) for i in [0,n) on the calling thread plus up to `threads` - 1 threads of the process-wide pool
 // (dynamic chunks of `grain`; hostpool.h).
@@ -275,7 +280,10 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
 
 // Lane-group width for a read of length R under the given FP32 variant. Narrow groups (more rows per
 // lane) exist for the uniform-gcp kernels only; forced_w (config.reserved[1]) overrides the choice.
-int choose_width(int R, Variant v, int forced_w) {
+int choose_width(int R, Variant v, int forced_w, bool f64_w16) {
+    // use_double chunks with a uniform gap-continuation penalty: the wide FP64 kernel at two reads per warp (W = 16) where
+    // the rows per lane fit its registers -- twice the rows per lane halve the per-cell share of shuffles / selects / loop
+    if (f64_w16 && R <= 16 * kMaxKF64W16 && bin_of_read(R, 16) >= 0) return 16;
     if (!is_packed_f32(v)) return 32;
     if (forced_w && bin_of_read(R, forced_w) >= 0) return forced_w;
     // the narrowest group that fits wins: more rows per lane amortise the per-column overhead (shuffles,
@@ -287,14 +295,15 @@ int choose_width(int R, Variant v, int forced_w) {
 
 // Pass A2 for one region, once the chunk's kernel variant is known: order the unique reads by kernel bin
 // (stable, so equal-length reads keep their input order) and form the bin runs.
-void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w) {
+void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w, bool f64_w16) {
     const uint32_t n = pl.n_uniq;
     std::vector<uint16_t> bin(n);
     for (uint32_t j = 0; j < n; ++j) {
         const int R = read_ref(rv, pl.uniq_src[j]).len;
         if (R > kMaxReadLen) { bin[j] = (uint16_t)kLongBin; continue; }      // swept in row stripes by long.cu, one unit per pair
-        bin[j] = (uint16_t)bin_of_read(R, choose_width(R, v, forced_w));
+        bin[j] = (uint16_t)bin_of_read(R, choose_width(R, v, forced_w, f64_w16));
         pl.pairs32[bin_of_read(R, 32)] += (uint32_t)rv.n_haps;
+        if (R <= 16 * kMaxKF64W16) pl.pairs16[bin_of_read(R, 16) - kBinBase[1]] += (uint32_t)rv.n_haps;
     }
     std::vector<uint32_t> order(n), inv(n);
     for (uint32_t j = 0; j < n; ++j) order[j] = j;
@@ -407,7 +416,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
                 const int len = read_ref(regs[i], (size_t)r).len;
                 if (len < 1 || len > kMaxReadLen) continue;
                 ++n_ok; rmax = std::max(rmax, len);
-                warps += 1.0 / (double)reads_per_warp(Variant::F32_PK, choose_width(len, Variant::F32_PK, forced));
+                warps += 1.0 / (double)reads_per_warp(Variant::F32_PK, choose_width(len, Variant::F32_PK, forced, false));
             }
             for (int wi = 0; wi < kNumWidths; ++wi) {
                 const uint32_t per_warp = (uint32_t)reads_per_warp(Variant::F32_PK, kWidths[wi]);
@@ -454,9 +463,11 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     // haplotype indices and breaks ties by position, so it keeps the caller's order
     const bool pfx_candidate = s.float_variant == Variant::F32_PK && h->cfg.reserved[4] && !h->ep_on;
     const int forced_w = chunk_w;
+    static const bool f64_w16_on = std::getenv("PAIRHMM_CUDA_F64_W32") == nullptr;
+    const bool f64_w16 = f64_w16_on && h->cfg.use_double && s.uniform_gcp && !h->cfg.reserved[0] && !h->cfg.reserved[2] && !h->cfg.exact_fp32;
     const double ms_plan = ms_since(t0);
     parallel_for(n_regs, threads, 8, [&](size_t i) {
-        bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w);
+        bin_region(s.regions[i], s.plans[i], s.float_variant, forced_w, f64_w16);
         if (pfx_candidate) plan_prefix(s.regions[i], s.plans[i]);
     });
     if (pfx_candidate) {
@@ -474,6 +485,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     uint32_t nu = 0, nh = 0, hw = kLeadWords, hl = 0, up = 0;
     std::vector<uint32_t> bin_count(kNumBins + 1, 0);
     uint32_t bin_pairs[kNumBinsW32] = {0};
+    uint32_t bin_pairs16[kNumBinsW16] = {0};
     int32_t hap_max = 0;
     for (size_t i = 0; i < n_regs; ++i) {
         RegionPlan &p = s.plans[i];
@@ -488,6 +500,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             bin_count[run.bin] += (run.n_reads + per_warp - 1) / per_warp * p.n_groups;
         }
         for (int k = 0; k < kNumBinsW32; ++k) bin_pairs[k] += p.pairs32[k];
+        for (int k = 0; k < kNumBinsW16; ++k) bin_pairs16[k] += p.pairs16[k];
         if ((uint32_t)s.regions[i].n_haps > 0xffffu)
             return fail(h, PAIRHMM_ERR_ARG, "more than 65535 haplotypes in one region");
         const uint64_t up_next = (uint64_t)up + (uint64_t)p.n_uniq * (uint64_t)s.regions[i].n_haps;
@@ -504,6 +517,17 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     s.rescue_base[0] = 0;
     for (int k = 0; k <= kNumBins; ++k) s.bin_start[k + 1] = s.bin_start[k] + bin_count[k];
     for (int k = 0; k < kNumBinsW32; ++k) s.rescue_base[k + 1] = s.rescue_base[k] + bin_pairs[k];
+    // FP64 pass with two reads per warp (rescue_scan_kernel): the lists of the W = 16 bins (a unit takes two reads' pairs)
+    // and the pairing candidates lie behind the W = 32 lists. Only where the chunk could fill the GPU that way (the scan
+    // decides by the number of pairs that did underflow); config.reserved[7]: 1 = never, 2 = always (testing)
+    {
+        const bool wide64 = s.uniform_gcp && !h->cfg.use_double && !h->cfg.exact_fp32 && !h->cfg.reserved[0] && !h->cfg.reserved[2];
+        const uint32_t slots16 = (uint32_t)h->sm_count * 8u;
+        s.pair_mode = (!wide64 || h->cfg.reserved[7] == 1) ? 0u : h->cfg.reserved[7] == 2 ? 2u : (up >= 4u * slots16 ? 1u : 0u);
+        s.rescue_base16[0] = up + 1;
+        for (int k = 0; k < kNumBinsW16; ++k) s.rescue_base16[k + 1] = s.rescue_base16[k] + (s.pair_mode ? (bin_pairs16[k] + 1) / 2 : 0u);
+        s.pending_off = s.rescue_base16[kNumBinsW16];
+    }
     const uint32_t n_units = s.bin_start[kNumBins + 1];
     s.hap_max = hap_max;
     // the packed FP32 kernels and the wide FP64 kernel take the (uniform) gap-continuation penalty as a launch constant and
@@ -561,6 +585,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         s.h_rd.set_view(s.h_meta.p + o_rd); s.d_rd.set_view(s.d_meta.p + o_rd);
         std::memset(s.h_counters.p, 0, sizeof(uint32_t) * kCounterWords);
         std::memcpy(s.h_counters.p + kRescueBaseDev, s.rescue_base, sizeof(uint32_t) * (kNumBinsW32 + 1));
+        std::memcpy(s.h_counters.p + kRescueBase16Dev, s.rescue_base16, sizeof(uint32_t) * (kNumBinsW16 + 1));
     }
     {   // results: the log10 values and, behind them, the rescued flags -- one buffer on either side, ONE copy back
         const uint64_t flag_off = sizeof(double) * ((uint64_t)up + 1);
@@ -569,7 +594,12 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         s.h_out.set_view(s.h_res.p); s.d_out.set_view(s.d_res.p);
         s.h_flag.set_view(s.h_res.p + flag_off); s.d_flag.set_view(s.d_res.p + flag_off);
     }
-    RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, up + 1);
+    RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, s.pair_mode ? (size_t)s.pending_off + up + 1 : (size_t)up + 1);
+    if (s.pair_mode && !s.d_pair_table.p) {
+        RES(d_pair_table, kPairSlots);
+        if ((e = cudaMemsetAsync(s.d_pair_table.p, 0, sizeof(uint32_t) * kPairSlots, s.stream)) != cudaSuccess)
+            return fail_cuda(h, e, "zero d_pair_table");
+    }
     if (s.ep_on) { RES(h_summ, nu + 1); RES(d_summ, nu + 1); }
 #undef RES
 
@@ -760,17 +790,47 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s, bool replay) {
                          // 0 = chosen on the device from the number of underflowed pairs finalize_kernel counted
                          h->cfg.reserved[6] > 0 ? (uint32_t)h->cfg.reserved[6] : 0u, s.d_counters.p + kRescuedPairs,
                          (uint32_t)h->sm_count * 12u};
+        r.pair_mode = s.pair_mode;
+        r.pending = s.d_rescue.p + s.pending_off; r.pending_count = s.d_counters.p + kPendingCount;
+        r.pair_table = s.d_pair_table.p;
+        r.rescue_base16 = s.d_counters.p + kRescueBase16Dev; r.rescue_count16 = s.d_counters.p + kRescueCount16;
+        r.fp64_warp_slots16 = (uint32_t)h->sm_count * 8u;
+        r.n_pairs = s.n_upairs;
         CU(h, launch_rescue_scan(r, st));
         if (r.n_units) h->stats.kernel_launches += 1;
+        if (r.n_units && r.pair_mode) {
+            CU(h, launch_rescue_flush(r, st));
+            h->stats.kernel_launches += 1;
+        }
     }
     if (s.timed) CU(h, cudaEventRecord(s.ev_float_done, st));
     a.ph2pr = h->d_ph2pr_d; a.mm = h->d_mm_d;
     a.rescue_filter = all_double ? 0u : 1u;
-    for (int b = 0; b < kNumBinsW32; ++b) {
+    // Units of two reads first (the W = 16 instance of the wide FP64 kernel), the units of one read beside them on the slot's
+    // second stream: both are persistent grids that leave when their list is empty, so the second launch moves into the SMs
+    // as the first one's warps run dry -- in series each launch would end in its own tail.
+    cudaStream_t st32 = st;
+    if (!all_double && s.pair_mode) {
+        CU(h, cudaEventRecord(s.ev_fork, st));
+        for (int b = 0; b < kNumBinsW16; ++b) {
+            const uint64_t cap = (uint64_t)s.rescue_base16[b + 1] - s.rescue_base16[b];
+            if (!cap) continue;
+            int W, K, KL; bin_shape(kBinBase[1] + b, W, K, KL);
+            a.queue = s.d_counters.p + kQueueD16 + b;
+            a.units = s.d_rescue.p + s.rescue_base16[b]; a.n_units = 0;
+            a.n_units_dev = s.d_counters.p + kRescueCount16 + b;
+            CU(h, launch_forward(Variant::F64_PK, W, K, KL, a, grid_for(Variant::F64_PK, kBinBase[1] + b, cap), st));
+            h->stats.kernel_launches += 1;
+        }
+        st32 = s.stream2;
+        CU(h, cudaStreamWaitEvent(st32, s.ev_fork, 0));
+    }
+    for (int b = 0; b < (all_double ? kNumBins : kNumBinsW32); ++b) {
         int W, K, KL; bin_shape(b, W, K, KL);
-        a.queue = s.d_counters.p + kQueueD + b;
+        // use_double: the FP32 pass' queues are free, one per bin of any width
+        a.queue = s.d_counters.p + (all_double ? kQueueF : kQueueD) + b;
         int grid;
-        if (all_double) {      // every unit straight to the FP64 kernels (the chunk was binned at W = 32)
+        if (all_double) {      // every unit straight to the FP64 kernels (the chunk was binned for them: choose_width)
             const uint32_t n = s.bin_start[b + 1] - s.bin_start[b];
             if (!n) continue;
             a.units = s.d_units.p + s.bin_start[b]; a.n_units = n; a.n_units_dev = nullptr;
@@ -783,8 +843,12 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s, bool replay) {
             a.n_units_dev = s.d_counters.p + kRescueCount + b;
             grid = grid_for(vd, b, cap);
         }
-        CU(h, launch_forward(vd, W, K, KL, a, grid, st));
+        CU(h, launch_forward(vd, W, K, KL, a, grid, st32));
         h->stats.kernel_launches += 1;
+    }
+    if (st32 != st) {
+        CU(h, cudaEventRecord(s.ev_join, st32));
+        CU(h, cudaStreamWaitEvent(st, s.ev_join, 0));
     }
     if (const uint32_t n_long = s.bin_start[kNumBins + 1] - s.bin_start[kNumBins]) {
         // reads longer than 384 bases: row stripes, one warp per pair, float + threshold + double + log10 in one kernel;
@@ -833,6 +897,17 @@ int download_chunk(pairhmm_cuda_handle *h, Slot &s) {
     return PAIRHMM_OK;
 }
 
+// PAIRHMM_CUDA_TRACE: what the scan made of the chunk's underflowed pairs (the stream is idle)
+static void trace_rescue_counts(pairhmm_cuda_handle *h, Slot &s) {
+    std::vector<uint32_t> c(kCounterWords);
+    if (cudaMemcpy(c.data(), s.d_counters.p, sizeof(uint32_t) * kCounterWords, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    uint64_t u32 = 0, u16 = 0;
+    for (int b = 0; b < kNumBinsW32; ++b) u32 += c[kRescueCount + b];
+    for (int b = 0; b < kNumBinsW16; ++b) u16 += c[kRescueCount16 + b];
+    std::fprintf(stderr, "[trace d%d] rescue: %u pairs underflowed of %u; units of one read %llu, of two reads %llu; candidates %u (mode %u)\n",
+                 h->device, c[kRescuedPairs], s.n_upairs, (unsigned long long)u32, (unsigned long long)u16, c[kPendingCount], s.pair_mode);
+}
+
 // Waits for the slot's stream, then maps unique (read, hap) results back to every input read
 // (VectorLoglessPairHMM.cpp:123-125: read-major, duplicates share their unique read's row).
 int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
@@ -843,6 +918,7 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
         cudaEventElapsedTime(&ms_f, s.ev_begin, s.ev_float_done);
         cudaEventElapsedTime(&ms_all, s.ev_begin, s.ev_end);
     }
+    if (trace_on()) trace_rescue_counts(h, s);
     if (trace_on() && g_trace_base) {
         float b0 = 0.f, b1 = 0.f;
         cudaEventElapsedTime(&b0, g_trace_base, s.ev_begin); cudaEventElapsedTime(&b1, g_trace_base, s.ev_end);
@@ -1013,6 +1089,9 @@ int pairhmm_cuda_create(const pairhmm_cuda_config *cfg, pairhmm_cuda_handle **ou
 #undef UP
     for (auto &s : h->slots) {
         if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&s.stream2, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.ev_join, cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreate(&s.ev_begin) != cudaSuccess || cudaEventCreate(&s.ev_float_done) != cudaSuccess ||
             cudaEventCreate(&s.ev_fwd_done) != cudaSuccess ||
             cudaEventCreate(&s.ev_end) != cudaSuccess)
@@ -1565,6 +1644,7 @@ int pairhmm_cuda_resident_run(pairhmm_cuda_handle *h, float *kernel_ms, float *f
     int st = run_kernels(h, s, true);
     if (st != PAIRHMM_OK) return st;
     CU(h, cudaStreamSynchronize(s.stream));
+    if (trace_on()) trace_rescue_counts(h, s);
     float a = 0.f, b = 0.f;
     CU(h, cudaEventElapsedTime(&a, s.ev_begin, s.ev_end));
     CU(h, cudaEventElapsedTime(&b, s.ev_begin, s.ev_fwd_done));   // FP32 forward kernels only (no finalize)

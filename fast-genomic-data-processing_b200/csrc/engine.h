@@ -58,6 +58,7 @@ struct RegionPlan {
     struct BinRun { uint16_t bin; uint32_t first, n_reads, unit_off; };
     std::vector<BinRun> runs;
     uint32_t pairs32[kNumBinsW32] = {0};   // unique pairs per W=32 bin (bounds that bin's FP64 rescue list)
+    uint32_t pairs16[kNumBinsW16] = {0};   // the same per W=16 bin, reads the W=16 FP64 kernel takes (two of them per unit)
     uint8_t gcp_min = 255, gcp_max = 0;    // range of the (masked) gap-continuation bytes of the unique reads
     std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
     std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
@@ -72,6 +73,8 @@ struct RegionPlan {
 // Everything one in-flight chunk needs: pinned staging, device mirrors, stream, events.
 struct Slot {
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;   // FP64 pass: the units of one read run beside the units of two reads (run_kernels)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_fwd_done = nullptr, ev_float_done = nullptr, ev_end = nullptr;
     // host staging
     PinnedBuf<uint8_t> h_rd, h_hapbytes, h_flag;
@@ -121,6 +124,10 @@ struct Slot {
     uint64_t hap_bytes = 0;
     uint32_t bin_start[kNumBins + 2] = {0};   // units of bin b are [bin_start[b], bin_start[b+1]); bin kLongBin = long reads (long.cu)
     uint32_t rescue_base[kNumBinsW32 + 1] = {0}; // W=32 bin b appends its rescue units at d_rescue + rescue_base[b]
+    uint32_t rescue_base16[kNumBinsW16 + 1] = {0}; // ... and W=16 bin b its units of two reads (behind the W=32 lists)
+    uint32_t pair_mode = 0;                   // RescueScanArgs::pair_mode of this chunk (0: no W=16 lists, no pending area)
+    uint32_t pending_off = 0;                 // first entry of the pairing candidates' area in d_rescue
+    DevBuf<uint32_t> d_pair_table;            // kPairSlots words, zero between chunks
     Variant float_variant = Variant::F32_GEN; // kernels this chunk was binned for
     bool uniform_gcp = false;                 // every gcp byte of the chunk equals gcp_value -> UG kernels
     uint8_t gcp_value = 0;

@@ -172,12 +172,16 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
         if (u >= n_units) break;
         const DevUnit unit = a.units[u];
         uint32_t unit_nh = unit.shape & 0xffu;
-        const uint32_t unit_nreads = (unit.shape >> 8) & 0xffu, stride = unit.shape >> 16;
+        uint32_t unit_nreads = (unit.shape >> 8) & 0xffu, rstep = 1u;
+        const uint32_t stride = unit.shape >> 16;
+        // a rescue unit of the W = 16 FP64 instance holds two reads of one region that need not be neighbours: the field is
+        // the distance between them (rescue_scan_kernel, kernels.cu)
+        if constexpr (F64 && W == 16) if (a.rescue_filter) { rstep = unit_nreads; unit_nreads = 2u; }
         // a partial unit leaves halves without a read: they recompute read 0 and emit nothing
         const uint32_t ra = (uint32_t)P::kReads * (uint32_t)seg, rb = ra + (uint32_t)P::kReads - 1u;
         const bool valid_a = ra < unit_nreads, valid_b = rb < unit_nreads;
-        const uint32_t read_a = unit.read + (valid_a ? ra : 0u), read_b = unit.read + (valid_b ? rb : 0u);
-        const uint32_t out_a = unit.out + ra * stride, out_b = unit.out + rb * stride;
+        const uint32_t read_a = unit.read + (valid_a ? ra * rstep : 0u), read_b = unit.read + (valid_b ? rb * rstep : 0u);
+        const uint32_t out_a = unit.out + ra * rstep * stride, out_b = unit.out + rb * rstep * stride;
         const DevRead rra = a.reads[read_a], rrb = a.reads[read_b];
         const int last_a = (rra.len - 1) / K, last_b = (rrb.len - 1) / K;   // lane that owns the last row (slot KL)
 
@@ -230,7 +234,10 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
             // a rescue unit (rescue_scan_kernel) names the read's whole haplotype run: sweep only those whose FP32 sum
             // fell below the reference's threshold (IntelPairHmm.cc:342), back to back -- one pipeline fill per read
             bool keep = (uint32_t)lane < unit_nh;
-            if (a.rescue_filter && keep) keep = a.fres[unit.out + lane] < 1e-28f;
+            if (a.rescue_filter && keep) {
+                keep = a.fres[unit.out + lane] < 1e-28f;
+                if constexpr (W == 16) keep |= a.fres[unit.out + rstep * stride + lane] < 1e-28f;   // either read needs it
+            }
             const uint32_t km = __ballot_sync(kFull, keep);
             unit_nh = (uint32_t)__popc(km);
             if (keep) {
@@ -301,6 +308,8 @@ __device__ __forceinline__ void wide_forward(const KernelArgs &a) {
                 a.fres[my_out + cur] = r;
             } else {
                 const uint32_t o = my_out + hap_info[cur].idx;
+                // two reads per warp sweep the union of what either needs: a pair whose FP32 result stands keeps it
+                if (W == 16 && a.rescue_filter && !(a.fres[o] < 1e-28f)) return;
                 a.out[o] = log10(flush_denormal(r)) - a.log10_init_d;              // IntelPairHmm.cc:344
                 a.flag[o] = 1;
             }

@@ -43,7 +43,48 @@ __global__ void finalize_kernel(const FinalizeArgs a) {
     a.flag[i] = 0;
 }
 
-// One thread per (FP32 work unit, read of the unit): any pair of the read below the threshold -> one FP64 unit.
+// ---- FP64 rescue lists --------------------------------------------------------------------------------------------
+__device__ __forceinline__ int bin_w32(int len) { const int k = (len + 31) >> 5; return k * (k - 1) / 2 + (len - 1) % k; }
+__device__ __forceinline__ int bin_w16(int len) { const int k = (len + 15) >> 4; return k * (k - 1) / 2 + (len - 1) % k; }
+// a unit of one read for the W = 32 FP64 kernel
+__device__ __forceinline__ void emit_single(const RescueScanArgs &a, int bin32, uint32_t read, uint32_t hap_list, uint32_t nh, uint32_t out) {
+    const uint32_t slot = a.rescue_base[bin32] + atomicAdd(a.rescue_count + bin32, 1u);
+    a.rescue_units[slot] = DevUnit{read, hap_list, unit_shape(nh, 1u, 0u), out};
+}
+// Candidate `me` (shape = haplotypes | W = 16 bin << 8 | row stride << 16) looks for a read of the same bin that needs the same
+// haplotype run: the table holds, per hash slot, one waiting candidate (index into a.pending, + 1). Found: both leave as ONE
+// unit of the W = 16 kernel, {lower read, run, haplotypes | distance between the reads << 8 | stride << 16}. An occupant that
+// does not fit (hash collision, reads too far apart) stays; `me` then leaves alone, as whoever still waits when the scan ends
+// does (rescue_flush_kernel). Which reads meet depends on timing; every pair's arithmetic does not.
+__device__ void pair_or_wait(const RescueScanArgs &a, const DevUnit me, int len, int neighbourhood) {
+    const uint32_t idx = atomicAdd(a.pending_count, 1u);
+    a.pending[idx] = me;
+    __threadfence();
+    // partners are sought among the 2^neighbourhood reads around this one: a slot then sees a handful of candidates, not
+    // every underflowed read of a deep region (2000 reads x 16 runs on 16 words: the scan took longer than it saved)
+    const uint32_t key = me.hap_list * 0x9E3779B1u ^ ((me.shape >> 8) & 0xffu) * 0x85EBCA6Bu ^ (me.read >> neighbourhood) * 0xC2B2AE35u;
+    uint32_t *slot = a.pair_table + ((key >> 12) & (kPairSlots - 1u));
+    for (;;) {
+        const uint32_t old = atomicCAS(slot, 0u, idx + 1u);
+        if (old == 0u) return;                                    // waiting
+        const uint4 q = __ldcg(reinterpret_cast<const uint4 *>(a.pending + (old - 1u)));
+        const DevUnit c{q.x, q.y, q.z, q.w};
+        const uint32_t dist = c.read > me.read ? c.read - me.read : me.read - c.read;
+        if (c.hap_list != me.hap_list || c.shape != me.shape || dist == 0u || dist > 255u) {
+            emit_single(a, bin_w32(len), me.read, me.hap_list, me.shape & 0xffu, me.out);
+            return;
+        }
+        if (atomicCAS(slot, old, 0u) == old) {
+            const DevUnit &lo = c.read < me.read ? c : me;
+            const int b16 = (int)((me.shape >> 8) & 0xffu);
+            const uint32_t at = a.rescue_base16[b16] + atomicAdd(a.rescue_count16 + b16, 1u);
+            a.rescue_units[at] = DevUnit{lo.read, lo.hap_list, (me.shape & 0xffff00ffu) | dist << 8, lo.out};
+            return;
+        }
+    }
+}
+
+// One thread per (FP32 work unit, read of the unit): the read's pairs below the threshold -> units of the FP64 pass.
 __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t u = t / kMaxUnitReads, j = t % kMaxUnitReads;
@@ -54,8 +95,31 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     const uint32_t out = unit.out + j * stride;
     const int len = a.reads[unit.read + j].len;
     if (len < 1) return;
-    const int k32 = (len + 31) >> 5;                   // the FP64 kernels run at W = 32
-    const int bin = k32 * (k32 - 1) / 2 + (len - 1) % k32;
+    const uint32_t rescued = *a.rescued_pairs;
+    // Reads of up to 16 x kMaxKF64W16 rows go to the W = 16 instance of the FP64 kernel two at a time when the chunk has
+    // underflowed pairs enough to fill the GPU that way: twice the rows per lane halve the per-cell share of the shuffles,
+    // selects and loop overhead (1544 -> 1741 GCUPS with every pair of BASELINE configs[1] through the FP64 kernel). Both reads of
+    // a unit sweep the same haplotypes, so a candidate is (read, FIXED run of its FP32 unit's haplotypes, `per` of them) with
+    // at least one underflowed pair; the kernel sweeps the union of what the two reads need and writes only the pairs that
+    // underflowed. Underflow goes with the read far more than with the haplotype (the haplotypes of a region differ in a few
+    // bases), so the union is rarely larger than either part.
+    if (a.pair_mode && len <= 16 * kMaxKF64W16 && (a.pair_mode == 2u || rescued >= 4u * a.fp64_warp_slots16)) {
+        const uint32_t per = a.max_pairs ? a.max_pairs
+                             : min((uint32_t)kMaxUnitHaps, max(1u, rescued / (8u * a.fp64_warp_slots16)));
+        // 16 to 32 underflowed reads per neighbourhood (an odd one is left over in every other): 2^6 reads when a third of the
+        // pairs underflow, a whole region at 2 %
+        const uint32_t span = min(1u << 16, max(16u, (uint32_t)(32ull * a.n_pairs / max(rescued, 1u))));
+        const int neighbourhood = 31 - __clz((int)span);
+        for (uint32_t first = 0; first < nh; first += per) {
+            const uint32_t n = min(per, nh - first);
+            bool any = false;
+            for (uint32_t i = 0; i < n; ++i) any |= a.fres[out + first + i] < 1e-28f;
+            if (any)
+                pair_or_wait(a, DevUnit{unit.read + j, unit.hap_list + first, n | (uint32_t)bin_w16(len) << 8 | stride << 16, out + first}, len, neighbourhood);
+        }
+        return;
+    }
+    const int bin = bin_w32(len);                      // everything else: one read per warp, W = 32
     // a run of the read's haplotypes with at most max_pairs underflowed ones becomes one FP64 unit: the whole row in a big
     // chunk (one pipeline fill per read), single pairs in a small one (one region per call: the FP64 pass is as long as
     // its longest unit, and a sweep of one 150 x 400 pair alone takes ~25 us)
@@ -63,16 +127,26 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     // all busy; many: runs of pairs, up to the read's whole row (one pipeline fill per unit) -- about four units per
     // resident warp of the FP64 kernel
     const uint32_t max_pairs = a.max_pairs ? a.max_pairs
-                               : min((uint32_t)kMaxUnitHaps, max(1u, *a.rescued_pairs / (4u * a.fp64_warp_slots)));
+                               : min((uint32_t)kMaxUnitHaps, max(1u, rescued / (4u * a.fp64_warp_slots)));
     uint32_t first = 0, cnt = 0;
     for (uint32_t i = 0; i < nh; ++i) {
         cnt += a.fres[out + i] < 1e-28f ? 1u : 0u;
         if (cnt && (cnt == max_pairs || i + 1 == nh)) {
-            const uint32_t slot = a.rescue_base[bin] + atomicAdd(a.rescue_count + bin, 1u);
-            a.rescue_units[slot] = DevUnit{unit.read + j, unit.hap_list + first, unit_shape(i + 1 - first, 1u, 0u), out + first};
+            emit_single(a, bin, unit.read + j, unit.hap_list + first, i + 1 - first, out + first);
             first = i + 1; cnt = 0;
         }
     }
+}
+
+// One thread per slot of the pairing table: who still waits leaves alone; the table is all zero again afterwards.
+__global__ void rescue_flush_kernel(const RescueScanArgs a) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= kPairSlots) return;
+    const uint32_t v = a.pair_table[t];
+    if (!v) return;
+    a.pair_table[t] = 0u;
+    const DevUnit c = a.pending[v - 1u];
+    emit_single(a, bin_w32(a.reads[c.read].len), c.read, c.hap_list, c.shape & 0xffu, c.out);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -211,6 +285,11 @@ cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st) {
     if (a.n_units == 0) return cudaSuccess;
     const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
     rescue_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+cudaError_t launch_rescue_flush(const RescueScanArgs &a, cudaStream_t st) {
+    if (a.n_units == 0 || !a.pair_mode) return cudaSuccess;
+    rescue_flush_kernel<<<kPairSlots / 256, 256, 0, st>>>(a);
     return cudaGetLastError();
 }
 

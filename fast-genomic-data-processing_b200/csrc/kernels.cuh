@@ -122,6 +122,17 @@ struct RescueScanArgs {
                                   // on the device from the chunk's number of underflowed pairs:
     const uint32_t *rescued_pairs;  //   counted by finalize_kernel
     uint32_t fp64_warp_slots;     //   warps of the FP64 kernel resident on the device
+    // Read pairing for the wide FP64 kernel at W = 16 (two reads per warp, rows of up to kMaxKF64W16 per lane): see
+    // rescue_scan_kernel. The lists of the W = 16 bins lie in rescue_units too, behind those of the W = 32 bins.
+    uint32_t pair_mode;           // 0 = off; 1 = when the chunk has enough underflowed pairs to fill the GPU with pairs of reads;
+                                  // 2 = always (testing)
+    DevUnit *pending;             // candidates (a read x a run of its haplotypes) that wait for a partner
+    uint32_t *pending_count;
+    uint32_t *pair_table;         // kPairSlots words, all zero between chunks (rescue_flush_kernel leaves them so)
+    const uint32_t *rescue_base16;
+    uint32_t *rescue_count16;
+    uint32_t fp64_warp_slots16;   // warps of the W = 16 FP64 kernel resident on the device
+    uint32_t n_pairs;             // unique pairs of the chunk
 };
 constexpr int kMaxUnitReads = 8;  // reads of one work unit: 2 * 32 / 8 (packed kernel, 8-lane groups)
 
@@ -182,10 +193,13 @@ struct FinalizeArgs {
 constexpr int kNumWidths = 3;
 constexpr int kWidths[kNumWidths] = {32, 16, 8};
 constexpr int kMaxK[kNumWidths] = {kMaxRowsPerLane, 12, 12};   // rows per lane limit per width
+constexpr int kMaxKF64W16 = 10;     // the wide FP64 kernel at W = 16 (two reads per warp): rows per lane its registers hold
 constexpr int tri(int k) { return k * (k + 1) / 2; }
 constexpr int kBinBase[kNumWidths + 1] = {0, tri(12), tri(12) + tri(12), tri(12) + tri(12) + tri(12)};
 constexpr int kNumBins = kBinBase[kNumWidths];           // 78 + 78 + 78 = 234
 constexpr int kNumBinsW32 = kBinBase[1];
+constexpr int kNumBinsW16 = kBinBase[2] - kBinBase[1];
+constexpr uint32_t kPairSlots = 1u << 15;   // RescueScanArgs::pair_table
 constexpr int kLongBin = kNumBins;                       // pseudo-bin of the reads longer than kMaxReadLen (long.cu)
 
 inline int width_index(int W) { return W == 32 ? 0 : W == 16 ? 1 : W == 8 ? 2 : -1; }
@@ -224,6 +238,7 @@ cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a,
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 cudaError_t launch_forward_long(const LongArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
+cudaError_t launch_rescue_flush(const RescueScanArgs &a, cudaStream_t st);   // after the scan, when a.pair_mode != 0
 cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st);
 cudaError_t launch_prep_reads(const PrepReadsArgs &a, int sm_count, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids

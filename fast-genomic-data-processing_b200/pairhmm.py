@@ -216,7 +216,8 @@ class Engine:
 
     def __init__(self, device=-1, use_double=False, exact_fp32=False, dedup_reads=True, pack_threads=0,
                  chunk_cells=0, force_general=False, lane_group=0, scalar_uniform=False, max_ctas_per_sm=0,
-                 prefix_sharing=False, unit_haps=0, rescue_pairs_per_unit=0, device_mask=0, batch_window_us=0):
+                 prefix_sharing=False, unit_haps=0, rescue_pairs_per_unit=0, device_mask=0, batch_window_us=0,
+                 rescue_read_pairing=0):
         self.lib = load_library()
         cfg = Config()
         self.lib.pairhmm_cuda_default_config(C.byref(cfg))
@@ -231,6 +232,7 @@ class Engine:
         cfg.reserved[4] = int(prefix_sharing)
         cfg.reserved[5] = int(unit_haps)       # haplotypes per work unit (tuning / testing)
         cfg.reserved[6] = int(rescue_pairs_per_unit)   # underflowed pairs per FP64 unit (tuning; 0 = by chunk size)
+        cfg.reserved[7] = int(rescue_read_pairing)     # FP64 pass with two reads per warp: 0 = by chunk size, 1 = never, 2 = always (testing)
         cfg.device_mask = int(device_mask)     # != 0: one handle over these CUDA ordinals (multi-GPU inside the library)
         cfg.batch_window_us = int(batch_window_us)   # > 0: blocking region calls of all such handles share one batcher
         self.h = C.c_void_p()

@@ -97,6 +97,8 @@ typedef struct pairhmm_cuda_config {
                              /* [5] > 0: at most that many haplotypes per work unit (tuning; default: all of a region's, fewer */
                              /*     when the batch is too small to fill the GPU otherwise)                  */
                              /* [6] > 0: underflowed pairs per unit of the FP64 pass (tuning; default by chunk size) */
+                             /* [7]: FP64 pass with two reads per warp where the rows fit: 0 = when the launch group has enough   */
+                             /*     underflowed pairs, 1 = never, 2 = always (testing); results do not depend on it                 */
                              /* [4] != 0: prefix sharing -- same-length haplotypes of a region that share  */
                              /*     a prefix are swept from a checkpoint (the reference's trie,            */
                              /*     VectorLoglessPairHMM.cpp:35,150-286; M2/trie/buildTreeUtils.cpp:155);  */

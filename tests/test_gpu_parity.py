@@ -132,6 +132,54 @@ def test_config3_rescue_heavy(engine, oracle):
     assert wresc.mean() > 0.2
 
 
+def test_rescue_with_two_reads_per_warp_equals_one_read_per_warp(oracle):
+    """FP64 pass, W = 16 instance (config.reserved[7]): reads that underflow are paired up on the device (which two meet depends
+    on timing) and sweep the union of the haplotypes either needs. Forced on for small inputs: the bits of every result and
+    the rescued flags equal those of the one-read-per-warp pass, for every size of the haplotype runs, reads of many
+    lengths (bins of the W = 16 instance, and reads it does not take), duplicate reads and ragged regions; and the oracle
+    agrees. use_double handles take the W = 16 instance for every read that fits."""
+    rng = np.random.default_rng(77)
+    mixed = synth.make_batch(991, [9, 40, 1, 33], [[260, 300, 310], [90] * 7, [400], [333, 350] * 9], 150, profile="lowq", name="mixed-150")
+    lens = synth.concat([synth.make_batch(1000 + R, [6], [[200, 220, 231, 250, 180]], R, profile="lowq", foreign_frac=0.4) for R in
+                         (1, 15, 16, 17, 33, 97, 128, 129, 144, 145, 159, 160, 161, 200)], name="many-read-lengths")
+    off = fgdp_b200.Engine(rescue_read_pairing=1)
+    engines = [fgdp_b200.Engine(rescue_read_pairing=2, rescue_pairs_per_unit=k) for k in (0, 1, 3, 32)]
+    try:
+        for b in (synth.config3(300, 12), mixed, lens, synth.edge_cases(), synth.config2(30, profile="lowq")):
+            want, wresc = off.compute_batch(b)
+            for e in engines:
+                for rep in range(2):
+                    got, gresc = e.compute_batch(b)
+                    assert np.array_equal(got, want) and np.array_equal(gresc, wresc), b.name
+            ow, owr, _ = oracle.compute(b.as_flat(), threads=8)
+            assert_parity(want, wresc, ow, owr, what=b.name)
+        st = engines[0].stats()
+        assert st["rescued_pairs"] > 0
+        # the default decides by the chunk's size: a large launch group pairs, and gives the same bits
+        big = synth.config3(1500, 16)
+        want, wresc = off.compute_batch(big)
+        dflt = fgdp_b200.Engine()
+        try:
+            got, gresc = dflt.compute_batch(big)
+        finally:
+            dflt.close()
+        assert np.array_equal(got, want) and np.array_equal(gresc, wresc) and wresc.mean() > 0.2
+    finally:
+        off.close()
+        for e in engines:
+            e.close()
+    # use_double: W = 16 for the reads that fit, W = 32 for the others, one chunk
+    e = fgdp_b200.Engine(use_double=True)
+    try:
+        for b in (lens, mixed):
+            got, gresc = e.compute_batch(b)
+            ow = oracle.compute(b.as_flat(), threads=8, use_double=True)[0]
+            fin = np.isfinite(ow)
+            assert gresc.all() and np.array_equal(np.isfinite(got), fin) and np.abs(got[fin] - ow[fin]).max() < 1e-9, b.name
+    finally:
+        e.close()
+
+
 def test_config4_long_haps(engine, oracle):
     b = synth.config4(3, 12, 4)
     want, wresc, _ = oracle.compute(b.as_flat(), threads=4)

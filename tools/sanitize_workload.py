@@ -1,5 +1,5 @@
 """Small pass over every kernel of the library for compute-sanitizer (tools/sanitize.sh): packed / scalar / exact FP32
-kernels, FP64 rescue, prefix sharing, raw-read pre-pass, fused epilogue, both Smith-Waterman kernels."""
+kernels, FP64 rescue (one and two reads per warp), prefix sharing, raw-read pre-pass, fused epilogue, both Smith-Waterman kernels."""
 import sys, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -10,7 +10,8 @@ from fgdp_b200 import synth, smithwaterman as sw
 outs = {}
 for name, kw in (("packed", {}), ("scalar_ug", {"scalar_uniform": True}), ("general", {"force_general": True}),
                  ("exact", {"exact_fp32": True}), ("double", {"use_double": True}), ("w8", {"lane_group": 8}), ("w32", {"lane_group": 32}),
-                 ("prefix", {"prefix_sharing": 2, "unit_haps": 32})):
+                 ("prefix", {"prefix_sharing": 2, "unit_haps": 32}), ("rescue_pairs", {"rescue_read_pairing": 2}),
+                 ("rescue_pairs_1", {"rescue_read_pairing": 2, "rescue_pairs_per_unit": 1})):
     e = fgdp_b200.Engine(**kw)
     for b in (synth.config1("lowq"), synth.edge_cases(), synth.snv_family(3, 20, 9, 150, 203, indel_frac=0.2)):
         out, resc = e.compute_batch(b)
