@@ -11,6 +11,7 @@
 #include <mutex>
 #include <thread>
 
+#include "hostcopy.h"
 #include "hostpool.h"
 #include "tables.h"
 
@@ -229,7 +230,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
         if (r.len < 0 || (r.len > 0 && (!r.bases || !r.base_q || (!rv.raw && (!r.ins_q || !r.del_q || !r.gcp)))))
             return fail(h, PAIRHMM_ERR_ARG, "bad read");
         pl.read_len_sum += (uint64_t)r.len;
-        if (r.len == 0) continue;   // undefined in the reference; reported as -inf, see scatter
+        if (r.len == 0) { pl.identity = false; continue; }   // undefined in the reference; reported as -inf, see scatter
         uint32_t u = kNoRead;
         if (!table.empty()) {
             const uint64_t hv = hash_read(r);
@@ -264,6 +265,7 @@ int plan_region(pairhmm_cuda_handle *h, const RegionView &rv, RegionPlan &pl, ui
             }
         }
         pl.uniq_of_read[i] = u;
+        pl.identity &= u == (uint32_t)i;
     }
     pl.n_uniq = (uint32_t)pl.uniq_src.size();
     pl.hmax = hmax;
@@ -310,6 +312,7 @@ void bin_region(const RegionView &rv, RegionPlan &pl, Variant v, int forced_w, b
     bool sorted = true;
     for (uint32_t j = 1; j < n && sorted; ++j) sorted = bin[j - 1] <= bin[j];
     if (!sorted) {
+        pl.identity = false;
         std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return bin[a] < bin[b]; });
         std::vector<uint32_t> src(n);
         for (uint32_t j = 0; j < n; ++j) { src[j] = pl.uniq_src[order[j]]; inv[order[j]] = j; }
@@ -615,15 +618,16 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
         ReadRef run0{}; uint64_t run_ro = 0, run_len = 0;
         auto flush = [&] {
             if (!run_len) return;
+            // the next reader of the arena is the copy engine: streaming stores (hostcopy.h; runs below 512 bytes are memcpy'd)
             uint8_t *d = s.h_rd.p + run_ro;
-            std::memcpy(d, run0.bases, run_len); std::memcpy(d + s.plane, run0.base_q, run_len);
+            copy_stream(d, run0.bases, run_len); copy_stream(d + s.plane, run0.base_q, run_len);
             if (!s.raw_on) {
-                std::memcpy(d + 2 * s.plane, run0.ins_q, run_len); std::memcpy(d + 3 * s.plane, run0.del_q, run_len);
-                if (!s.skip_gcp) std::memcpy(d + 4 * s.plane, run0.gcp, run_len);
+                copy_stream(d + 2 * s.plane, run0.ins_q, run_len); copy_stream(d + 3 * s.plane, run0.del_q, run_len);
+                if (!s.skip_gcp) copy_stream(d + 4 * s.plane, run0.gcp, run_len);
             } else if (s.raw_indel_q) {
                 // planes 2-4 are filled on the device unless some read of the chunk has its own indel qualities
-                if (run0.ins_q) std::memcpy(d + 2 * s.plane, run0.ins_q, run_len); else std::memset(d + 2 * s.plane, 45, run_len);
-                if (run0.del_q) std::memcpy(d + 3 * s.plane, run0.del_q, run_len); else std::memset(d + 3 * s.plane, 45, run_len);
+                if (run0.ins_q) copy_stream(d + 2 * s.plane, run0.ins_q, run_len); else std::memset(d + 2 * s.plane, 45, run_len);
+                if (run0.del_q) copy_stream(d + 3 * s.plane, run0.del_q, run_len); else std::memset(d + 3 * s.plane, 45, run_len);
             }
             run_len = 0;
         };
@@ -677,6 +681,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
             s.h_haplist.p[p.hap_list_off + q] = p.first_hap + (uint32_t)q;
             ho += (uint64_t)hp.len; wo += hap_words(hp.len);
         }
+        copy_stream_fence();
     });
     // A chunk of few units (a handful of waves of warps) ends when its slowest warp does: hand the long units out first
     // (LPT). Large chunks keep the packing order -- their tail is a fraction of a per cent and sorting a million units is not free.
@@ -928,12 +933,28 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
     h->stats.gpu_ms_float += ms_f; h->stats.gpu_ms_double += ms_all - ms_f; h->stats.gpu_ms_total += ms_all;
     auto t0 = clk::now();
     std::atomic<uint64_t> rescued{0}, uniq_pairs{0};
+    const bool stream_out = s.n_upairs >= (1u << 18);
     parallel_for(s.regions.size(), threads, 16, [&](size_t i) {
         const RegionView &rv = s.regions[i];
         const RegionPlan &p = s.plans[i];
         const size_t nh = (size_t)rv.n_haps;
         uint64_t resc = 0;
-        for (int r = 0; r < rv.n_reads; ++r) {
+        // every read unique, none empty, none moved by the binning: the region's block of the chunk's matrix IS the caller's
+        // matrix -- one copy instead of one per read (streaming stores for a large chunk: the caller reads it much later)
+        const bool whole = p.identity && p.hap_order.empty() && rv.n_reads > 0 && nh > 0;
+        if (whole) {
+            const size_t n = (size_t)rv.n_reads * nh;
+            if (stream_out) {
+                copy_stream(rv.out, s.h_out.p + p.upair_off, n * sizeof(double));
+                if (rv.resc) copy_stream(rv.resc, s.h_flag.p + p.upair_off, n);
+                copy_stream_fence();
+            } else {
+                std::memcpy(rv.out, s.h_out.p + p.upair_off, n * sizeof(double));
+                if (rv.resc) std::memcpy(rv.resc, s.h_flag.p + p.upair_off, n);
+            }
+            if (s.ep_on && rv.summ) std::memcpy(rv.summ, s.h_summ.p + p.first_uniq, sizeof(phmm_read_summary) * (size_t)rv.n_reads);
+        }
+        for (int r = 0; r < rv.n_reads && !whole; ++r) {
             const uint32_t u = p.uniq_of_read[r];
             double *o = rv.out + (size_t)r * nh;
             uint8_t *f = rv.resc ? rv.resc + (size_t)r * nh : nullptr;

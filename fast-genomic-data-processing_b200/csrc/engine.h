@@ -63,6 +63,7 @@ struct RegionPlan {
     std::vector<uint32_t> uniq_of_read;  // per input read: local unique index, or 0xffffffff for len==0
     std::vector<uint32_t> uniq_src;      // per local unique read: index of its first occurrence
     bool any_indel_q = false;            // raw reads: some read has its own insertion / deletion qualities
+    bool identity = true;                // unique read j is input read j for every j (no duplicates, no empty reads, no re-ordering)
     // prefix sharing (Variant::F32_PFX): the region's haplotypes are laid out ordered by (length, bytes)
     std::vector<uint32_t> hap_order;     // position in the chunk -> index in the caller's list (empty = identity)
     std::vector<uint2> hap_plan;         // sweep plan per position (kernels.cuh: pfx_plan)
