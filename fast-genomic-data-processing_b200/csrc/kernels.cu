@@ -51,18 +51,21 @@ __device__ __forceinline__ void emit_single(const RescueScanArgs &a, int bin32, 
     const uint32_t slot = a.rescue_base[bin32] + atomicAdd(a.rescue_count + bin32, 1u);
     a.rescue_units[slot] = DevUnit{read, hap_list, unit_shape(nh, 1u, 0u), out};
 }
-// Candidate `me` (shape = haplotypes | W = 16 bin << 8 | row stride << 16) looks for a read of the same bin that needs the same
-// haplotype run: the table holds, per hash slot, one waiting candidate (index into a.pending, + 1). Found: both leave as ONE
+// Candidate `me` (shape = haplotypes | W = 16 bin << 8 | 16-bit hash of its underflow pattern << 16) looks for a read of the same
+// bin that needs the same haplotypes of the same run: the table holds, per hash slot, one waiting candidate (index into
+// a.pending, + 1). The kernel sweeps the union of what the two reads of a unit need, so two reads with different patterns would
+// each pay for the other's haplotypes (BASELINE configs[4]: half a row underflows on average, pairs of any two reads made the
+// pass 13 % slower, not faster); a collision of the pattern hash costs time, never a result. Found: both leave as ONE
 // unit of the W = 16 kernel, {lower read, run, haplotypes | distance between the reads << 8 | stride << 16}. An occupant that
 // does not fit (hash collision, reads too far apart) stays; `me` then leaves alone, as whoever still waits when the scan ends
 // does (rescue_flush_kernel). Which reads meet depends on timing; every pair's arithmetic does not.
-__device__ void pair_or_wait(const RescueScanArgs &a, const DevUnit me, int len, int neighbourhood) {
+__device__ void pair_or_wait(const RescueScanArgs &a, const DevUnit me, int len, int neighbourhood, uint32_t stride) {
     const uint32_t idx = atomicAdd(a.pending_count, 1u);
     a.pending[idx] = me;
     __threadfence();
     // partners are sought among the 2^neighbourhood reads around this one: a slot then sees a handful of candidates, not
     // every underflowed read of a deep region (2000 reads x 16 runs on 16 words: the scan took longer than it saved)
-    const uint32_t key = me.hap_list * 0x9E3779B1u ^ ((me.shape >> 8) & 0xffu) * 0x85EBCA6Bu ^ (me.read >> neighbourhood) * 0xC2B2AE35u;
+    const uint32_t key = me.hap_list * 0x9E3779B1u ^ (me.shape >> 8) * 0x85EBCA6Bu ^ (me.read >> neighbourhood) * 0xC2B2AE35u;
     uint32_t *slot = a.pair_table + ((key >> 12) & (kPairSlots - 1u));
     for (;;) {
         const uint32_t old = atomicCAS(slot, 0u, idx + 1u);
@@ -78,7 +81,7 @@ __device__ void pair_or_wait(const RescueScanArgs &a, const DevUnit me, int len,
             const DevUnit &lo = c.read < me.read ? c : me;
             const int b16 = (int)((me.shape >> 8) & 0xffu);
             const uint32_t at = a.rescue_base16[b16] + atomicAdd(a.rescue_count16 + b16, 1u);
-            a.rescue_units[at] = DevUnit{lo.read, lo.hap_list, (me.shape & 0xffff00ffu) | dist << 8, lo.out};
+            a.rescue_units[at] = DevUnit{lo.read, lo.hap_list, (me.shape & 0xffu) | dist << 8 | stride << 16, lo.out};
             return;
         }
     }
@@ -112,10 +115,12 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
         const int neighbourhood = 31 - __clz((int)span);
         for (uint32_t first = 0; first < nh; first += per) {
             const uint32_t n = min(per, nh - first);
-            bool any = false;
-            for (uint32_t i = 0; i < n; ++i) any |= a.fres[out + first + i] < 1e-28f;
-            if (any)
-                pair_or_wait(a, DevUnit{unit.read + j, unit.hap_list + first, n | (uint32_t)bin_w16(len) << 8 | stride << 16, out + first}, len, neighbourhood);
+            uint32_t pattern = 0;
+            for (uint32_t i = 0; i < n; ++i) pattern |= (a.fres[out + first + i] < 1e-28f ? 1u : 0u) << i;
+            if (pattern)
+                pair_or_wait(a, DevUnit{unit.read + j, unit.hap_list + first,
+                                        n | (uint32_t)bin_w16(len) << 8 | ((pattern * 0x9E3779B1u) >> 16) << 16, out + first},
+                             len, neighbourhood, stride);
         }
         return;
     }

@@ -7,7 +7,7 @@ import fgdp_b200
 from fgdp_b200 import synth
 which = sys.argv[1] if len(sys.argv) > 1 else "c3"
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 2000
-b = {"c3": lambda: synth.config3(), "c2": lambda: synth.config2(n), "c4": lambda: synth.config4(),
+b = {"c3": lambda: synth.config3(), "c2": lambda: synth.config2(n), "c4": lambda: synth.config4(), "c5": lambda: synth.config5(n),
      "c3x": lambda: synth.concat([synth.config3(2000, 32)] * 1 + [synth.make_batch(7 + k, [2000], [[600] * 32], 150, profile="lowq") for k in range(n)])}[which]()
 ref = None
 for mode, per in ((1, 0), (0, 0), (2, 1), (2, 2), (2, 3), (2, 4), (2, 5), (2, 6), (2, 8), (2, 32), (1, 0)):
