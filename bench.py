@@ -322,8 +322,8 @@ def main():
                     "150 bp reads, 250-500 bp haps, per GPU" % args.regions)
     cells, pairs = batch.cells(), batch.n_pairs
     # several ranks share the box's host threads: split them instead of 16 packing threads per rank
-    eng = fgdp_b200.Engine(device=local, pack_threads=0 if world == 1 else max(2, min(16, (os.cpu_count() or 16) // world)),
-                           prefix_sharing=args.workload == "snv")
+    per_rank = int(os.environ.get("BENCH_PACK_THREADS", "0")) or max(2, min(16, (os.cpu_count() or 16) // world))
+    eng = fgdp_b200.Engine(device=local, pack_threads=0 if world == 1 else per_rank, prefix_sharing=args.workload == "snv")
     eng.initialize(int(batch.read_len.max()), int(batch.hap_len.max()))
 
     # ---- device-resident replay: `value` and the roofline of the FP32 forward kernel
