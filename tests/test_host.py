@@ -149,3 +149,39 @@ def test_reference_side_adapter_compiles():
     if r.returncode == 77:
         pytest.skip("reference tree absent")
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_streaming_copy_equals_memcpy(tmp_path):
+    """csrc/hostcopy.cpp (the packer's and the scatter's copies with non-temporal stores): every size around the thresholds,
+    every source / destination alignment, bytes before and after the destination untouched. Host code: compiled and run here."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    csrc = os.path.join(root, "fast-genomic-data-processing_b200", "csrc")
+    main = tmp_path / "t.cpp"
+    main.write_text(r'''
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "hostcopy.h"
+int main() {
+    std::vector<unsigned char> src(1 << 16), dst(1 << 16), want(1 << 16);
+    for (size_t i = 0; i < src.size(); ++i) src[i] = (unsigned char)(i * 131 + 7);
+    const size_t sizes[] = {0, 1, 31, 32, 33, 127, 128, 129, 511, 512, 513, 640, 1000, 4096, 4097, 30000, 60000};
+    long checked = 0;
+    for (size_t n : sizes)
+        for (size_t da = 0; da < 67; da += (n > 4096 ? 13 : 1))
+            for (size_t sa = 0; sa < 35; sa += (n > 4096 ? 11 : 3)) {
+                std::memset(dst.data(), 0xEE, dst.size()); std::memset(want.data(), 0xEE, want.size());
+                std::memcpy(want.data() + 64 + da, src.data() + sa, n);
+                phmm::copy_stream(dst.data() + 64 + da, src.data() + sa, n);
+                phmm::copy_stream_fence();
+                if (std::memcmp(dst.data(), want.data(), dst.size())) { std::printf("FAIL n=%zu da=%zu sa=%zu\n", n, da, sa); return 1; }
+                ++checked;
+            }
+    std::printf("ok %ld\n", checked);
+    return 0;
+}
+''')
+    exe = tmp_path / "t"
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", csrc, str(main), os.path.join(csrc, "hostcopy.cpp"), "-o", str(exe)], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.startswith("ok"), r.stdout + r.stderr
