@@ -788,8 +788,14 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s, bool replay) {
         }
         if (s.timed) CU(h, cudaEventRecord(s.ev_fwd_done, st));
         FinalizeArgs f{s.d_fres.p, s.d_out.p, s.d_flag.p, s.n_upairs, h->log10_init_f, s.d_counters.p + kRescuedPairs};
-        CU(h, launch_finalize(f, st));
-        if (s.n_upairs) h->stats.kernel_launches += 1;
+        // a chunk of fewer pairs than would ever make the scan group them (max_pairs = rescued / (4 x resident FP64 warps) < 2):
+        // finalize and scan in one launch (a region per call: one launch of five less)
+        static const bool no_fuse = std::getenv("PAIRHMM_CUDA_NO_FUSED_SCAN") != nullptr;
+        const bool fused_scan = !no_fuse && !s.pair_mode && h->cfg.reserved[6] <= 0 && s.n_upairs < 8u * (uint32_t)h->sm_count * 12u;
+        if (!fused_scan) {
+            CU(h, launch_finalize(f, st));
+            if (s.n_upairs) h->stats.kernel_launches += 1;
+        }
         RescueScanArgs r{s.d_units.p, s.bin_start[kNumBins], s.d_reads.p, s.d_fres.p, s.d_rescue.p,
                          s.d_counters.p + kRescueBaseDev, s.d_counters.p + kRescueCount,
                          // 0 = chosen on the device from the number of underflowed pairs finalize_kernel counted
@@ -801,7 +807,8 @@ int run_kernels(pairhmm_cuda_handle *h, Slot &s, bool replay) {
         r.rescue_base16 = s.d_counters.p + kRescueBase16Dev; r.rescue_count16 = s.d_counters.p + kRescueCount16;
         r.fp64_warp_slots16 = (uint32_t)h->sm_count * 8u;
         r.n_pairs = s.n_upairs;
-        CU(h, launch_rescue_scan(r, st));
+        if (fused_scan) CU(h, launch_finalize_scan_small(r, f, st));
+        else CU(h, launch_rescue_scan(r, st));
         if (r.n_units) h->stats.kernel_launches += 1;
         if (r.n_units && r.pair_mode) {
             CU(h, launch_rescue_flush(r, st));

@@ -143,6 +143,34 @@ __global__ void rescue_scan_kernel(const RescueScanArgs a) {
     }
 }
 
+// finalize_kernel + rescue_scan_kernel in ONE launch for a chunk so small that the scan would make single-pair units whatever
+// underflows (fewer unique pairs than 2 x 4 x the FP64 kernel's resident warps: a region per call). One thread per (FP32 work
+// unit, read): a launch less on a path whose kernels run for 50 us each.
+__global__ void finalize_scan_small_kernel(const RescueScanArgs a, const FinalizeArgs f) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t u = t / kMaxUnitReads, j = t % kMaxUnitReads;
+    if (u >= a.n_units) return;
+    const DevUnit unit = a.units[u];
+    const uint32_t nh = unit.shape & 0xffu, nreads = (unit.shape >> 8) & 0xffu, stride = unit.shape >> 16;
+    if (j >= nreads) return;
+    const uint32_t out = unit.out + j * stride;
+    const int len = a.reads[unit.read + j].len;
+    if (len < 1) return;
+    const int bin = bin_w32(len);
+    uint32_t cnt = 0;
+    for (uint32_t i = 0; i < nh; ++i) {
+        const float v = a.fres[out + i];
+        if (v < 1e-28f) {                                  // IntelPairHmm.cc:342
+            emit_single(a, bin, unit.read + j, unit.hap_list + i, 1u, out + i);
+            ++cnt;
+        } else {                                           // IntelPairHmm.cc:348, as finalize_kernel
+            f.out[out + i] = (double)__fsub_rn((float)log10((double)v), f.log10_init_f);
+            f.flag[out + i] = 0;
+        }
+    }
+    if (cnt) atomicAdd(f.rescued_pairs, cnt);
+}
+
 // One thread per slot of the pairing table: who still waits leaves alone; the table is all zero again afterwards.
 __global__ void rescue_flush_kernel(const RescueScanArgs a) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -290,6 +318,12 @@ cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st) {
     if (a.n_units == 0) return cudaSuccess;
     const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
     rescue_scan_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+cudaError_t launch_finalize_scan_small(const RescueScanArgs &a, const FinalizeArgs &f, cudaStream_t st) {
+    if (a.n_units == 0) return cudaSuccess;
+    const uint64_t threads = (uint64_t)a.n_units * kMaxUnitReads;
+    finalize_scan_small_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(a, f);
     return cudaGetLastError();
 }
 cudaError_t launch_rescue_flush(const RescueScanArgs &a, cudaStream_t st) {

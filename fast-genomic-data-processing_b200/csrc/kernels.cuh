@@ -238,7 +238,9 @@ cudaError_t launch_forward(Variant v, int W, int K, int KL, const KernelArgs &a,
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t st);
 cudaError_t launch_forward_long(const LongArgs &a, int grid_blocks, cudaStream_t st);
 cudaError_t launch_rescue_scan(const RescueScanArgs &a, cudaStream_t st);
-cudaError_t launch_rescue_flush(const RescueScanArgs &a, cudaStream_t st);   // after the scan, when a.pair_mode != 0
+cudaError_t launch_rescue_flush(const RescueScanArgs &a, cudaStream_t st);
+// finalize + scan in one launch; valid when the scan would make single-pair units (kernels.cu)
+cudaError_t launch_finalize_scan_small(const RescueScanArgs &a, const FinalizeArgs &f, cudaStream_t st);   // after the scan, when a.pair_mode != 0
 cudaError_t launch_epilogue(const EpilogueArgs &a, cudaStream_t st);
 cudaError_t launch_prep_reads(const PrepReadsArgs &a, int sm_count, cudaStream_t st);
 // resident CTAs per SM of the given instantiation (occupancy API), for sizing persistent grids
