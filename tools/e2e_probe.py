@@ -5,9 +5,9 @@ import numpy as np
 import fgdp_b200
 from fgdp_b200 import synth
 b = synth.config2(int(sys.argv[1]) if len(sys.argv) > 1 else 10000)
-e = fgdp_b200.Engine(chunk_cells=int(float(sys.argv[2])) if len(sys.argv) > 2 else 0)
+e = fgdp_b200.Engine(chunk_cells=int(float(sys.argv[2])) if len(sys.argv) > 2 else 0, pack_threads=int(sys.argv[3]) if len(sys.argv) > 3 else 0)
 out = np.zeros(b.n_pairs); rs = np.zeros(b.n_pairs, np.uint8)
-for i in range(3):
+for i in range(4):
     e.stats_reset()
     print("---- call", i, file=sys.stderr, flush=True)
     t = time.perf_counter(); e.compute_batch(b, out, rs); dt = time.perf_counter() - t
