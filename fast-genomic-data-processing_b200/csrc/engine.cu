@@ -574,10 +574,7 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
                        o_rows = part(s.ep_on ? sizeof(RowInfo) * ((uint64_t)nu + 1) : 0), o_rd = part(0);
         s.meta_bytes = o_rd + s.plane * (uint64_t)s.sent_planes;
         s.ctr_off = o_ctr;
-        // both slots grow to the largest chunk either has held: which slot a call's largest chunk lands in depends on the
-        // ladder, and a slot that met it first in a handle's third call re-allocated its arena then (tens of ms)
-        h->cap_meta_h = std::max<uint64_t>(h->cap_meta_h, s.meta_bytes + 16); h->cap_meta_d = std::max<uint64_t>(h->cap_meta_d, o_rd + s.plane * 5 + 16);
-        RES(h_meta, h->cap_meta_h); RES(d_meta, h->cap_meta_d);
+        RES(h_meta, s.meta_bytes + 16); RES(d_meta, o_rd + s.plane * 5 + 16);
         s.h_reads.set_view(s.h_meta.p + o_reads); s.d_reads.set_view(s.d_meta.p + o_reads);
         s.h_hapoff.set_view(s.h_meta.p + o_hapoff); s.d_hapoff.set_view(s.d_meta.p + o_hapoff);
         s.h_haps.set_view(s.h_meta.p + o_haps); s.d_haps.set_view(s.d_meta.p + o_haps);
@@ -596,14 +593,11 @@ int pack_chunk(pairhmm_cuda_handle *h, Slot &s, const RegionView *regs, size_t n
     {   // results: the log10 values and, behind them, the rescued flags -- one buffer on either side, ONE copy back
         const uint64_t flag_off = sizeof(double) * ((uint64_t)up + 1);
         s.res_bytes = flag_off + (uint64_t)up + 1;
-        h->cap_res = std::max<uint64_t>(h->cap_res, s.res_bytes);
-        RES(h_res, h->cap_res); RES(d_res, h->cap_res);
+        RES(h_res, s.res_bytes); RES(d_res, s.res_bytes);
         s.h_out.set_view(s.h_res.p); s.d_out.set_view(s.d_res.p);
         s.h_flag.set_view(s.h_res.p + flag_off); s.d_flag.set_view(s.d_res.p + flag_off);
     }
-    h->cap_hapw = std::max<uint64_t>(h->cap_hapw, (uint64_t)hw + 4 * kTile); h->cap_fres = std::max<uint64_t>(h->cap_fres, (uint64_t)up + 1);
-    h->cap_rescue = std::max<uint64_t>(h->cap_rescue, s.pair_mode ? (uint64_t)s.pending_off + up + 1 : (uint64_t)up + 1);
-    RES(d_hapw, h->cap_hapw); RES(d_fres, h->cap_fres); RES(d_rescue, h->cap_rescue);
+    RES(d_hapw, (size_t)hw + 4 * kTile); RES(d_fres, up + 1); RES(d_rescue, s.pair_mode ? (size_t)s.pending_off + up + 1 : (size_t)up + 1);
     if (s.pair_mode && !s.d_pair_table.p) {
         RES(d_pair_table, kPairSlots);
         if ((e = cudaMemsetAsync(s.d_pair_table.p, 0, sizeof(uint32_t) * kPairSlots, s.stream)) != cudaSuccess)
@@ -944,7 +938,6 @@ int finish_chunk(pairhmm_cuda_handle *h, Slot &s, int threads) {
                      h->device, ms_since(g_trace_t0), b0, b1, b1 - b0, (double)s.cells);
     }
     h->stats.gpu_ms_float += ms_f; h->stats.gpu_ms_double += ms_all - ms_f; h->stats.gpu_ms_total += ms_all;
-    if (s.timed && ms_all > 0.05f && s.cells > 0) { h->last_gpu_ms = ms_all; h->last_gpu_cells = (double)s.cells; }   // the chunk ladder's GPU rate
     auto t0 = clk::now();
     std::atomic<uint64_t> rescued{0}, uniq_pairs{0};
     const bool stream_out = s.n_upairs >= (1u << 18);
@@ -1257,8 +1250,6 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
     int status = PAIRHMM_OK;
     int chunk_no = 0;
     int ladder = 0;
-    static const bool adaptive_ladder = std::getenv("PAIRHMM_CUDA_FIXED_LADDER") == nullptr;
-    double limit_f = (double)(chunk_cells >> 4), last_pack_ms = 0.0, last_pack_cells = 0.0;
     std::vector<uint64_t> sums;
     size_t summed = 0, sum_block = 128;
     while (i < n_regions && status == PAIRHMM_OK) {
@@ -1270,20 +1261,7 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
         // packing rate differed from call to call, and the slots' grow-only pinned buffers were re-allocated (tens of ms
         // each) in a handle's second and third large call.
         if (chunk_no > 0 && ladder < 4) ++ladder;
-        int64_t chunk_limit = chunk_cells >> (4 - ladder);
-        if (adaptive_ladder && chunk_no > 0) {
-            // x2 only when the host packs at least ~2.4x as fast as the kernels compute: with two slots the GPU waits
-            // pack(next) - kernels(this) at every step up, i.e. (growth / ratio - 1) x this chunk's kernel time. A host that
-            // packs for eight devices at once (ratio ~1.3) climbs in steps of x1.2 instead and loses a launch group's fixed
-            // cost per extra chunk, not a chunk's kernel time per step.
-            double growth = 2.0;
-            if (h->last_gpu_ms > 0.0 && last_pack_ms > 0.0) {
-                const double ratio = (last_pack_cells / last_pack_ms) / (h->last_gpu_cells / h->last_gpu_ms);
-                growth = std::min(2.0, std::max(1.2, 0.85 * ratio));
-            }
-            limit_f = std::min((double)chunk_cells, limit_f * growth);
-            chunk_limit = (int64_t)limit_f;
-        }
+        const int64_t chunk_limit = chunk_cells >> (4 - ladder);
         ++chunk_no;
         int64_t cells = 0;
         uint64_t pairs = 0, rbytes = 0;
@@ -1320,9 +1298,7 @@ int phmm::compute_batch_impl(pairhmm_cuda_handle *h, const RegionView *regions, 
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: chunk of %zu regions cut\n", h->device, ms_since(g_trace_t0), views.size());
         if (s.busy) status = finish_chunk(h, s, threads);
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: slot free, packing\n", h->device, ms_since(g_trace_t0));
-        const auto t_sub = clk::now();
         if (status == PAIRHMM_OK) status = submit_chunk(h, s, views.data(), views.size(), threads);
-        last_pack_ms = ms_since(t_sub); last_pack_cells = (double)cells;
         if (trace_on()) std::fprintf(stderr, "[trace d%d] host %.1f ms: submitted\n", h->device, ms_since(g_trace_t0));
         si ^= 1;
     }

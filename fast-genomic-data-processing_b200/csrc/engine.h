@@ -208,8 +208,6 @@ struct pairhmm_cuda_handle {
     phmm::Slot slots[2];
     int64_t next_ticket = 1;
     int64_t slot_ticket[2] = {0, 0};
-    double last_gpu_ms = 0.0, last_gpu_cells = 0.0;   // kernels of the last timed chunk that finished (the chunk ladder's GPU rate)
-    uint64_t cap_meta_h = 0, cap_meta_d = 0, cap_res = 0, cap_hapw = 0, cap_fres = 0, cap_rescue = 0;   // largest chunk either slot held
     cudaEvent_t prev_end = nullptr;   // end event of the most recently submitted chunk still in flight (kernels of the next one wait on it)
     bool light_call = false;          // set around a single-region submit: no timing events (stats gpu_ms_* stay 0 for it
                                       // unless PAIRHMM_CUDA_TIMING is set), fewer driver calls
